@@ -1,0 +1,143 @@
+/*
+ * rm_b200.h -- C ABI of the B200-native differentiable sphere-tracing path.
+ *
+ * The reference (kyle-rosa/ray_marching) has no FFI layer: its boundary is the Python
+ * nn.Module surface.  Each entry point below names the reference
+ * interface whose *body* it replaces.  Conventions:
+ *   - plain C, no C++/torch types; every pointer is a DEVICE pointer unless the name ends
+ *     in _host; the caller allocates and owns every buffer;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
+ *   - returns 0 on success, a negative RmStatus otherwise; never throws; the message of the
+ *     last failure on the calling thread is available from rm_last_error();
+ *   - no global mutable state: safe to call concurrently on different streams/buffers;
+ *   - all floating point data is IEEE float32, tensors are contiguous, channels last.
+ */
+#ifndef RM_B200_H
+#define RM_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RM_B200_ABI_VERSION 1
+
+typedef enum RmStatus {
+    RM_OK = 0,
+    RM_ERR_INVALID = -1,     /* bad argument (null pointer, negative size, tape too deep ...) */
+    RM_ERR_CUDA = -2,        /* a CUDA runtime call failed; see rm_last_error() */
+    RM_ERR_UNSUPPORTED = -3  /* e.g. tape larger than shared memory */
+} RmStatus;
+
+/* Lowered scene (ray_marching_b200/tape.py).  Replaces the recursive nn.Module tree walk of
+ * scene/primitives.py:11-102 and scene/transformations.py:33-132. */
+typedef struct RmTape {
+    const int32_t* code;   /* [n_instr][4]: head, param offset (float4 units), ordinal, node id */
+    const float*   par;    /* [n_par] parameter records, 16-byte aligned                       */
+    int32_t n_instr;
+    int32_t n_par;         /* multiple of 4 */
+    int32_t max_depth;     /* union nesting depth (<= 8) */
+    int32_t n_nodes;       /* number of union nodes */
+} RmTape;
+
+/* Pinhole camera intrinsics: PinholeCamera.__init__, rendering/ray_marching.py:10-55. */
+typedef struct RmCamera {
+    int32_t n_views;       /* num_cameras */
+    int32_t width;         /* px_width  */
+    int32_t height;        /* px_height */
+    float   focal_length;
+    float   sensor_width;
+    float   sensor_height;
+} RmCamera;
+
+/* Per-view pose record, 20 floats: R[9] row-major (rotation polynomial of the camera quaternion,
+ * quaternion.py:55-72), t[3], fwd[3] = third column of QuaternionToSO3(q) (quaternion.py:114-124,
+ * used by the vignette shader, shader.py:62-66), q[4] (camera quaternion, spin shader
+ * shader.py:157-171), 1 pad. */
+#define RM_POSE_STRIDE 20
+
+/* Shader mode bits; bit m = mode index m of Shader.forward (rendering/shader.py:204-209). */
+enum {
+    RM_MODE_LAMBERTIAN = 1 << 0, RM_MODE_DISTANCE = 1 << 1, RM_MODE_PROXIMITY = 1 << 2,
+    RM_MODE_VIGNETTE = 1 << 3, RM_MODE_NORMAL = 1 << 4, RM_MODE_LAPLACIAN = 1 << 5,
+    RM_MODE_TANGENT = 1 << 6, RM_MODE_SPIN = 1 << 7
+};
+
+/* Global-reduction scratch written by rm_render and consumed by rm_shade_finalize (8 floats):
+ * [0] min, [1] max of the distance-shader log, [2] min, [3] max of the proximity-shader log,
+ * [4] max |laplacian|, [5] NaN seen in distance log, [6] in proximity log, [7] in laplacian.
+ * Plain floats so a tile- or view-sharded job can all-reduce them (MIN/MAX) between the calls. */
+#define RM_REDUCE_FLOATS 8
+
+/* Output planes of the fused render; any pointer may be NULL (plane not produced).
+ * A "ray" is one pixel of one view; planes are indexed by the LOCAL ray index
+ * r - ray_begin, r = (view*height + row)*width + col. */
+typedef struct RmRenderOut {
+    float* origin;      /* [n][3] ray start = pixel position   (PinholeCamera.forward item 0/2) */
+    float* dirs;        /* [n][3] unit ray direction           (PinholeCamera.forward item 3)   */
+    float* pos;         /* [n][3] marched position             (SDFMarcher.forward)             */
+    float* sdf;         /* [n]    f(pos)                       (control.py:244)                 */
+    float* normals;     /* [n][3]                              (SDFNormals.forward item 0)      */
+    float* laplacian;   /* [n]                                 (SDFNormals.forward item 1)      */
+    float* image[8];    /* per shader mode: [n] for modes 0,1,2,3,5, [n][3] for modes 4,6,7     */
+    float* rgba;        /* [n][4] headless display buffer for `display_mode` (alpha = 1); the
+                           reference's torchwindow contract, torchwindow/window.py:146-174       */
+    float* reduce;      /* [RM_REDUCE_FLOATS] scratch, see above; required for modes 1,2,5      */
+} RmRenderOut;
+
+typedef struct RmRenderArgs {
+    int64_t ray_begin;      /* first global ray of this shard */
+    int64_t n_rays;         /* rays in this shard */
+    int32_t steps;          /* marching_steps (reference default 32) */
+    int32_t bounces;        /* reflected-ray segments after the first (0 = reference behaviour) */
+    float   normals_eps;    /* stencil size (RenderLoop default 5e-2) */
+    float   hit_tau;        /* |f| threshold for a reflection hit (config 3: 1e-3) */
+    float   lift_delta;     /* lift along the normal after a hit (config 3: 2*eps) */
+    uint32_t mode_mask;     /* which image[] planes to shade */
+    int32_t display_mode;   /* mode index shaded into rgba, or -1 */
+    int32_t degree;         /* colour-wheel multiplicity of modes 6,7 */
+    int32_t early_exit;     /* 1: stop marching a ray once p stops changing (bit-identical) */
+    int32_t fast_math;      /* 1: approximate sqrt/exp inside march steps (stencil stays IEEE) */
+    const float* cmap;      /* [4096][3] cyclic colour LUT for modes 6,7 (may be NULL otherwise) */
+} RmRenderArgs;
+
+int rm_abi_version(void);
+const char* rm_last_error(void);
+
+/* scene(points) -> sdf.  Replaces the nn.Module call of every scene node
+ * (scene/primitives.py:11,25,40,51,69,91; scene/transformations.py:33,67,90,117,131). */
+int rm_sdf_eval(const RmTape* tape, const float* points, int64_t n_points, float* sdf_out,
+                void* stream);
+
+/* PinholeCamera.forward (rendering/ray_marching.py:57-64): world-space ray origins + directions
+ * for rays [ray_begin, ray_begin + n_rays). */
+int rm_camera_rays(const RmCamera* cam, const float* poses, int64_t ray_begin, int64_t n_rays,
+                   float* origin_out, float* dirs_out, void* stream);
+
+/* SDFMarcher.forward (rendering/ray_marching.py:72-84): p <- f(p) v + p, `steps` times. */
+int rm_march(const RmTape* tape, const float* origin, const float* dirs, int64_t n_rays,
+             int32_t steps, int32_t fast_math, float* pos_out, void* stream);
+
+/* SDFNormals.forward (rendering/ray_marching.py:115-125). */
+int rm_normals(const RmTape* tape, const float* points, int64_t n_points, float normals_eps,
+               float* normals_out, float* laplacian_out, void* stream);
+
+/* RenderLoop.forward (control.py:231-258) fused: camera -> march (+reflected segments) ->
+ * f(p) -> stencil -> per-pixel shaders.  Normalising shaders (modes 1,2,5) leave their
+ * un-normalised value in image[m] and min/max in out->reduce; call rm_shade_finalize next. */
+int rm_render(const RmTape* tape, const RmCamera* cam, const float* poses,
+              const RmRenderArgs* args, const RmRenderOut* out, void* stream);
+
+/* Resets the reduction scratch (call before the rm_render calls that share it). */
+int rm_reduce_init(float* reduce, void* stream);
+
+/* Second phase of DistanceShader / ProximityShader / LaplacianShader (shader.py:34-38,51-55,
+ * 81-89): applies the global min/max normalisation and the 1/2.33 gamma in place. */
+int rm_shade_finalize(const float* reduce, uint32_t mode_mask, int64_t n_rays,
+                      float* const* image, float* rgba, int32_t display_mode, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RM_B200_H */

@@ -1,0 +1,225 @@
+"""Generate tests/golden/*.npz from the UNMODIFIED reference.  TEST INFRASTRUCTURE ONLY.
+
+Run in the build container only (needs /root/reference):
+
+    python -m oracle.make_golden
+
+Everything is float32 CPU, seeded.  The fixtures pin the oracle (tests/test_oracle_golden.py)
+and, through it, the CUDA kernels.  Re-running must reproduce the committed files bit for bit
+on the same torch build.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, ROOT)
+
+from oracle import cases, ref_import  # noqa: E402
+from ray_marching_b200.scene.scene_registry import make_test_scene, make_test_scene2  # noqa: E402
+from ray_marching_b200.scene.synthetic import make_synthetic_scene  # noqa: E402
+
+OUT = os.path.join(ROOT, "tests", "golden")
+
+
+def np32(t):
+    return t.detach().cpu().numpy()
+
+
+def param_list(module):
+    return [(n, p) for n, p in module.named_parameters()]
+
+
+def gen_quaternion(ref, out):
+    g = torch.Generator().manual_seed(11)
+    p = torch.randn(48, 4, generator=g)
+    q = torch.randn(48, 4, generator=g)
+    v = torch.randn(48, 3, generator=g)
+    small = torch.rand(48, 3, generator=g) * 0.5
+    so3 = ref.Q.QuaternionToSO3()
+    out.update({
+        "quat/p": np32(p), "quat/q": np32(q), "quat/v": np32(v), "quat/small": np32(small),
+        "quat/cross": np32(ref.Q.cross_product(v, small)),
+        "quat/multiply": np32(ref.Q.multiply(p, q)),
+        "quat/conjugate": np32(ref.Q.conjugate(q)),
+        "quat/rotation": np32(ref.Q.rotation(v, q)),
+        "quat/to_versor": np32(ref.Q.to_versor(small)),
+        "quat/so3": np32(so3(q[:, None, None, :])),
+        "quat/reflect": np32(ref.make_reflection_directions(
+            torch.nn.functional.normalize(small, dim=-1), v)),
+    })
+
+
+def gen_nodes(ref, out):
+    pts = cases.eval_points()
+    g = torch.Generator().manual_seed(5)
+    w = torch.randn(pts.shape[0], 1, generator=g)
+    # keep the far points out of the weighted sum used for gradients (1e9 swamps fp32)
+    w[14:16] = 0.0
+    out["nodes/points"] = np32(pts)
+    out["nodes/weights"] = np32(w)
+    for name, node in cases.node_cases(ref).items():
+        x = pts.clone().requires_grad_(True)
+        d = node(x)
+        params = param_list(node)
+        grads = torch.autograd.grad((d * w).sum(), [x] + [p for _, p in params],
+                                    allow_unused=True)
+        out[f"nodes/{name}/value"] = np32(d)
+        out[f"nodes/{name}/dpoints"] = np32(grads[0])
+        for (pn, p), gp in zip(params, grads[1:]):
+            out[f"nodes/{name}/dparam/{pn}"] = np32(gp if gp is not None else torch.zeros_like(p))
+    for name, scene in (("test_scene", ref.SR.make_test_scene()),
+                        ("test_scene2", ref.SR.make_test_scene2()),
+                        ("synthetic8_shell", make_synthetic_scene(8, 0, True, classes=ref)),
+                        ("synthetic64", make_synthetic_scene(64, 0, False, classes=ref))):
+        x = pts.clone().requires_grad_(True)
+        d = scene(x)
+        params = param_list(scene)
+        grads = torch.autograd.grad((d * w).sum(), [x] + [p for _, p in params], allow_unused=True)
+        out[f"scenes/{name}/value"] = np32(d)
+        out[f"scenes/{name}/dpoints"] = np32(grads[0])
+        flat = torch.cat([(gp if gp is not None else torch.zeros_like(p)).reshape(-1)
+                          for (_, p), gp in zip(params, grads[1:])])
+        out[f"scenes/{name}/dparams_flat"] = np32(flat)
+        out[f"scenes/{name}/params_flat"] = np32(torch.cat([p.reshape(-1) for _, p in params]))
+
+
+def gen_camera(ref, out):
+    g = torch.Generator().manual_seed(3)
+    q = torch.nn.functional.normalize(torch.randn(2, 4, generator=g), dim=-1)
+    t = torch.randn(2, 3, generator=g)
+    cam = ref.RM.PinholeCamera(2, 8, 6, 17e-3, 24e-3, 18e-3)
+    pos, frames, _, dirs = cam(q, t)
+    out.update({"camera/q": np32(q), "camera/t": np32(t), "camera/pos": np32(pos),
+                "camera/dirs": np32(dirs), "camera/frames": np32(frames),
+                "camera/base_pos": np32(cam.ray_positions), "camera/base_dirs": np32(cam.ray_directions)})
+    # config-1 geometry at full 640x480: three probe pixels
+    c1 = cases.config1_camera(640, 480)
+    cam1 = ref.RM.PinholeCamera(**c1)
+    pos, frames, _, dirs = cam1(torch.tensor([[1.0, 0, 0, 0]]), torch.tensor([[0.0, 0, 1.0]]))
+    sel = ([240, 0, 100], [320, 0, 500])
+    out["camera/c1_pos_sel"] = np32(pos[0][sel])
+    out["camera/c1_dirs_sel"] = np32(dirs[0][sel])
+    scene = ref.SR.make_test_scene2()
+    marched = ref.RM.SDFMarcher(scene)(pos, dirs, 32)
+    normals, lap = ref.RM.SDFNormals(scene, 5e-2)(marched)
+    out["camera/c1_hit_sel"] = np32(marched[0][sel])
+    out["camera/c1_sdf_sel"] = np32(scene(marched)[0][sel])
+    out["camera/c1_normals_sel"] = np32(normals[0][sel])
+    out["camera/c1_lap_sel"] = np32(lap[0][sel])
+
+
+def gen_render(ref, out):
+    W, H = 32, 24
+    intr = cases.config1_camera(W, H)
+    for tag, scene, q, t in (
+        ("scene2", ref.SR.make_test_scene2(), [[1.0, 0, 0, 0]], [[0.0, 0, 1.0]]),
+        ("scene1", ref.SR.make_test_scene(), [[1.0, 0, 0, 0]], [[0.0, 0, -1.5]]),
+        ("syn8", make_synthetic_scene(8, 0, True, classes=ref), [[0.96, 0.1, -0.2, 0.15]], [[0.3, -0.2, -4.0]]),
+    ):
+        q = torch.tensor(q)
+        q = q / q.norm(dim=-1, keepdim=True)
+        t = torch.tensor(t)
+        loop = ref.RenderLoop(scene, normals_eps=5e-2, **intr)
+        with torch.no_grad():
+            px, frames, pos0, dirs = loop.camera(q, t)
+            pos = loop.marcher(pos0, dirs, 32)
+            sd = scene(pos)
+            normals, lap = loop.normals(pos)
+            out[f"render/{tag}/q"] = np32(q)
+            out[f"render/{tag}/t"] = np32(t)
+            out[f"render/{tag}/pos0"] = np32(pos0)
+            out[f"render/{tag}/dirs"] = np32(dirs)
+            out[f"render/{tag}/pos"] = np32(pos)
+            out[f"render/{tag}/sdf"] = np32(sd)
+            out[f"render/{tag}/normals"] = np32(normals)
+            out[f"render/{tag}/lap"] = np32(lap)
+            for mode in range(8):
+                img = loop(q, t, mode, 3 if mode >= 6 else 1, 32)
+                out[f"render/{tag}/mode{mode}"] = np32(img.contiguous())
+            out[f"render/{tag}/steps7_mode0"] = np32(loop(q, t, 0, 1, 7).contiguous())
+
+
+def gen_grads(ref, out):
+    """Config-4 style loss through the reference's unrolled autograd graph."""
+    W = H = 16
+    intr = cases.config1_camera(W, H)
+    for tag, scene_fn, t0 in (("scene2", lambda: ref.SR.make_test_scene2(), [0.0, 0.1, 1.0]),
+                              ("syn8", lambda: make_synthetic_scene(8, 0, True, classes=ref),
+                               [0.3, -0.2, -4.0])):
+        scene = scene_fn()
+        loop = ref.RenderLoop(scene, normals_eps=5e-2, **intr)
+        q = torch.nn.functional.normalize(torch.tensor([[0.98, 0.05, -0.12, 0.08]]), dim=-1)
+        t = torch.tensor([t0])
+
+        def gbuf(q, t):
+            px, frames, pos0, dirs = loop.camera(q, t)
+            pos = loop.marcher(pos0, dirs, 32)
+            normals, lap = loop.normals(pos)
+            lam = (dirs * normals).sum(-1, keepdim=True).neg().clamp(0, 1)
+            depth = (pos - px).norm(dim=-1, keepdim=True)
+            return lam, depth, lap
+
+        # target: seeded perturbation of the parameters (p + 0.05 randn, seed 1)
+        params = param_list(scene)
+        saved = [p.detach().clone() for _, p in params]
+        g = torch.Generator().manual_seed(1)
+        with torch.no_grad():
+            for _, p in params:
+                p.add_(0.05 * torch.randn(p.shape, generator=g))
+            lam_t, depth_t, _ = gbuf(q, t)
+            for (_, p), s in zip(params, saved):
+                p.copy_(s)
+        q = q.clone().requires_grad_(True)
+        t = t.clone().requires_grad_(True)
+        lam, depth, lap = gbuf(q, t)
+        loss = ((lam - lam_t) ** 2).mean() + ((depth - depth_t) ** 2).mean()
+        grads = torch.autograd.grad(loss, [q, t] + [p for _, p in params], allow_unused=True,
+                                    retain_graph=True)
+        out[f"grads/{tag}/q"] = np32(q)
+        out[f"grads/{tag}/t"] = np32(t)
+        out[f"grads/{tag}/lam_target"] = np32(lam_t)
+        out[f"grads/{tag}/depth_target"] = np32(depth_t)
+        out[f"grads/{tag}/loss"] = np32(loss)
+        out[f"grads/{tag}/dq"] = np32(grads[0])
+        out[f"grads/{tag}/dt"] = np32(grads[1])
+        out[f"grads/{tag}/dparams_flat"] = np32(torch.cat(
+            [(gp if gp is not None else torch.zeros_like(p)).reshape(-1)
+             for (_, p), gp in zip(params, grads[2:])]))
+        # second loss exercising the Laplacian and sdf outputs
+        loss2 = (lap * 1e-3).pow(2).mean()
+        grads2 = torch.autograd.grad(loss2, [q, t] + [p for _, p in params], allow_unused=True)
+        out[f"grads/{tag}/lap_dq"] = np32(grads2[0])
+        out[f"grads/{tag}/lap_dt"] = np32(grads2[1])
+        out[f"grads/{tag}/lap_dparams_flat"] = np32(torch.cat(
+            [(gp if gp is not None else torch.zeros_like(p)).reshape(-1)
+             for (_, p), gp in zip(params, grads2[2:])]))
+
+
+def main():
+    assert ref_import.available(), "needs /root/reference (build container only)"
+    torch.manual_seed(0)
+    torch.set_num_threads(1)          # deterministic reduction order
+    ref = ref_import.load()
+    os.makedirs(OUT, exist_ok=True)
+    for name, fn in (("quaternion", gen_quaternion), ("nodes", gen_nodes), ("camera", gen_camera),
+                     ("render", gen_render), ("grads", gen_grads)):
+        out = {}
+        fn(ref, out)
+        path = os.path.join(OUT, f"{name}.npz")
+        np.savez_compressed(path, **out)
+        print(f"{path}: {len(out)} arrays, {os.path.getsize(path)/1024:.1f} KiB")
+    cmap = ref.shader.cyclic_cmap.contiguous().numpy().astype(np.float32)
+    # the colour LUT is an *input* of the tangent/spin shaders (data/cyclic_cmap.pt, (4096,3) f64,
+    # loaded at shader.py:177); kept as a float32 data asset so the GPU box has it
+    np.save(os.path.join(ROOT, "ray_marching_b200", "data", "cyclic_cmap_f32.npy"), cmap)
+    print("cmap", cmap.shape, cmap.dtype)
+
+
+if __name__ == "__main__":
+    main()

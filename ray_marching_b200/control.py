@@ -1,0 +1,95 @@
+"""Drop-in ``RenderLoop`` and ``make_reflection_directions`` (reference ``control.py:179-258``).
+
+``EventAggregator`` (keyboard / mouse input through pynput, ``control.py:18-176``) is host
+input glue that needs an X session and is out of scope; its ``get_state()`` tuple is what
+``RenderLoop.forward`` consumes, unchanged.
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence
+
+import torch
+import torch.nn as nn
+from torch import Tensor
+
+from . import _lib, ops
+from .rendering.ray_marching import PinholeCamera, SDFMarcher, SDFNormals, _grad_mode
+from .rendering.shader import Shader
+from .tape import tape_of
+
+
+def make_reflection_directions(surface_normals: Tensor, ray_dirs: Tensor) -> Tensor:
+    """``v - 2 (v.n) n`` (reference ``control.py:179-194``)."""
+    return ray_dirs - 2 * (ray_dirs * surface_normals).sum(dim=-1, keepdim=True) * surface_normals
+
+
+class RenderLoop(nn.Module):
+    """camera -> march -> f(p) -> stencil -> shader, ``(N,H,W,3)`` (reference ``control.py:197-258``).
+
+    Without autograd one fused kernel produces the requested image.  With autograd recording
+    (scene parameters or camera pose require grad) the same pipeline is composed from the
+    differentiable custom ops.  Extra, non-reference arguments are keyword-only."""
+
+    def __init__(self, scene, num_cameras: int = 1, px_width: int = 800, px_height: int = 800,
+                 focal_length: float = 17e-3, sensor_width: float = 17e-3,
+                 sensor_height: float = 17e-3, normals_eps: float = 5e-2):
+        super().__init__()
+        self.scene = scene
+        self.px_width = px_width
+        self.px_height = px_height
+        self.camera = PinholeCamera(num_cameras=num_cameras, px_width=px_width,
+                                    px_height=px_height, focal_length=focal_length,
+                                    sensor_width=sensor_width, sensor_height=sensor_height)
+        self.marcher = SDFMarcher(sdf_scene=self.scene)
+        self.normals = SDFNormals(sdf_scene=self.scene, normals_eps=normals_eps)
+        self.shader = Shader()
+        self.early_exit = False          # bit-identical fixed-point exit of the march loop
+        self.fast_math = True            # approximate sqrt/exp inside march steps only
+
+    # ---- fused, no autograd -------------------------------------------------------------
+    def render_planes(self, orientations: Tensor, translations: Tensor, *, modes: Sequence[int] = (),
+                      gbuffer: bool = False, display_mode: int = -1, degree: int = 1,
+                      marching_steps: int = 32, bounces: int = 0, hit_tau: float = 1e-3,
+                      lift_delta: Optional[float] = None, ray_begin: int = 0,
+                      n_rays: Optional[int] = None, finalize: bool = True,
+                      out: Optional[ops.RenderResult] = None) -> ops.RenderResult:
+        """One launch for several shader modes and/or the G-buffer (planes are flat, ray-major)."""
+        _lib.require_cuda(orientations, translations)
+        mask = 0
+        for m in modes:
+            mask |= 1 << (m % 8)
+        poses = ops.pose_records(orientations, translations)
+        return ops.render(tape_of(self.scene), self.camera.struct(), poses, steps=marching_steps,
+                          normals_eps=self.normals.normals_eps, mode_mask=mask, gbuffer=gbuffer,
+                          display_mode=display_mode, degree=degree, bounces=bounces,
+                          hit_tau=hit_tau, lift_delta=lift_delta, early_exit=self.early_exit,
+                          fast_math=self.fast_math, cmap=self.shader.cyclic_cmap,
+                          ray_begin=ray_begin, n_rays=n_rays, finalize=finalize, out=out)
+
+    def display_frame(self, orientations: Tensor, translations: Tensor, mode: int = 0,
+                      degree: int = 1, marching_steps: int = 32) -> Tensor:
+        """Headless replacement of ``Window.draw`` input (``main.py:78-84``): contiguous
+        ``(H,W,4)`` float32 RGBA, alpha 1 (single camera)."""
+        if self.camera.num_cameras != 1:
+            raise ValueError("display_frame renders one camera; average a batch on the caller side")
+        res = self.render_planes(orientations, translations, display_mode=mode % 8, degree=degree,
+                                 marching_steps=marching_steps)
+        return res.rgba.reshape(self.px_height, self.px_width, 4)
+
+    # ---- reference signature --------------------------------------------------------------
+    def forward(self, orientations: Tensor, translations: Tensor, mode: int = 0, degree: int = 1,
+                marching_steps: int = 32):
+        N, H, W = self.camera.num_cameras, self.px_height, self.px_width
+        tape = tape_of(self.scene)
+        if not (_grad_mode(orientations, translations) or _grad_mode(*tape.params)):
+            m = mode % 8
+            res = self.render_planes(orientations, translations, modes=(m,), degree=degree,
+                                     marching_steps=marching_steps)
+            return res.images[m].reshape(N, H, W, -1).expand(-1, H, W, 3)
+        (pixel_pos, pixel_frames, ray_pos, ray_dirs) = self.camera(orientations, translations)
+        marched = self.marcher(ray_pos, ray_dirs, marching_steps)
+        dists = self.scene(marched)
+        (n, lap) = self.normals(marched)
+        image = self.shader(pixel_pos, orientations, pixel_frames, ray_dirs, marched, n, lap, dists,
+                            mode=mode, degree=degree)
+        return image.expand(-1, H, W, 3)

@@ -1,0 +1,182 @@
+// extern "C" entry points of the forward path.  Included by rm_forward.cu.
+#pragma once
+
+namespace rm {
+
+inline unsigned grid_for(int64_t n) { return (unsigned)((n + (int64_t)BLOCK * K - 1) / ((int64_t)BLOCK * K)); }
+
+inline int make_cam(const RmCamera* c, CamParams* out) {
+    if (c == nullptr || c->n_views <= 0 || c->width <= 0 || c->height <= 0)
+        return fail(RM_ERR_INVALID, "camera is null or has a non-positive size");
+    out->n_views = c->n_views; out->width = c->width; out->height = c->height;
+    out->focal = c->focal_length;
+    out->half_w = c->sensor_width / 2;
+    out->neg_half_h = -c->sensor_height / 2;
+    out->inv_w = 1.0f / (float)c->width;
+    out->inv_h = 1.0f / (float)c->height;
+    return RM_OK;
+}
+
+// SDFNormals.__init__ (ray_marching.py:94-113), float64 on the host, rounded once to float32.
+inline void make_stencil(float eps, Stencil* st) {
+    const double s = sqrt(0.5);
+    const double raw[4][3] = {{1, 0, -s}, {-1, 0, -s}, {0, 1, s}, {0, -1, s}};
+    double off[4][3];
+    for (int j = 0; j < 4; ++j) {
+        const double len = sqrt(raw[j][0] * raw[j][0] + raw[j][1] * raw[j][1] + raw[j][2] * raw[j][2]);
+        for (int c = 0; c < 3; ++c) {
+            off[j][c] = raw[j][c] / len * (double)eps;
+            st->off[j][c] = (float)off[j][c];
+        }
+    }
+    double A[3][3], inv[3][3];
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) A[r][c] = off[r + 1][c] - off[0][c];
+    const double det = A[0][0] * (A[1][1] * A[2][2] - A[1][2] * A[2][1]) -
+                       A[0][1] * (A[1][0] * A[2][2] - A[1][2] * A[2][0]) +
+                       A[0][2] * (A[1][0] * A[2][1] - A[1][1] * A[2][0]);
+    inv[0][0] = (A[1][1] * A[2][2] - A[1][2] * A[2][1]) / det;
+    inv[0][1] = (A[0][2] * A[2][1] - A[0][1] * A[2][2]) / det;
+    inv[0][2] = (A[0][1] * A[1][2] - A[0][2] * A[1][1]) / det;
+    inv[1][0] = (A[1][2] * A[2][0] - A[1][0] * A[2][2]) / det;
+    inv[1][1] = (A[0][0] * A[2][2] - A[0][2] * A[2][0]) / det;
+    inv[1][2] = (A[0][2] * A[1][0] - A[0][0] * A[1][2]) / det;
+    inv[2][0] = (A[1][0] * A[2][1] - A[1][1] * A[2][0]) / det;
+    inv[2][1] = (A[0][1] * A[2][0] - A[0][0] * A[2][1]) / det;
+    inv[2][2] = (A[0][0] * A[1][1] - A[0][1] * A[1][0]) / det;
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) st->inv[r * 3 + c] = (float)inv[r][c];
+    st->lap_scale = (float)(6.0 / ((double)eps * (double)eps));
+}
+
+}  // namespace rm
+
+using namespace rm;
+
+extern "C" int rm_sdf_eval(const RmTape* tape, const float* points, int64_t n, float* out, void* stream) {
+    if (int s = check_tape(tape)) return s;
+    if (n < 0 || (n > 0 && (points == nullptr || out == nullptr)))
+        return fail(RM_ERR_INVALID, "rm_sdf_eval: null buffer or negative count");
+    if (n == 0) return RM_OK;
+    const size_t sm = tape_smem_bytes(tape);
+    if (int s = prepare_smem(sdf_eval_kernel, sm)) return s;
+    sdf_eval_kernel<<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
+        tape->code, tape->par, tape->n_instr, tape->n_par, points, n, out);
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+}
+
+extern "C" int rm_camera_rays(const RmCamera* cam, const float* poses, int64_t ray_begin, int64_t n,
+                              float* origin, float* dirs, void* stream) {
+    CamParams c;
+    if (int s = make_cam(cam, &c)) return s;
+    const int64_t total = (int64_t)c.n_views * c.width * c.height;
+    if (poses == nullptr || ray_begin < 0 || n < 0 || ray_begin + n > total)
+        return fail(RM_ERR_INVALID, "rm_camera_rays: ray range outside the camera batch");
+    if (n == 0) return RM_OK;
+    camera_kernel<<<grid_for(n), BLOCK, 0, (cudaStream_t)stream>>>(c, poses, ray_begin, n, origin, dirs);
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+}
+
+extern "C" int rm_march(const RmTape* tape, const float* origin, const float* dirs, int64_t n,
+                        int32_t steps, int32_t fast_math, float* pos_out, void* stream) {
+    if (int s = check_tape(tape)) return s;
+    if (n < 0 || steps < 0 || (n > 0 && (!origin || !dirs || !pos_out)))
+        return fail(RM_ERR_INVALID, "rm_march: null buffer or negative count");
+    if (n == 0) return RM_OK;
+    const size_t sm = tape_smem_bytes(tape);
+    if (fast_math) {
+        if (int s = prepare_smem(march_kernel<true>, sm)) return s;
+        march_kernel<true><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
+            tape->code, tape->par, tape->n_instr, tape->n_par, origin, dirs, n, steps, pos_out);
+    } else {
+        if (int s = prepare_smem(march_kernel<false>, sm)) return s;
+        march_kernel<false><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
+            tape->code, tape->par, tape->n_instr, tape->n_par, origin, dirs, n, steps, pos_out);
+    }
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+}
+
+extern "C" int rm_normals(const RmTape* tape, const float* points, int64_t n, float eps,
+                          float* normals, float* lap, void* stream) {
+    if (int s = check_tape(tape)) return s;
+    if (n < 0 || !(eps > 0.f) || (n > 0 && points == nullptr))
+        return fail(RM_ERR_INVALID, "rm_normals: null buffer, negative count or eps <= 0");
+    if (n == 0) return RM_OK;
+    Stencil st;
+    make_stencil(eps, &st);
+    const size_t sm = tape_smem_bytes(tape);
+    if (int s = prepare_smem(normals_kernel, sm)) return s;
+    normals_kernel<<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
+        tape->code, tape->par, tape->n_instr, tape->n_par, st, points, n, normals, lap);
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+}
+
+extern "C" int rm_reduce_init(float* reduce, void* stream) {
+    if (reduce == nullptr) return fail(RM_ERR_INVALID, "rm_reduce_init: null scratch");
+    reduce_init_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(reduce);
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+}
+
+extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* poses,
+                         const RmRenderArgs* a, const RmRenderOut* out, void* stream) {
+    if (int s = check_tape(tape)) return s;
+    RenderParams P;
+    if (int s = make_cam(cam, &P.cam)) return s;
+    if (a == nullptr || out == nullptr || poses == nullptr)
+        return fail(RM_ERR_INVALID, "rm_render: null argument block");
+    const int64_t total = (int64_t)P.cam.n_views * P.cam.width * P.cam.height;
+    if (a->ray_begin < 0 || a->n_rays < 0 || a->ray_begin + a->n_rays > total)
+        return fail(RM_ERR_INVALID, "rm_render: ray range outside the camera batch");
+    if (a->steps < 0 || a->bounces < 0 || !(a->normals_eps > 0.f))
+        return fail(RM_ERR_INVALID, "rm_render: negative steps/bounces or eps <= 0");
+    if (a->display_mode > 7) return fail(RM_ERR_INVALID, "rm_render: display_mode must be -1..7");
+    const unsigned mask = a->mode_mask | (a->display_mode >= 0 ? (1u << a->display_mode) : 0u);
+    for (int m = 0; m < 8; ++m)
+        if ((a->mode_mask >> m & 1u) && out->image[m] == nullptr)
+            return fail(RM_ERR_INVALID, "rm_render: mode %d requested but image[%d] is null", m, m);
+    if ((mask & (RM_MODE_TANGENT | RM_MODE_SPIN)) && a->cmap == nullptr)
+        return fail(RM_ERR_INVALID, "rm_render: modes 6/7 need the colour LUT");
+    if ((mask & (RM_MODE_DISTANCE | RM_MODE_PROXIMITY | RM_MODE_LAPLACIAN)) && out->reduce == nullptr)
+        return fail(RM_ERR_INVALID, "rm_render: modes 1/2/5 need the reduction scratch");
+    if (a->display_mode >= 0 && out->rgba == nullptr)
+        return fail(RM_ERR_INVALID, "rm_render: display_mode set but rgba is null");
+    if (a->n_rays == 0) return RM_OK;
+    make_stencil(a->normals_eps, &P.st);
+    P.ray_begin = a->ray_begin; P.n_rays = a->n_rays; P.steps = a->steps; P.bounces = a->bounces;
+    P.hit_tau = a->hit_tau; P.lift_delta = a->lift_delta; P.mode_mask = a->mode_mask;
+    P.display_mode = a->display_mode; P.degree = a->degree; P.early_exit = a->early_exit;
+    P.cmap = a->cmap; P.out = *out;
+    const size_t sm = tape_smem_bytes(tape);
+    if (a->fast_math) {
+        if (int s = prepare_smem(render_kernel<true>, sm)) return s;
+        render_kernel<true><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+            tape->code, tape->par, tape->n_instr, tape->n_par, poses, P);
+    } else {
+        if (int s = prepare_smem(render_kernel<false>, sm)) return s;
+        render_kernel<false><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+            tape->code, tape->par, tape->n_instr, tape->n_par, poses, P);
+    }
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+}
+
+extern "C" int rm_shade_finalize(const float* reduce, uint32_t mode_mask, int64_t n,
+                                 float* const* image, float* rgba, int32_t display_mode, void* stream) {
+    if (reduce == nullptr || n < 0) return fail(RM_ERR_INVALID, "rm_shade_finalize: null scratch");
+    FinalizeParams F;
+    for (int m = 0; m < 8; ++m) F.image[m] = image ? image[m] : nullptr;
+    F.rgba = rgba; F.mode_mask = mode_mask; F.display_mode = display_mode; F.n = n;
+    const bool any = (mode_mask & (RM_MODE_DISTANCE | RM_MODE_PROXIMITY | RM_MODE_LAPLACIAN)) ||
+                     (rgba && (display_mode == 1 || display_mode == 2 || display_mode == 5));
+    if (!any || n == 0) return RM_OK;
+    int64_t blocks = ((n >> 2) + 1 + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    shade_finalize_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(reduce, F);
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+}

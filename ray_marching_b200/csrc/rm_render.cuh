@@ -1,0 +1,281 @@
+// Fused RenderLoop.forward (control.py:231-258): camera -> march (+ reflected segments) ->
+// f(p) -> stencil -> shaders, one kernel, nothing but the requested planes touches HBM.
+// Included by rm_forward.cu.
+#pragma once
+
+namespace rm {
+
+struct RenderParams {
+    CamParams cam;
+    Stencil st;
+    int64_t ray_begin, n_rays;
+    int steps, bounces;
+    float hit_tau, lift_delta;
+    unsigned mode_mask;
+    int display_mode, degree, early_exit;
+    const float* cmap;
+    RmRenderOut out;
+};
+
+// ---- float atomic min / max on plain float storage (initialised to +inf / -inf) -------------
+__device__ __forceinline__ void atomic_min_f(float* addr, float v) {
+    v += 0.f;                                          // -0 -> +0
+    if (v >= 0.f) atomicMin(reinterpret_cast<int*>(addr), __float_as_int(v));
+    else atomicMax(reinterpret_cast<unsigned*>(addr), __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_max_f(float* addr, float v) {
+    v += 0.f;
+    if (v >= 0.f) atomicMax(reinterpret_cast<int*>(addr), __float_as_int(v));
+    else atomicMin(reinterpret_cast<unsigned*>(addr), __float_as_uint(v));
+}
+
+// Block-level min/max/NaN-flag reduction of one quantity, one global atomic per block.
+// torch's .min()/.max() return NaN if any element is NaN (shader.py:35-36): NaNs are kept out of
+// the ordered atomics and reported through a flag instead.
+struct MinMax {
+    float mn, mx, nan;
+    __device__ __forceinline__ void init() { mn = CUDART_INF_F; mx = -CUDART_INF_F; nan = 0.f; }
+    __device__ __forceinline__ void add(float v, bool valid) {
+        if (!valid) return;
+        if (v != v) nan = 1.f;
+        else { mn = fminf(mn, v); mx = fmaxf(mx, v); }
+    }
+};
+
+__device__ __forceinline__ void block_minmax(MinMax m, float* gmin, float* gmax, float* gnan,
+                                             float (*sh)[3]) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        m.mn = fminf(m.mn, __shfl_xor_sync(0xffffffffu, m.mn, o));
+        m.mx = fmaxf(m.mx, __shfl_xor_sync(0xffffffffu, m.mx, o));
+        m.nan = fmaxf(m.nan, __shfl_xor_sync(0xffffffffu, m.nan, o));
+    }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __syncthreads();
+    if (lane == 0) { sh[warp][0] = m.mn; sh[warp][1] = m.mx; sh[warp][2] = m.nan; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < BLOCK / 32; ++w) {
+            m.mn = fminf(m.mn, sh[w][0]); m.mx = fmaxf(m.mx, sh[w][1]); m.nan = fmaxf(m.nan, sh[w][2]);
+        }
+        if (gmin && m.mn != CUDART_INF_F) atomic_min_f(gmin, m.mn);
+        if (gmax && m.mx != -CUDART_INF_F) atomic_max_f(gmax, m.mx);
+        if (m.nan > 0.f) atomicMax(reinterpret_cast<int*>(gnan), __float_as_int(1.0f));
+    }
+}
+
+template <bool FAST>
+__global__ void __launch_bounds__(BLOCK)
+render_kernel(const int32_t* code, const float* par, int n_instr, int n_par,
+              const float* __restrict__ poses, const RenderParams P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ float red[BLOCK / 32][3];
+    const TapeView T = stage_tape(code, par, n_instr, n_par, smem);
+    const int64_t n = P.n_rays;
+    const int64_t first = ((int64_t)blockIdx.x * BLOCK + threadIdx.x) * K;
+    const bool active = first < n;          // whole thread out of range: still joins reductions
+    const unsigned mask = P.mode_mask | (P.display_mode >= 0 ? (1u << P.display_mode) : 0u);
+    const bool need_stencil =
+        (mask & (RM_MODE_LAMBERTIAN | RM_MODE_NORMAL | RM_MODE_LAPLACIAN | RM_MODE_TANGENT |
+                 RM_MODE_SPIN)) || P.out.normals || P.out.laplacian || P.bounces > 0;
+
+    float ox[K], oy[K], oz[K], vx[K], vy[K], vz[K];
+    float px[K], py[K], pz[K], f[K], nx[K], ny[K], nz[K], lap[K];
+    MinMax mm_dist, mm_prox, mm_lap;
+    mm_dist.init(); mm_prox.init(); mm_lap.init();
+
+    if (active) {
+        make_rays(P.cam, poses, P.ray_begin + first, ox, oy, oz, vx, vy, vz);
+        store3(P.out.origin, first, n, ox, oy, oz);
+#pragma unroll
+        for (int k = 0; k < K; ++k) { px[k] = ox[k]; py[k] = oy[k]; pz[k] = oz[k]; }
+
+        for (int b = 0;; ++b) {
+            march_rays<FAST>(T, P.steps, P.early_exit != 0, px, py, pz, vx, vy, vz);
+            stencil_eval(T, P.st, need_stencil, px, py, pz, f, nx, ny, nz, lap);
+            if (b >= P.bounces) break;
+            // reflected-ray branch (reflect = control.py:179-194)
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                const bool hit = fabsf(f[k]) < P.hit_tau;
+                const float nv = -(nx[k] * vx[k] + ny[k] * vy[k] + nz[k] * vz[k]);
+                const float rx = nv * nx[k] * 2.f + vx[k];
+                const float ry = nv * ny[k] * 2.f + vy[k];
+                const float rz = nv * nz[k] * 2.f + vz[k];
+                vx[k] = hit ? rx : vx[k]; vy[k] = hit ? ry : vy[k]; vz[k] = hit ? rz : vz[k];
+                px[k] = hit ? px[k] + P.lift_delta * nx[k] : px[k];
+                py[k] = hit ? py[k] + P.lift_delta * ny[k] : py[k];
+                pz[k] = hit ? pz[k] + P.lift_delta * nz[k] : pz[k];
+            }
+        }
+        // G-buffer planes
+        store3(P.out.dirs, first, n, vx, vy, vz);
+        store3(P.out.pos, first, n, px, py, pz);
+        store1(P.out.sdf, first, n, f);
+        store3(P.out.normals, first, n, nx, ny, nz);
+        store1(P.out.laplacian, first, n, lap);
+
+        // ---- per-pixel shaders (rendering/shader.py); pixel position = ray origin ----
+        const int64_t per_view = (int64_t)P.cam.width * P.cam.height;
+        float img[K], rgb0[K], rgb1[K], rgb2[K];
+        const int dm = P.display_mode;
+        float dr[K], dg[K], db[K];
+#pragma unroll
+        for (int k = 0; k < K; ++k) dr[k] = dg[k] = db[k] = 0.f;
+
+        if (mask & RM_MODE_LAMBERTIAN) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                const float v3[3] = {vx[k], vy[k], vz[k]}, n3[3] = {nx[k], ny[k], nz[k]};
+                img[k] = shade_lambertian(v3, n3);
+                if (dm == 0) dr[k] = dg[k] = db[k] = img[k];
+            }
+            if (P.mode_mask & RM_MODE_LAMBERTIAN) store1(P.out.image[0], first, n, img);
+        }
+        if (mask & RM_MODE_DISTANCE) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                const float ex = ox[k] - px[k], ey = oy[k] - py[k], ez = oz[k] - pz[k];
+                img[k] = shade_log_clamped(__fsqrt_rn(ex * ex + ey * ey + ez * ez));
+                mm_dist.add(img[k], first + k < n);
+                if (dm == 1) dr[k] = img[k];
+            }
+            if (P.mode_mask & RM_MODE_DISTANCE) store1(P.out.image[1], first, n, img);
+        }
+        if (mask & RM_MODE_PROXIMITY) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                img[k] = shade_log_clamped(f[k]);
+                mm_prox.add(img[k], first + k < n);
+                if (dm == 2) dr[k] = img[k];
+            }
+            if (P.mode_mask & RM_MODE_PROXIMITY) store1(P.out.image[2], first, n, img);
+        }
+        if (mask & (RM_MODE_VIGNETTE | RM_MODE_TANGENT | RM_MODE_SPIN)) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                int64_t r = P.ray_begin + first + k;
+                const int64_t total = per_view * P.cam.n_views;
+                if (r >= total) r = total - 1;
+                const Pose pose = load_pose(poses, (int)(r / per_view));
+                const float v3[3] = {vx[k], vy[k], vz[k]}, n3[3] = {nx[k], ny[k], nz[k]};
+                if (mask & RM_MODE_VIGNETTE) {
+                    img[k] = shade_vignette(v3, pose.fwd);
+                    if (dm == 3) dr[k] = dg[k] = db[k] = img[k];
+                }
+                if (mask & RM_MODE_TANGENT) {
+                    float c3[3];
+                    shade_tangent(pose, v3, n3, P.cmap, P.degree, c3);
+                    rgb0[k] = c3[0]; rgb1[k] = c3[1]; rgb2[k] = c3[2];
+                    if (dm == 6) { dr[k] = c3[0]; dg[k] = c3[1]; db[k] = c3[2]; }
+                }
+            }
+            if (P.mode_mask & RM_MODE_VIGNETTE) store1(P.out.image[3], first, n, img);
+            if (P.mode_mask & RM_MODE_TANGENT) store3(P.out.image[6], first, n, rgb0, rgb1, rgb2);
+            if (mask & RM_MODE_SPIN) {
+#pragma unroll
+                for (int k = 0; k < K; ++k) {
+                    int64_t r = P.ray_begin + first + k;
+                    const int64_t total = per_view * P.cam.n_views;
+                    if (r >= total) r = total - 1;
+                    const Pose pose = load_pose(poses, (int)(r / per_view));
+                    const float n3[3] = {nx[k], ny[k], nz[k]};
+                    float c3[3];
+                    shade_spin(pose, n3, P.cmap, P.degree, c3);
+                    rgb0[k] = c3[0]; rgb1[k] = c3[1]; rgb2[k] = c3[2];
+                    if (dm == 7) { dr[k] = c3[0]; dg[k] = c3[1]; db[k] = c3[2]; }
+                }
+                if (P.mode_mask & RM_MODE_SPIN) store3(P.out.image[7], first, n, rgb0, rgb1, rgb2);
+            }
+        }
+        if (mask & RM_MODE_NORMAL) {                         // shader.py:73-74
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                rgb0[k] = clamp_nan(fabsf(nx[k]), 0.f, 1.f);
+                rgb1[k] = clamp_nan(fabsf(ny[k]), 0.f, 1.f);
+                rgb2[k] = clamp_nan(fabsf(nz[k]), 0.f, 1.f);
+                if (dm == 4) { dr[k] = rgb0[k]; dg[k] = rgb1[k]; db[k] = rgb2[k]; }
+            }
+            if (P.mode_mask & RM_MODE_NORMAL) store3(P.out.image[4], first, n, rgb0, rgb1, rgb2);
+        }
+        if (mask & RM_MODE_LAPLACIAN) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                mm_lap.add(fabsf(lap[k]), first + k < n);
+                if (dm == 5) dr[k] = lap[k];
+            }
+            if (P.mode_mask & RM_MODE_LAPLACIAN) store1(P.out.image[5], first, n, lap);
+        }
+        if (P.out.rgba != nullptr && dm >= 0) {
+            // modes 1,2,5 park their un-normalised value in .x; rm_shade_finalize completes them
+#pragma unroll
+            for (int k = 0; k < K; ++k)
+                if (first + k < n)
+                    reinterpret_cast<float4*>(P.out.rgba)[first + k] =
+                        make_float4(dr[k], dg[k], db[k], 1.0f);
+        }
+    }
+    if (P.out.reduce != nullptr) {
+        float* r = P.out.reduce;
+        if (mask & RM_MODE_DISTANCE) block_minmax(mm_dist, r + 0, r + 1, r + 5, red);
+        if (mask & RM_MODE_PROXIMITY) block_minmax(mm_prox, r + 2, r + 3, r + 6, red);
+        if (mask & RM_MODE_LAPLACIAN) block_minmax(mm_lap, nullptr, r + 4, r + 7, red);
+    }
+}
+
+__global__ void reduce_init_kernel(float* r) {
+    if (threadIdx.x == 0) {
+        r[0] = CUDART_INF_F; r[1] = -CUDART_INF_F; r[2] = CUDART_INF_F; r[3] = -CUDART_INF_F;
+        r[4] = -CUDART_INF_F; r[5] = 0.f; r[6] = 0.f; r[7] = 0.f;
+    }
+}
+
+struct FinalizeParams {
+    float* image[8];
+    float* rgba;
+    unsigned mode_mask;
+    int display_mode;
+    int64_t n;
+};
+
+// Second phase of the normalising shaders: HBM-bound elementwise pass, 128-bit accesses.
+__global__ void __launch_bounds__(256)
+shade_finalize_kernel(const float* __restrict__ reduce, const FinalizeParams F) {
+    const float nan = CUDART_NAN_F;
+    const float dmin = reduce[5] > 0.f ? nan : reduce[0], dmax = reduce[5] > 0.f ? nan : reduce[1];
+    const float pmin = reduce[6] > 0.f ? nan : reduce[2], pmax = reduce[6] > 0.f ? nan : reduce[3];
+    const float lmax = reduce[7] > 0.f ? nan : reduce[4];
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t n4 = F.n >> 2;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4 + 1; i += stride) {
+        const int cnt = i < n4 ? 4 : (int)(F.n & 3);
+        if (cnt == 0) break;
+#pragma unroll
+        for (int m = 1; m <= 5; ++m) {
+            if (m == 3 || m == 4) continue;
+            if (!(F.mode_mask & (1u << m)) || F.image[m] == nullptr) continue;
+            float* p = F.image[m] + i * 4;
+            float v[4];
+            if (cnt == 4) { const float4 t = *reinterpret_cast<float4*>(p); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w; }
+            else for (int k = 0; k < cnt; ++k) v[k] = p[k];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                v[k] = m == 1 ? finish_lognorm(v[k], dmin, dmax)
+                     : m == 2 ? finish_lognorm(v[k], pmin, pmax) : finish_laplacian(v[k], lmax);
+            if (cnt == 4) *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+            else for (int k = 0; k < cnt; ++k) p[k] = v[k];
+        }
+        const int dm = F.display_mode;
+        if (F.rgba != nullptr && (dm == 1 || dm == 2 || dm == 5)) {
+            for (int k = 0; k < cnt; ++k) {
+                float4* q = reinterpret_cast<float4*>(F.rgba) + i * 4 + k;
+                const float raw = q->x;
+                const float s = dm == 1 ? finish_lognorm(raw, dmin, dmax)
+                              : dm == 2 ? finish_lognorm(raw, pmin, pmax) : finish_laplacian(raw, lmax);
+                *q = make_float4(s, s, s, 1.0f);
+            }
+        }
+    }
+}
+
+}  // namespace rm

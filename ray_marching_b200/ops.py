@@ -1,0 +1,219 @@
+"""``torch.library`` custom ops over the C ABI (``include/rm_b200.h``).
+
+Forward ops take the lowered tape as two tensors (``code`` int32, ``par`` float32) so that
+autograd sees ``par`` as an ordinary differentiable input; ``tape.lower_theta`` connects it to
+the scene's ``nn.Parameter`` objects.  Backward ops are registered with ``register_autograd``
+(see the bottom of this file).  Nothing here computes on the CPU: non-CUDA tensors raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _lib
+from ._lib import RmCamera, RmRenderArgs, RmRenderOut, RmTape, check, lib, ptr, stream_ptr
+
+MODES = ["lambertian", "distance", "proximity", "vignette", "normal", "laplacian",
+         "tangent", "spin"]
+MODE_CHANNELS = [1, 1, 1, 1, 3, 1, 3, 3]
+NORMALISED_MODES = (1 << 1) | (1 << 2) | (1 << 5)
+
+
+def _tape_struct(code: Tensor, par: Tensor, n_nodes: int, max_depth: int) -> RmTape:
+    return RmTape(ptr(code), ptr(par), code.shape[0], par.numel(), max_depth, n_nodes)
+
+
+def _flat3(t: Tensor) -> Tensor:
+    return t.reshape(-1, 3).contiguous()
+
+
+# ------------------------------------------------------------------------------ sdf_eval
+@torch.library.custom_op("rm_b200::sdf_eval", mutates_args=())
+def _sdf_eval(code: Tensor, par: Tensor, points: Tensor, n_nodes: int, max_depth: int) -> Tensor:
+    dev = _lib.require_cuda(par, points)
+    pts = _flat3(points)
+    out = torch.empty(pts.shape[0], device=dev, dtype=torch.float32)
+    tape = _tape_struct(code, par, n_nodes, max_depth)
+    check(lib().rm_sdf_eval(C.byref(tape), ptr(pts), pts.shape[0], ptr(out), stream_ptr(dev)),
+          "rm_sdf_eval")
+    return out.reshape(*points.shape[:-1], 1)
+
+
+@_sdf_eval.register_fake
+def _(code, par, points, n_nodes, max_depth):
+    return points.new_empty(*points.shape[:-1], 1)
+
+
+def sdf_eval(tape, points: Tensor) -> Tensor:
+    """``scene(points (...,3)) -> (...,1)`` through the tape interpreter."""
+    if points.shape[-1] != 3:
+        raise ValueError(f"query positions must have a trailing dimension of 3, got {tuple(points.shape)}")
+    _lib.require_cuda(points)
+    return _sdf_eval(tape.code_tensor(points.device), tape.lowered_params(points.device), points,
+                     tape.n_nodes, tape.max_depth)
+
+
+# ------------------------------------------------------------------------------ march
+@torch.library.custom_op("rm_b200::march", mutates_args=())
+def _march(code: Tensor, par: Tensor, origin: Tensor, dirs: Tensor, steps: int, fast: bool,
+           n_nodes: int, max_depth: int) -> Tensor:
+    dev = _lib.require_cuda(par, origin, dirs)
+    o, v = _flat3(origin), _flat3(dirs)
+    out = torch.empty_like(o)
+    tape = _tape_struct(code, par, n_nodes, max_depth)
+    check(lib().rm_march(C.byref(tape), ptr(o), ptr(v), o.shape[0], steps, int(fast), ptr(out),
+                         stream_ptr(dev)), "rm_march")
+    return out.reshape(origin.shape)
+
+
+@_march.register_fake
+def _(code, par, origin, dirs, steps, fast, n_nodes, max_depth):
+    return torch.empty_like(origin)
+
+
+def march(tape, origin: Tensor, dirs: Tensor, steps: int = 32, fast: bool = False) -> Tensor:
+    """``SDFMarcher.forward``: ``p <- f(p) v + p`` repeated ``steps`` times."""
+    origin, dirs = torch.broadcast_tensors(origin, dirs)
+    _lib.require_cuda(origin, dirs)
+    return _march(tape.code_tensor(origin.device), tape.lowered_params(origin.device), origin, dirs,
+                  int(steps), bool(fast), tape.n_nodes, tape.max_depth)
+
+
+# ------------------------------------------------------------------------------ normals
+@torch.library.custom_op("rm_b200::normals", mutates_args=())
+def _normals(code: Tensor, par: Tensor, points: Tensor, eps: float, n_nodes: int,
+             max_depth: int) -> Tuple[Tensor, Tensor]:
+    dev = _lib.require_cuda(par, points)
+    pts = _flat3(points)
+    n = torch.empty_like(pts)
+    lap = torch.empty(pts.shape[0], device=dev, dtype=torch.float32)
+    tape = _tape_struct(code, par, n_nodes, max_depth)
+    check(lib().rm_normals(C.byref(tape), ptr(pts), pts.shape[0], float(eps), ptr(n), ptr(lap),
+                           stream_ptr(dev)), "rm_normals")
+    return n.reshape(points.shape), lap.reshape(*points.shape[:-1], 1)
+
+
+@_normals.register_fake
+def _(code, par, points, eps, n_nodes, max_depth):
+    return torch.empty_like(points), points.new_empty(*points.shape[:-1], 1)
+
+
+def normals(tape, points: Tensor, eps: float) -> Tuple[Tensor, Tensor]:
+    """Fused ``SDFNormals.forward`` (no autograd; the differentiable route composes sdf_eval)."""
+    _lib.require_cuda(points)
+    return _normals(tape.code_tensor(points.device), tape.lowered_params(points.device), points, float(eps),
+                    tape.n_nodes, tape.max_depth)
+
+
+# ------------------------------------------------------------------------------ camera
+def camera_struct(n_views, width, height, focal, sensor_w, sensor_h) -> RmCamera:
+    return RmCamera(int(n_views), int(width), int(height), float(focal), float(sensor_w),
+                    float(sensor_h))
+
+
+def camera_rays(cam: RmCamera, poses: Tensor, ray_begin: int = 0,
+                n_rays: Optional[int] = None) -> Tuple[Tensor, Tensor]:
+    """World-space ray origins/directions ``(n,3)`` for a contiguous range of rays."""
+    dev = _lib.require_cuda(poses)
+    total = cam.n_views * cam.width * cam.height
+    n = total - ray_begin if n_rays is None else n_rays
+    origin = torch.empty(n, 3, device=dev, dtype=torch.float32)
+    dirs = torch.empty(n, 3, device=dev, dtype=torch.float32)
+    poses = poses.contiguous()
+    check(lib().rm_camera_rays(C.byref(cam), ptr(poses), ray_begin, n, ptr(origin), ptr(dirs),
+                               stream_ptr(dev)), "rm_camera_rays")
+    return origin, dirs
+
+
+# ------------------------------------------------------------------------------ fused render
+class RenderResult:
+    """Planes produced by one fused render call (all on the GPU, local-ray indexed)."""
+
+    def __init__(self):
+        self.origin = self.dirs = self.pos = self.sdf = self.normals = self.laplacian = None
+        self.images: List[Optional[Tensor]] = [None] * 8
+        self.rgba = None
+        self.reduce = None
+
+
+def render(tape, cam: RmCamera, poses: Tensor, *, steps: int = 32, normals_eps: float = 5e-2,
+           mode_mask: int = 0, gbuffer: bool = False, display_mode: int = -1, degree: int = 1,
+           bounces: int = 0, hit_tau: float = 1e-3, lift_delta: Optional[float] = None,
+           early_exit: bool = False, fast_math: bool = True, cmap: Optional[Tensor] = None,
+           ray_begin: int = 0, n_rays: Optional[int] = None, finalize: bool = True,
+           reduce: Optional[Tensor] = None, out: Optional[RenderResult] = None) -> RenderResult:
+    """One launch of the fused camera->march->stencil->shade kernel (no autograd).
+
+    ``finalize=False`` leaves modes 1/2/5 un-normalised (so a sharded job can all-reduce
+    ``result.reduce`` first and then call :func:`shade_finalize`)."""
+    dev = _lib.require_cuda(poses)
+    with torch.no_grad():
+        par = tape.lowered_params(dev)
+        total = cam.n_views * cam.width * cam.height
+        n = total - ray_begin if n_rays is None else n_rays
+        res = out or RenderResult()
+        new = lambda *shape: torch.empty(*shape, device=dev, dtype=torch.float32)
+        if gbuffer:
+            res.origin = res.origin if res.origin is not None else new(n, 3)
+            res.dirs = res.dirs if res.dirs is not None else new(n, 3)
+            res.pos = res.pos if res.pos is not None else new(n, 3)
+            res.sdf = res.sdf if res.sdf is not None else new(n)
+            res.normals = res.normals if res.normals is not None else new(n, 3)
+            res.laplacian = res.laplacian if res.laplacian is not None else new(n)
+        for m in range(8):
+            if mode_mask >> m & 1 and res.images[m] is None:
+                res.images[m] = new(n, MODE_CHANNELS[m])
+        if display_mode >= 0 and res.rgba is None:
+            res.rgba = new(n, 4)
+        full_mask = mode_mask | ((1 << display_mode) if display_mode >= 0 else 0)
+        if full_mask & NORMALISED_MODES:
+            if reduce is not None:
+                res.reduce = reduce
+            elif res.reduce is None:
+                res.reduce = new(_lib.REDUCE_FLOATS)
+            if reduce is None:
+                check(lib().rm_reduce_init(ptr(res.reduce), stream_ptr(dev)), "rm_reduce_init")
+        o = RmRenderOut()
+        o.origin, o.dirs, o.pos = ptr(res.origin), ptr(res.dirs), ptr(res.pos)
+        o.sdf, o.normals, o.laplacian = ptr(res.sdf), ptr(res.normals), ptr(res.laplacian)
+        for m in range(8):
+            o.image[m] = ptr(res.images[m]) if mode_mask >> m & 1 else 0
+        o.rgba, o.reduce = ptr(res.rgba), ptr(res.reduce)
+        poses = poses.contiguous()
+        a = RmRenderArgs(ray_begin, n, int(steps), int(bounces), float(normals_eps), float(hit_tau),
+                         float(2 * normals_eps if lift_delta is None else lift_delta),
+                         int(mode_mask), int(display_mode), int(degree), int(early_exit),
+                         int(fast_math), ptr(cmap))
+        t = _tape_struct(tape.code_tensor(dev), par, tape.n_nodes, tape.max_depth)
+        check(lib().rm_render(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(o),
+                              stream_ptr(dev)), "rm_render")
+        res._keep = (par, poses, cmap)       # keep inputs alive until the stream has consumed them
+        if finalize and (full_mask & NORMALISED_MODES):
+            shade_finalize(res, mode_mask, display_mode)
+    return res
+
+
+def shade_finalize(res: RenderResult, mode_mask: int, display_mode: int = -1) -> None:
+    """Second phase of the normalising shaders (modes 1, 2, 5), in place."""
+    dev = res.reduce.device
+    n = next(t for t in (res.images + [res.rgba]) if t is not None).shape[0]
+    imgs = (C.c_void_p * 8)(*[ptr(t) for t in res.images])
+    check(lib().rm_shade_finalize(ptr(res.reduce), int(mode_mask), n, imgs, ptr(res.rgba),
+                                  int(display_mode), stream_ptr(dev)), "rm_shade_finalize")
+
+
+def pose_records(orientations: Tensor, translations: Tensor) -> Tensor:
+    """``(N,4),(N,3) -> (N,20)`` pose records: R(q) row-major, t, forward axis, q, pad.
+
+    ``R`` is the rotation polynomial of ``Q.rotation`` (ray_marching.py:58-63); ``fwd`` is the
+    third column of ``QuaternionToSO3(q)`` (quaternion.py:114-124) used by the vignette shader."""
+    from . import quaternion as Q
+    _lib.require_cuda(orientations, translations)
+    R = Q.rotation_matrix(orientations).reshape(-1, 9)
+    w, x, y, z = orientations.unbind(-1)
+    fwd = torch.stack([2 * (w * y + x * z), 2 * (y * z - w * x), w * w - x * x - y * y + z * z], -1)
+    pad = torch.zeros_like(w)[:, None]
+    return torch.cat([R, translations, fwd, orientations, pad], dim=-1).contiguous()

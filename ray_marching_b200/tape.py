@@ -1,0 +1,318 @@
+"""Scene-build-time lowering of an SDF module tree to a flat instruction tape.
+
+The reference evaluates a scene by recursive ``nn.Module`` calls that materialise one
+``(N,H,W,k)`` tensor per torch op (``scene/transformations.py:33-41,67-71,90-94``).  Here the
+tree is walked once and turned into
+
+* ``code``  int32 ``(n_instr, 4)``: ``(head, param_offset/4, ordinal_in_parent, node_id)``
+* ``par``   float32 ``(n_par,)``: per-instruction parameter records, 16-byte aligned,
+
+which the per-ray CUDA interpreter (``csrc/rm_eval.cuh``) executes from shared memory.
+
+Lowering rules
+--------------
+* **Frames.** Every affine transform chain above a leaf is composed at lowering time into one
+  world->local frame ``q = A p + b`` (``A = R(conj(q_n)) ... R(conj(q_1))``).  ``R`` is the same
+  polynomial in the (un-normalised) quaternion as ``quaternion.rotation``
+  (``quaternion.py:55-72``), so values *and* d/dq agree with the reference for non-unit q.
+  A leaf loads a new frame only when it differs from the one currently held in registers.
+* **Unary value ops** (rounding ``f - rho``, onion ``|f| - r``; ``transformations.py:117-118``,
+  ``:131-132``) are attached as post-ops to the leaf / union-close instruction they act on.
+* **Unions** become ``OPEN`` ... children ... ``CLOSE``; every child instruction carries the fold
+  kind of its parent (hard ``min`` or online ``logsumexp``) and its ordinal among the parent's
+  children (``min`` ties go to the first child, as ``torch.min(dim)`` does).
+* **Parameters are read live on every call**: ``lowered_params()`` gathers the current
+  ``nn.Parameter`` values into ``par`` with a handful of batched, autograd-tracked torch ops
+  (a concatenate, the frame composition, one permutation gather), so the backward kernel only
+  has to return ``d loss / d par`` and autograd scatters it to ``.grad`` of every parameter.
+
+``flops_per_eval`` follows the algorithmic counting rule of SURVEY.md §8(d).
+"""
+from __future__ import annotations
+
+import dataclasses
+from typing import List, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import quaternion as Q
+
+# ---- instruction encoding (mirrored in csrc/rm_tape.h) -------------------------------------
+OP_SPHERE, OP_BOX, OP_PLANE, OP_LINE, OP_DISK, OP_TORUS = 1, 2, 3, 4, 5, 6
+OP_OPEN_MIN, OP_OPEN_SMOOTH, OP_CLOSE_MIN, OP_CLOSE_SMOOTH = 8, 9, 10, 11
+FRAME_KEEP, FRAME_WORLD, FRAME_NEW = 0, 1, 2
+FOLD_NONE, FOLD_MIN, FOLD_SMOOTH = 0, 1, 2
+POST_ROUND, POST_ONION = 1, 2
+MAX_POST = 3
+MAX_DEPTH = 8          # union nesting depth supported by the interpreter's spill stack
+
+_PRIM_OP = {"SDFSphere": OP_SPHERE, "SDFBox": OP_BOX, "SDFPlane": OP_PLANE,
+            "SDFLine": OP_LINE, "SDFDisk": OP_DISK, "SDFTorus": OP_TORUS}
+_PRIM_F4 = {OP_SPHERE: 1, OP_BOX: 1, OP_PLANE: 0, OP_LINE: 3, OP_DISK: 1, OP_TORUS: 1}
+# algorithmic flops per node, SURVEY.md §8(d)
+_PRIM_FLOPS = {OP_SPHERE: 7, OP_BOX: 19, OP_PLANE: 0, OP_LINE: 23, OP_DISK: 10, OP_TORUS: 10}
+AFFINE_FLOPS, ROUND_FLOPS, ONION_FLOPS = 33, 1, 2
+
+
+def encode_head(op, frame=0, fold=0, posts=()):
+    head = op | (frame << 4) | (fold << 6) | (len(posts) << 8)
+    for i, kind in enumerate(posts):
+        head |= kind << (10 + 2 * i)
+    return head
+
+
+class _Src:
+    """Where a lowered float comes from: piece name + index inside that piece."""
+    ZERO = ("zero", 0)
+
+
+@dataclasses.dataclass
+class _Affine:
+    q_slot: int            # start of the quaternion in theta
+    t_slot: int            # start of the translation in theta
+    parent: int            # index of the enclosing affine (-1: world)
+    level: int             # chain depth (0 for a top-level affine)
+
+
+class Tape:
+    """Lowered scene: static code + the recipe that gathers live parameters into ``par``."""
+
+    def __init__(self, root: nn.Module):
+        self.root = root
+        self.params: List[nn.Parameter] = []
+        self._slot_of = {}
+        off = 0
+        for p in root.parameters():
+            if id(p) in self._slot_of:
+                continue
+            self._slot_of[id(p)] = off
+            self.params.append(p)
+            off += p.numel()
+        self.n_theta = off
+
+        self._code: List[List[int]] = []
+        self._src: List[tuple] = []        # per par float: (piece, index)
+        self._affines: List[_Affine] = []
+        self._lines: List[tuple] = []      # (start_slot, end_slot)
+        self._cur_frame: Optional[int] = None   # None: nothing loaded yet; -1: world
+        self.n_nodes = 0
+        self.n_leaves = 0
+        self.max_depth = 0
+        self.flops_per_eval = 0
+        self.leaf_kinds: List[int] = []
+
+        self._emit(root, frame=-1, fold=FOLD_NONE, ordinal=0, posts=[], depth=0)
+
+        self.code = np.asarray(self._code, dtype=np.int32).reshape(-1, 4)
+        self.n_instr = self.code.shape[0]
+        self.n_par = len(self._src)
+        assert self.n_par % 4 == 0
+        if self.max_depth > MAX_DEPTH:
+            raise NotImplementedError(
+                f"union nesting depth {self.max_depth} exceeds the interpreter limit {MAX_DEPTH}")
+        self._finalise_recipe()
+        self._dev_cache = {}
+        self._par_cache = None
+
+    # ------------------------------------------------------------------ tree walk
+    def _slot(self, p: nn.Parameter) -> int:
+        return self._slot_of[id(p)]
+
+    def _f4(self, entries):
+        """Append one 16-byte record; returns its offset in float4 units."""
+        assert len(entries) <= 4
+        off4 = len(self._src) // 4
+        self._src.extend(list(entries) + [_Src.ZERO] * (4 - len(entries)))
+        return off4
+
+    def _theta(self, p, i=0):
+        return ("theta", self._slot(p) + i)
+
+    def _post_record(self, posts):
+        kinds, entries = [], []
+        for kind, p in reversed(posts):          # innermost op is applied first
+            kinds.append(kind)
+            entries.append(self._theta(p))
+        if len(kinds) > MAX_POST:
+            raise NotImplementedError(
+                f"more than {MAX_POST} chained rounding/onion ops on one node are not supported")
+        return kinds, entries
+
+    def _emit(self, node, frame, fold, ordinal, posts, depth):
+        kind = type(node).__name__
+        if kind == "SDFAffineTransformation":
+            lvl = 0 if frame < 0 else self._affines[frame].level + 1
+            self._affines.append(_Affine(self._slot(node.orientation),
+                                         self._slot(node.translation), frame, lvl))
+            self.flops_per_eval += AFFINE_FLOPS
+            return self._emit(node.sdf, len(self._affines) - 1, fold, ordinal, posts, depth)
+        if kind == "SDFRounding":
+            self.flops_per_eval += ROUND_FLOPS
+            return self._emit(node.sdf, frame, fold, ordinal,
+                              posts + [(POST_ROUND, node.rounding)], depth)
+        if kind == "SDFOnion":
+            self.flops_per_eval += ONION_FLOPS
+            return self._emit(node.sdf, frame, fold, ordinal,
+                              posts + [(POST_ONION, node.radius)], depth)
+        if kind in ("SDFUnion", "SDFSmoothUnion"):
+            smooth = kind == "SDFSmoothUnion"
+            n = len(node.sdfs)
+            if n == 0:
+                raise ValueError(f"{kind} without children")
+            node_id = self.n_nodes
+            self.n_nodes += 1
+            self.max_depth = max(self.max_depth, depth + 1)
+            self.flops_per_eval += (5 * n + 1) if smooth else (n - 1)
+            if smooth:
+                off4 = self._f4([("neg_theta", self._slot(node.blend_k))])
+                self._code.append([encode_head(OP_OPEN_SMOOTH), off4, 0, node_id])
+            else:
+                self._code.append([encode_head(OP_OPEN_MIN), 0, 0, node_id])
+            child_fold = FOLD_SMOOTH if smooth else FOLD_MIN
+            for i, child in enumerate(node.sdfs):
+                self._emit(child, frame, child_fold, i, [], depth + 1)
+            kinds, entries = self._post_record(posts)
+            off4 = self._f4(entries) if kinds else 0
+            op = OP_CLOSE_SMOOTH if smooth else OP_CLOSE_MIN
+            self._code.append([encode_head(op, 0, fold, kinds), off4, ordinal, node_id])
+            return
+        if kind not in _PRIM_OP:
+            raise NotImplementedError(f"cannot lower scene node of type {kind}")
+        op = _PRIM_OP[kind]
+        self.flops_per_eval += _PRIM_FLOPS[op]
+        self.n_leaves += 1
+        self.leaf_kinds.append(op)
+        if frame == self._cur_frame:
+            fmode = FRAME_KEEP
+        elif frame < 0:
+            fmode = FRAME_WORLD
+        else:
+            fmode = FRAME_NEW
+        self._cur_frame = frame
+        first = len(self._src) // 4
+        if fmode == FRAME_NEW:
+            for r in range(3):
+                self._f4([("A", frame * 9 + r * 3 + c) for c in range(3)] + [("b", frame * 3 + r)])
+        if op == OP_SPHERE:
+            self._f4([self._theta(node.radius)])
+        elif op == OP_BOX:
+            self._f4([self._theta(node.halfsides, i) for i in range(3)])
+        elif op == OP_LINE:
+            li = len(self._lines)
+            self._lines.append((self._slot(node.start), self._slot(node.end)))
+            self._f4([self._theta(node.start, i) for i in range(3)] + [self._theta(node.radius)])
+            self._f4([("AB", li * 3 + i) for i in range(3)])
+            self._f4([("ABn", li * 3 + i) for i in range(3)])
+        elif op == OP_DISK:
+            self._f4([self._theta(node.radius)])
+        elif op == OP_TORUS:
+            self._f4([self._theta(node.radius1), self._theta(node.radius2)])
+        kinds, entries = self._post_record(posts)
+        if kinds:
+            self._f4(entries)
+        self._code.append([encode_head(op, fmode, fold, kinds), first, ordinal, 0])
+
+    # ------------------------------------------------------------------ lowering recipe
+    def _finalise_recipe(self):
+        nA, nL, P = len(self._affines), len(self._lines), self.n_theta
+        base = {"zero": 0, "theta": 1, "neg_theta": 1 + P, "AB": 1 + 2 * P,
+                "ABn": 1 + 2 * P + 3 * nL, "A": 1 + 2 * P + 6 * nL,
+                "b": 1 + 2 * P + 6 * nL + 9 * nA}
+        self._perm = torch.tensor([base[piece] + idx for piece, idx in self._src],
+                                  dtype=torch.int64)
+        ar3, ar4 = np.arange(3), np.arange(4)
+        self._q_idx = torch.tensor(np.array([a.q_slot + ar4 for a in self._affines]).reshape(-1, 4),
+                                   dtype=torch.int64)
+        self._t_idx = torch.tensor(np.array([a.t_slot + ar3 for a in self._affines]).reshape(-1, 3),
+                                   dtype=torch.int64)
+        self._ls_idx = torch.tensor(np.array([s + ar3 for s, _ in self._lines]).reshape(-1, 3),
+                                    dtype=torch.int64)
+        self._le_idx = torch.tensor(np.array([e + ar3 for _, e in self._lines]).reshape(-1, 3),
+                                    dtype=torch.int64)
+        # affine chains are composed level by level (batched); level 0 = directly under world
+        levels = {}
+        for i, a in enumerate(self._affines):
+            levels.setdefault(a.level, []).append(i)
+        self._levels = [
+            (torch.tensor(idx, dtype=torch.int64),
+             torch.tensor([self._affines[i].parent for i in idx], dtype=torch.int64))
+            for lvl, idx in sorted(levels.items()) if lvl > 0
+        ]
+
+    def _on(self, device):
+        key = str(device)
+        if key not in self._dev_cache:
+            mv = lambda t: t.to(device)
+            self._dev_cache[key] = dict(
+                perm=mv(self._perm), q_idx=mv(self._q_idx), t_idx=mv(self._t_idx),
+                ls_idx=mv(self._ls_idx), le_idx=mv(self._le_idx),
+                levels=[(mv(a), mv(b)) for a, b in self._levels],
+                code=torch.from_numpy(self.code.copy()).to(device).contiguous(),
+            )
+        return self._dev_cache[key]
+
+    @property
+    def device(self):
+        return self.params[0].device if self.params else torch.device("cpu")
+
+    def code_tensor(self, device=None) -> torch.Tensor:
+        return self._on(device or self.device)["code"]
+
+    def theta(self, device=None) -> torch.Tensor:
+        """Flat view of the current raw parameters (autograd-connected)."""
+        if not self.params:
+            return torch.zeros(0, device=device or self.device)
+        return torch.cat([p.reshape(-1) for p in self.params])
+
+    def lower_theta(self, theta: torch.Tensor) -> torch.Tensor:
+        """``theta (P,) -> par (n_par,)``; differentiable, device-agnostic (used on CPU in tests)."""
+        d = self._on(theta.device)
+        pieces = [theta.new_zeros(1), theta, -theta]
+        if len(self._lines):
+            s, e = theta[d["ls_idx"]], theta[d["le_idx"]]
+            ab = e - s                                        # primitives.py:52
+            pieces += [ab.reshape(-1), (ab / (ab * ab).sum(-1, keepdim=True)).reshape(-1)]  # :53-54
+        if len(self._affines):
+            q, t = theta[d["q_idx"]], theta[d["t_idx"]]
+            A = Q.rotation_matrix(Q.conjugate(q))             # transformations.py:35-41
+            b = -(A @ t[..., None])[..., 0]
+            for idx, parent in d["levels"]:                   # nested chains: inner o outer
+                Ai, Ap = A[idx], A[parent]
+                b = b.index_put((idx,), (Ai @ b[parent][..., None])[..., 0] + b[idx])
+                A = A.index_put((idx,), Ai @ Ap)
+            pieces += [A.reshape(-1), b.reshape(-1)]
+        return torch.cat(pieces)[d["perm"]]
+
+    def lowered_params(self, device=None) -> torch.Tensor:
+        """Current ``par`` on the parameters' device (``device`` only matters for a scene
+        without parameters).  Cached while no parameter changes and autograd is off (a static
+        scene under a moving camera costs nothing per frame)."""
+        if self.params and device is not None and torch.device(device) != self.device:
+            raise RuntimeError(f"scene parameters live on {self.device} but the query is on "
+                               f"{device}; move the scene with .to(device)")
+        track = torch.is_grad_enabled() and any(p.requires_grad for p in self.params)
+        if not track:
+            key = tuple(p._version for p in self.params) + (str(device or self.device),)
+            if self._par_cache is not None and self._par_cache[0] == key:
+                return self._par_cache[1]
+            with torch.no_grad():
+                par = self.lower_theta(self.theta(device)).contiguous()
+            self._par_cache = (key, par)
+            return par
+        return self.lower_theta(self.theta(device)).contiguous()
+
+    def describe(self) -> str:
+        return (f"Tape(instr={self.n_instr}, par={self.n_par} floats, leaves={self.n_leaves}, "
+                f"unions={self.n_nodes}, depth={self.max_depth}, theta={self.n_theta}, "
+                f"flops/eval={self.flops_per_eval})")
+
+
+def tape_of(module: nn.Module) -> Tape:
+    """Tape of ``module``'s sub-tree, cached on the module (structure is assumed immutable)."""
+    tape = module.__dict__.get("_rm_tape")
+    if tape is None:
+        tape = Tape(module)
+        module.__dict__["_rm_tape"] = tape
+    return tape

@@ -1,0 +1,96 @@
+"""Host logic: scene tree -> tape lowering, checked on CPU against the oracle through a torch
+executor that mirrors the CUDA interpreter (tests/tape_interp.py)."""
+import numpy as np
+import pytest
+import torch
+
+import tape_interp
+from oracle import cases, sdf_oracle as O
+from ray_marching_b200 import scene as S
+from ray_marching_b200 import tape as T
+from ray_marching_b200.scene.scene_registry import _default_classes
+
+C = _default_classes()
+ALL = dict(cases.node_cases(C))
+ALL.update(test_scene=S.make_test_scene(), test_scene2=S.make_test_scene2(),
+           syn8=S.make_synthetic_scene(8, 0, True), syn64=S.make_synthetic_scene(64, 0, False))
+
+
+@pytest.mark.parametrize("name", list(ALL.keys()))
+def test_lowered_tape_matches_oracle(name):
+    """Values in float32 (the precision the kernels run in); gradients in float64, where the
+    comparison is exact to rounding.  (In float32 the reference's own autograd loses e.g. d/dk of
+    a smooth union to cancellation -- 0.0 instead of 0.0272 on `smooth_nested` -- so float32
+    gradients are not a usable yardstick for the lowering logic.)"""
+    import copy
+    node = ALL[name]
+    tape = T.Tape(node)
+    pts = cases.eval_points()
+    pts = torch.cat([pts[:14], pts[16:]])   # the 1e3 / 1e9 points are checked on the GPU, values only
+    with torch.no_grad():
+        d = tape_interp.run(tape, tape.lower_theta(tape.theta()), pts)
+        np.testing.assert_allclose(d.numpy(), O.sdf(node, pts).numpy(), rtol=2e-5, atol=2e-6)
+    node64 = copy.deepcopy(node).double()
+    tape64 = T.Tape(node64)
+    p64 = pts.double()
+    theta = tape64.theta().detach().requires_grad_(True)
+    x = p64.clone().requires_grad_(True)
+    d = tape_interp.run(tape64, tape64.lower_theta(theta), x)
+    xo = p64.clone().requires_grad_(True)
+    do = O.sdf(node64, xo)
+    np.testing.assert_allclose(d.detach().numpy(), do.detach().numpy(), rtol=1e-12, atol=1e-12)
+    g = torch.Generator().manual_seed(7)
+    w = torch.randn(pts.shape[0], 1, generator=g).double()
+    params = list(node64.parameters())
+    gi = torch.autograd.grad((d * w).sum(), [x, theta], allow_unused=True)
+    go = torch.autograd.grad((do * w).sum(), [xo] + params, allow_unused=True)
+    np.testing.assert_allclose(gi[0].numpy(), go[0].numpy(), rtol=1e-9, atol=1e-9)
+    if params:
+        flat = torch.cat([(gp if gp is not None else torch.zeros_like(p)).reshape(-1)
+                          for p, gp in zip(params, go[1:])])
+        np.testing.assert_allclose(gi[1].numpy(), flat.numpy(), rtol=1e-8, atol=1e-9)
+
+
+def test_flops_per_eval_match_survey_table():
+    """algorithmic flops per scene evaluation."""
+    assert T.Tape(S.make_test_scene2()).flops_per_eval == 64
+    assert T.Tape(S.make_test_scene()).flops_per_eval == 181
+    assert T.Tape(S.make_synthetic_scene(64, 0, False)).flops_per_eval == 3382
+    assert T.Tape(S.make_synthetic_scene(64, 0, True)).flops_per_eval == 3404
+    assert T.Tape(S.make_synthetic_scene(512, 0, True)).flops_per_eval == 27070
+
+
+def test_tape_structure_and_errors():
+    t = T.Tape(S.make_test_scene2())
+    assert t.n_nodes == 2 and t.max_depth == 2 and t.n_leaves == 4
+    assert t.code.dtype == np.int32 and t.code.shape[1] == 4 and t.n_par % 4 == 0
+    ops = [h & 15 for h in t.code[:, 0]]
+    assert ops == [T.OP_OPEN_MIN, T.OP_BOX, T.OP_OPEN_MIN, T.OP_SPHERE, T.OP_TORUS, T.OP_LINE,
+                   T.OP_CLOSE_MIN, T.OP_CLOSE_MIN]
+    # parameter order follows module.parameters(), so optimisers / state_dict carry over
+    assert [n for n, _ in S.make_test_scene().named_parameters()][:3] == [
+        "blend_k", "sdfs.0.translation", "sdfs.0.orientation"]
+    with pytest.raises(NotImplementedError):
+        T.Tape(torch.nn.Linear(3, 1))
+    deep = S.SDFSphere(1.0)
+    for _ in range(4):
+        deep = S.SDFOnion(deep, 0.1)
+    with pytest.raises(NotImplementedError):
+        T.Tape(deep)
+    nest = S.SDFSphere(1.0)
+    for _ in range(9):
+        nest = S.SDFUnion([nest, S.SDFPlane()])
+    with pytest.raises(NotImplementedError):
+        T.Tape(nest)
+
+
+def test_lowered_params_cache_tracks_parameter_updates():
+    scene = S.make_test_scene()
+    tape = T.tape_of(scene)
+    with torch.no_grad():
+        a = tape.lowered_params()
+        assert tape.lowered_params() is a
+        scene.blend_k.add_(1.0)
+        b = tape.lowered_params()
+    assert b is not a and not torch.equal(a, b)
+    assert tape.lowered_params().requires_grad      # autograd on: fresh, connected to parameters
