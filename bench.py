@@ -1,0 +1,472 @@
+#!/usr/bin/env python
+"""Benchmark of the sphere-tracing hot path (contract: see the task statement / DESIGN.md §Measurement).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c1|c2|c3|c4|c5] [--impl reference]
+
+A *step* is one pass of the hot path over one batch of synthetic input: one rendered frame (one
+view per GPU; weak scaling), or, for c4, one forward+backward of the inverse-rendering loss.
+``value`` is whole-job Mrays/s with inputs resident in HBM, ``e2e`` the same through the public
+API from pinned host buffers (camera poses in, images out).  The dominant kernel is timed alone
+with CUDA events for the roofline line.  ``--impl reference`` times the CPU oracle port
+(oracle/sdf_oracle.py -- the reference's own PyTorch algorithm restated) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+PX = 3.45e-6            # main.py:25
+STEPS = 32              # main.py:26
+EPS = 5e-2              # main.py:42
+
+# shader flop counts of SURVEY.md §8(d)
+SHADER_FLOPS = {0: 8, 1: 18, 2: 7, 3: 7, 4: 6, 5: 7, 6: 20, 7: 20}
+STENCIL_MODES = {0, 4, 5, 6, 7}
+
+
+def workload(name: str):
+    """BASELINE.json configs as concrete inputs."""
+    from ray_marching_b200 import scene as S
+    if name == "c1":
+        return dict(name=name, scene=S.make_test_scene2, desc="make_test_scene2 640x480 distance+proximity",
+                    width=640, height=480, modes=(1, 2), bounces=0, cam_t=(0.0, 0.0, 1.0), backward=False)
+    if name == "c2":
+        return dict(name=name, scene=S.make_test_scene2,
+                    desc="make_test_scene2 1920x1080 normal+laplacian+lambertian+vignette from one march",
+                    width=1920, height=1080, modes=(4, 5, 0, 3), bounces=0, cam_t=(0.0, 0.0, 1.0),
+                    backward=False)
+    if name == "c3":
+        return dict(name=name, scene=lambda: S.make_synthetic_scene(64, 0, True),
+                    desc="synthetic-64 smooth union in shell, 3840x2160, 2 reflection bounces, lambertian",
+                    width=3840, height=2160, modes=(0,), bounces=2, cam_t=(0.0, 0.0, -4.0), backward=False)
+    if name == "c4":
+        return dict(name=name, scene=S.make_test_scene2,
+                    desc="inverse rendering fwd+bwd, make_test_scene2 1024x1024, lambertian+depth MSE",
+                    width=1024, height=1024, modes=(0,), bounces=0, cam_t=(0.0, 0.1, 1.0), backward=True)
+    if name == "c5":
+        return dict(name=name, scene=lambda: S.make_synthetic_scene(512, 0, True),
+                    desc="synthetic-512 smooth union in shell, 3840x2160 per view, lambertian",
+                    width=3840, height=2160, modes=(0,), bounces=0, cam_t=(0.0, 0.0, -4.0), backward=False)
+    raise SystemExit(f"unknown workload {name}")
+
+
+def flops_per_ray(tape, wl, steps=STEPS) -> float:
+    """Algorithmic forward flops per ray, SURVEY.md §8(d) counting rule."""
+    F = tape.flops_per_eval
+    stencil = bool(set(wl["modes"]) & STENCIL_MODES) or wl["bounces"] > 0
+    seg = steps * (F + 6) + F + (4 * F + 45 if stencil else 0)
+    total = 63 + seg * (wl["bounces"] + 1) + sum(SHADER_FLOPS[m] for m in wl["modes"])
+    if wl["bounces"]:
+        total += wl["bounces"] * 20            # hit test + reflection + lift
+    return float(total)
+
+
+def ring_pose(j: int, n: int, base_t, device):
+    """View j of n on a ring around the y axis looking at the origin."""
+    from ray_marching_b200 import quaternion as Q
+    th = 2 * math.pi * j / max(n, 1)
+    q = torch.tensor([[math.cos(th / 2), 0.0, math.sin(th / 2), 0.0]])
+    t = Q.rotation(torch.tensor([list(base_t)]), q)
+    return q.to(device), t.to(device)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons while the GPU is under load."""
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.FIELDS}",
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            parts = [p.strip() for p in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0])); mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measure_fp32_peak(device) -> dict:
+    """FFMA-only microbenchmark on all SMs -> TFLOP/s (the FP32 roofline denominator)."""
+    import ctypes as C
+    from ray_marching_b200 import _lib
+    lib = _lib.lib()
+    sink = torch.zeros(4, device=device)
+    blocks, iters = 148 * 8, 4096
+    st = torch.cuda.current_stream(device).cuda_stream
+    for _ in range(3):
+        _lib.check(lib.rm_probe_ffma(blocks, iters, sink.data_ptr(), st), "rm_probe_ffma")
+    best = float("inf")
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.check(lib.rm_probe_ffma(blocks, iters, sink.data_ptr(), st), "rm_probe_ffma")
+        e1.record()
+        e1.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    flops = blocks * 256 * iters * 128 * 2
+    return {"tflops": flops / (best * 1e-3) / 1e12, "ms": best}
+
+
+# ---------------------------------------------------------------------------- GPU arm
+def run_gpu(args):
+    import torch.distributed as dist
+    from ray_marching_b200 import RenderLoop, ops
+    from ray_marching_b200.tape import tape_of
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    wl = workload(args.workload)
+    W, H = wl["width"], wl["height"]
+    scene = wl["scene"]()
+    loop = RenderLoop(scene, num_cameras=1, px_width=W, px_height=H, focal_length=PX * H,
+                      sensor_width=PX * W, sensor_height=PX * H, normals_eps=EPS).to(dev)
+    loop.early_exit = bool(args.early_exit)
+    tape = tape_of(loop.scene)
+    rays = W * H                                   # per GPU and step: one view per rank (weak scaling)
+    fpr = flops_per_ray(tape, wl)
+    modes = wl["modes"]
+    needs_reduce = any(m in (1, 2, 5) for m in modes)
+    # view `rank` of a `world`-view ring; N=1 is the reference camera of the config
+    q, t = ring_pose(rank, world, wl["cam_t"], dev)
+    res_holder = {}
+
+    def gpu_step():
+        """One frame with everything resident in HBM.  Kernels: reduce_init, render, [finalize]."""
+        out = loop.render_planes(q, t, modes=modes, marching_steps=STEPS, bounces=wl["bounces"],
+                                 finalize=False, out=res_holder.get("res"))
+        res_holder["res"] = out
+        if needs_reduce:
+            if world > 1:      # global min/max over the camera batch (shader.py:35-36,84)
+                r = out.reduce
+                mins, maxs = r[[0, 2]].contiguous(), r[[1, 3, 4, 5, 6, 7]].contiguous()
+                dist.all_reduce(mins, op=dist.ReduceOp.MIN)
+                dist.all_reduce(maxs, op=dist.ReduceOp.MAX)
+                r[[0, 2]] = mins
+                r[[1, 3, 4, 5, 6, 7]] = maxs
+            mask = 0
+            for m in modes:
+                mask |= 1 << m
+            ops.shade_finalize(out, mask)
+        return out
+
+    if wl["backward"]:
+        gpu_step, extra = make_backward_step(loop, scene, q, t, dev, world)
+    launches_per_step = (3 if needs_reduce else 1) if not wl["backward"] else extra["launches"]
+
+    flush = torch.empty(192 * 1024 * 1024 // 4, device=dev)      # 192 MB > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    peak = measure_fp32_peak(dev)
+    for _ in range(max(args.warmup, 3)):
+        gpu_step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    evs = []
+    barrier()
+    wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush.zero_()                                # L2 flush between timed iterations (untimed)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        gpu_step()
+        e1.record()
+        evs.append((e0, e1))
+    barrier()
+    wall = time.perf_counter() - wall0
+    total_ms = sum(a.elapsed_time(b) for a, b in evs)
+
+    # dominant kernel alone (render_kernel), CUDA events on the launching stream
+    kern_ms = None
+    if not wl["backward"]:
+        ks = []
+        poses_k = ops.pose_records(q, t)
+        mask_k = sum(1 << m for m in modes)
+        for _ in range(max(3, min(args.steps, 20))):
+            flush.zero_()
+            if needs_reduce:
+                ops.check(ops.lib().rm_reduce_init(res_holder["res"].reduce.data_ptr(),
+                                                   torch.cuda.current_stream(dev).cuda_stream), "init")
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            ops.render(tape, loop.camera.struct(), poses_k, steps=STEPS, normals_eps=EPS,
+                       mode_mask=mask_k, bounces=wl["bounces"], early_exit=loop.early_exit,
+                       fast_math=loop.fast_math, cmap=loop.shader.cyclic_cmap, finalize=False,
+                       reduce=res_holder["res"].reduce if needs_reduce else None,
+                       out=res_holder["res"])
+            e1.record()
+            e1.synchronize()
+            ks.append(e0.elapsed_time(e1))
+        kern_ms = sum(ks) / len(ks)
+
+    # end-to-end: pinned host pose in, images out to pinned host memory, every step
+    e2e = measure_e2e(loop, wl, q, t, dev, args, world, barrier) if not wl["backward"] else \
+        extra["e2e"](args, barrier)
+
+    # sustained repeat of the same step while the clock sampler runs (>= 1.5 s under load)
+    t_end = time.perf_counter() + 1.5
+    while time.perf_counter() < t_end:
+        for _ in range(10):
+            gpu_step()
+        torch.cuda.synchronize()
+    clocks = sampler.stop() if rank == 0 else None
+
+    tmax = torch.tensor([total_ms, e2e["ms_total"], kern_ms or 0.0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    total_ms, e2e_ms, kern_max = (float(x) for x in tmax.tolist())
+
+    if rank == 0:
+        ms_step = total_ms / args.steps
+        value = rays * world / (ms_step * 1e-3) / 1e6
+        line = {
+            "metric": "Mrays/s fwd+bwd" if wl["backward"] else "Mrays/s fwd",
+            "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{wl['name']}: {wl['desc']}", "rays_per_gpu_per_step": rays,
+                       "marching_steps": STEPS, "views": world, "sharding": "one view per GPU",
+                       "l2": "flushed between timed iterations (192 MB memset, untimed)",
+                       "early_exit": bool(args.early_exit), "tape": tape.describe(),
+                       "msteps_per_s": value * STEPS * (wl["bounces"] + 1),
+                       "wall_s_timed_region": wall},
+            "e2e": {"value": rays * world / (e2e_ms / args.steps * 1e-3) / 1e6, "unit": "Mrays/s",
+                    "h2d_bytes_per_step": e2e["h2d"], "d2h_bytes_per_step": e2e["d2h"]},
+            "gpu_launches": launches_per_step * args.steps,
+            "clocks": clocks,
+        }
+        if kern_ms is not None:
+            ach = fpr * rays / (kern_max * 1e-3) / 1e12
+            line["roofline"] = {
+                "bound": "fp32", "kernel": "render_kernel", "achieved": ach, "peak": peak["tflops"],
+                "unit": "TFLOP/s", "frac": ach / peak["tflops"], "traffic": None,
+                "kernel_ms": kern_max, "algorithmic_flops_per_ray": fpr,
+                "peak_source": "measured: FFMA microbenchmark (rm_probe_ffma) on this GPU; "
+                               "nominal 74.5 TFLOP/s at 1965 MHz",
+            }
+        else:
+            line["roofline"] = extra["roofline"](total_ms / args.steps, peak)
+        line["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def measure_e2e(loop, wl, q, t, dev, args, world, barrier):
+    """Public API with HOST buffers: pose H2D from pinned memory, render, images D2H to pinned."""
+    from ray_marching_b200 import ops
+    modes = wl["modes"]
+    q_h, t_h = q.cpu().pin_memory(), t.cpu().pin_memory()
+    rays = wl["width"] * wl["height"]
+    host = {m: torch.empty(rays, ops.MODE_CHANNELS[m]).pin_memory() for m in modes}
+    d2h = sum(h.numel() * 4 for h in host.values())
+    h2d = (q_h.numel() + t_h.numel()) * 4
+
+    def step():
+        qd, td = q_h.to(dev, non_blocking=True), t_h.to(dev, non_blocking=True)
+        res = loop.render_planes(qd, td, modes=modes, marching_steps=STEPS, bounces=wl["bounces"])
+        for m in modes:
+            host[m].copy_(res.images[m], non_blocking=True)
+        torch.cuda.synchronize()
+
+    for _ in range(3):
+        step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    barrier()
+    return {"ms_total": (time.perf_counter() - t0) * 1e3, "h2d": h2d, "d2h": d2h}
+
+
+def make_backward_step(loop, scene, q, t, dev, world):
+    raise SystemExit("workload c4 (fwd+bwd) is wired in once the backward kernels land")
+
+
+# ---------------------------------------------------------------------------- CPU arm
+def _oracle_frame(wl, width, height, threads):
+    """One frame of the workload on the CPU oracle port (float32, eager) at width x height."""
+    from oracle import sdf_oracle as O
+    from ray_marching_b200.rendering.shader import load_cmap
+    torch.set_num_threads(threads)
+    scene = wl["scene"]()
+    orc = O.RenderLoopOracle(scene, 1, width, height, PX * wl["height"], PX * wl["width"],
+                             PX * wl["height"], EPS, cmap=load_cmap())
+    q = torch.tensor([[1.0, 0.0, 0.0, 0.0]])
+    t = torch.tensor([list(wl["cam_t"])])
+
+    def frame():
+        if wl["backward"]:
+            params = list(scene.parameters())
+            qq, tt = q.clone().requires_grad_(True), t.clone().requires_grad_(True)
+            gb = orc.gbuffer(qq, tt, STEPS)
+            lam = O.shade_lambertian(gb["dirs"], gb["normals"])
+            depth = (gb["pos"] - gb["px"]).norm(dim=-1, keepdim=True)
+            loss = ((lam - 0.5) ** 2).mean() + ((depth - 0.3) ** 2).mean()
+            torch.autograd.grad(loss, [qq, tt] + params, allow_unused=True)
+            return
+        with torch.no_grad():
+            px, frames, pos0, dirs = O.camera_rays(*orc.base, q, t)
+            if wl["bounces"]:
+                pos, dirs, _, normals, lap = O.reflected_march(scene, pos0, dirs, STEPS, EPS, wl["bounces"])
+                dists = O.sdf(scene, pos)
+            else:
+                pos = O.march(scene, pos0, dirs, STEPS)
+                dists = O.sdf(scene, pos)
+                normals, lap = O.normals_laplacian(scene, pos, EPS)
+            for m in wl["modes"]:
+                O.shade(px, q, frames, dirs, pos, normals, lap, dists, m, 1, orc.cmap)
+    return frame
+
+
+def cpu_sample_size(wl):
+    """Bounded sample of the same workload: full frame for the small scenes, a centred sub-image
+    (same camera, same per-ray work; rays are independent) for the large ones."""
+    if wl["name"] in ("c1", "c2"):
+        return wl["width"], wl["height"], "full frame"
+    if wl["name"] == "c4":
+        return 512, 512, "512x512 sub-sample of the 1024x1024 frame (same intrinsics per pixel), fwd+bwd"
+    if wl["name"] == "c3":
+        return 192, 108, "192x108 sub-sample of the 4K frame, all 3 march segments"
+    return 64, 36, "64x36 sub-sample of one 4K view"
+
+
+def cpu_baseline(wl, budget_s=30.0, steps=1, warmup=1):
+    threads = os.cpu_count() or 1
+    w, h, sample = cpu_sample_size(wl)
+    frame = _oracle_frame(wl, w, h, threads)
+    for _ in range(warmup):
+        frame()
+    best, spent, n = float("inf"), 0.0, 0
+    while n < max(steps, 1) or (n < 3 and spent < budget_s / 2):
+        t0 = time.perf_counter()
+        frame()
+        dt = time.perf_counter() - t0
+        best, spent, n = min(best, dt), spent + dt, n + 1
+    return {"value": w * h / best / 1e6, "unit": "Mrays/s", "cores": threads, "kind": "port",
+            "sample": f"{sample}; oracle/sdf_oracle.py (reference algorithm restated, torch CPU eager "
+                      f"float32), best of {n}, {best:.3f} s per frame"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path (oracle port; the
+    reference is Python/PyTorch and /root/reference does not exist on the GPU box)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    wl = workload(args.workload)
+    threads = os.cpu_count() or 1
+    w, h, sample = cpu_sample_size(wl)
+    frame = _oracle_frame(wl, w, h, threads)
+    for _ in range(min(args.warmup, 2)):
+        frame()
+    t0 = time.perf_counter()
+    steps = max(1, min(args.steps, 5))
+    for _ in range(steps):
+        frame()
+    dt = (time.perf_counter() - t0) / steps
+    value = w * h / dt / 1e6
+    line = {
+        "impl": "reference", "metric": "Mrays/s fwd+bwd" if wl["backward"] else "Mrays/s fwd",
+        "value": value, "unit": "Mrays/s", "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
+        "steps": steps, "warmup": min(args.warmup, 2), "ms_per_step": dt * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": f"{wl['name']}: {wl['desc']}", "sample": sample,
+                   "marching_steps": STEPS, "note": "CPU arm: host cores only, rank 0"},
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c4", "c5"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--early-exit", type=int, default=0,
+                    help="1: bit-identical fixed-point exit of the march loop (executed < algorithmic work)")
+    ap.add_argument("--cpu-budget", type=float, default=20.0)
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus != world and args.gpus > 1:
+        # convenience: python bench.py --gpus N re-launches itself under torchrun
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+               f"--nproc-per-node={args.gpus}", "--master-addr", "127.0.0.1", "--master-port", "29533",
+               os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()

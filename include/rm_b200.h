@@ -137,6 +137,10 @@ int rm_reduce_init(float* reduce, void* stream);
 int rm_shade_finalize(const float* reduce, uint32_t mode_mask, int64_t n_rays,
                       float* const* image, float* rgba, int32_t display_mode, void* stream);
 
+/* Measurement aid for the FP32 roofline denominator (bench.py): blocks x 256 threads, each issuing
+ * iters*128 independent FFMA (256 flop).  Not part of the render path. */
+int rm_probe_ffma(int32_t blocks, int32_t iters, float* sink, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

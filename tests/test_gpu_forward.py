@@ -1,0 +1,247 @@
+"""GPU parity of the forward path: CUDA kernels (through the drop-in modules -> torch ops ->
+ctypes -> C ABI) against the CPU oracle and the committed reference fixtures.
+
+Tolerances (BASELINE.json north_star): hit depth and SDF value 1e-4 relative (an absolute floor
+of 1e-5 scene units covers converged hits whose |f| is rounding noise), shaded pixels 1e-3
+absolute.  NaN masks must coincide wherever the reference is NaN on purpose.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import cases, sdf_oracle as O
+from ray_marching_b200 import scene as S
+from ray_marching_b200 import RenderLoop, PinholeCamera, SDFMarcher, SDFNormals, Shader
+from ray_marching_b200.rendering.shader import load_cmap
+from ray_marching_b200.scene.scene_registry import _default_classes
+from rm_testutil import t32
+
+pytestmark = pytest.mark.gpu
+C = _default_classes()
+DEV = "cuda"
+
+
+def close(a, b, rtol, atol, what=""):
+    a = a.detach().cpu().numpy() if isinstance(a, torch.Tensor) else np.asarray(a)
+    b = b.detach().cpu().numpy() if isinstance(b, torch.Tensor) else np.asarray(b)
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    assert np.array_equal(np.isnan(a), np.isnan(b)), f"{what}: NaN masks differ"
+    np.testing.assert_allclose(np.nan_to_num(a), np.nan_to_num(b), rtol=rtol, atol=atol, err_msg=what)
+
+
+SCENES = {
+    "test_scene": S.make_test_scene, "test_scene2": S.make_test_scene2,
+    "syn8": lambda: S.make_synthetic_scene(8, 0, True),
+    "syn64": lambda: S.make_synthetic_scene(64, 0, False),
+}
+
+
+@pytest.mark.parametrize("name", list(cases.node_cases(C).keys()) + list(SCENES.keys()))
+def test_sdf_eval_matches_oracle_and_golden(golden, name):
+    node = cases.node_cases(C)[name] if name not in SCENES else SCENES[name]()
+    pts = cases.eval_points()
+    want = O.sdf(node, pts).detach()
+    got = node.to(DEV)(pts.to(DEV))
+    assert got.shape == (pts.shape[0], 1) and got.is_cuda
+    close(got, want, 1e-4, 1e-5, name)
+    g = golden("nodes")
+    key = {"test_scene": "scenes/test_scene/value", "test_scene2": "scenes/test_scene2/value",
+           "syn8": "scenes/synthetic8_shell/value", "syn64": "scenes/synthetic64/value"}.get(
+               name, f"nodes/{name}/value")
+    close(got, g[key], 1e-4, 1e-5, name + " vs reference fixture")
+
+
+def test_sdf_eval_shapes_and_edge_cases():
+    scene = S.make_test_scene2().to(DEV)
+    assert scene(torch.zeros(0, 3, device=DEV)).shape == (0, 1)
+    for n in (1, 2, 3, 5, 511, 513):                     # ragged tails of the 4-per-thread mapping
+        p = torch.randn(n, 3, device=DEV)
+        close(scene(p), O.sdf(S.make_test_scene2(), p.cpu()).detach(), 1e-4, 1e-5, f"n={n}")
+    p = torch.randn(2, 5, 4, 3, device=DEV)              # arbitrary leading dims, stencil-style
+    assert scene(p).shape == (2, 5, 4, 1)
+    close(scene(p), O.sdf(S.make_test_scene2(), p.cpu()).detach(), 1e-4, 1e-5)
+    nc = p.transpose(0, 1)                               # non-contiguous input
+    close(scene(nc), O.sdf(S.make_test_scene2(), nc.cpu()).detach(), 1e-4, 1e-5)
+    with pytest.raises(ValueError):
+        scene(torch.zeros(4, 2, device=DEV))
+
+
+def test_camera_matches_reference_fixture(golden):
+    g = golden("camera")
+    cam = PinholeCamera(2, 8, 6, 17e-3, 24e-3, 18e-3)
+    pos, frames, pos2, dirs = cam(t32(g["camera/q"]).to(DEV), t32(g["camera/t"]).to(DEV))
+    assert pos is pos2 and pos.shape == (2, 6, 8, 3) and frames.shape == (2, 3, 3)
+    close(pos, g["camera/pos"], 1e-5, 1e-7, "pos")
+    close(dirs, g["camera/dirs"], 1e-5, 1e-6, "dirs")
+    close(frames, g["camera/frames"], 1e-5, 1e-6, "frames")
+    close(cam.ray_positions, g["camera/base_pos"], 1e-5, 1e-9, "base pos")
+    close(cam.ray_directions, g["camera/base_dirs"], 1e-5, 1e-6, "base dirs")
+
+
+def _loop(scene, w, h, n=1):
+    return RenderLoop(scene.to(DEV), normals_eps=5e-2,
+                      **dict(cases.config1_camera(w, h), num_cameras=n)).to(DEV)
+
+
+@pytest.mark.parametrize("tag,build,fast", [
+    ("scene2", S.make_test_scene2, True), ("scene2", S.make_test_scene2, False),
+    ("scene1", S.make_test_scene, False), ("syn8", lambda: S.make_synthetic_scene(8, 0, True), True),
+])
+def test_gbuffer_matches_reference_fixture(golden, tag, build, fast):
+    """camera + march + f(p) + stencil on the 32x24 fixtures (config-1 camera, 32 steps)."""
+    g = golden("render")
+    loop = _loop(build(), 32, 24)
+    loop.fast_math = fast
+    q, t = t32(g[f"render/{tag}/q"]).to(DEV), t32(g[f"render/{tag}/t"]).to(DEV)
+    res = loop.render_planes(q, t, gbuffer=True)
+    ref = {k: g[f"render/{tag}/{k}"].reshape(-1, g[f"render/{tag}/{k}"].shape[-1])
+           for k in ("pos0", "dirs", "pos", "sdf", "normals", "lap")}
+    close(res.origin, ref["pos0"], 1e-5, 1e-7, "origin")
+    close(res.dirs, ref["dirs"], 1e-5, 1e-6, "dirs")
+    depth_ref = np.linalg.norm(ref["pos"] - ref["pos0"], axis=-1)
+    hit = np.abs(ref["sdf"][:, 0]) < 1e-3               # rays that converged in the reference
+    assert hit.sum() > 50
+    depth = (res.pos - res.origin).norm(dim=-1).cpu().numpy()
+    np.testing.assert_allclose(depth[hit], depth_ref[hit], rtol=1e-4)
+    np.testing.assert_allclose(res.pos.cpu().numpy()[hit], ref["pos"][hit], rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(res.sdf.cpu().numpy()[hit], ref["sdf"][hit, 0], rtol=1e-4, atol=1e-5)
+    n_got, n_ref = res.normals.cpu().numpy()[hit], ref["normals"][hit]
+    assert np.isfinite(n_got).all()
+    np.testing.assert_allclose(n_got, n_ref, atol=1e-3)
+    np.testing.assert_allclose(res.laplacian.cpu().numpy()[hit], ref["lap"][hit, 0], rtol=2e-3, atol=2e-2)
+    if tag == "scene2":                                  # closed scene: every ray hits
+        assert hit.all()
+
+
+@pytest.mark.parametrize("tag,build", [("scene2", S.make_test_scene2),
+                                       ("syn8", lambda: S.make_synthetic_scene(8, 0, True))])
+@pytest.mark.parametrize("mode", range(8))
+def test_shaders_match_reference_fixture(golden, tag, build, mode):
+    """RenderLoop.forward for every shader mode; pixels within 1e-3 absolute."""
+    g = golden("render")
+    loop = _loop(build(), 32, 24)
+    q, t = t32(g[f"render/{tag}/q"]).to(DEV), t32(g[f"render/{tag}/t"]).to(DEV)
+    degree = 3 if mode >= 6 else 1
+    with torch.no_grad():
+        img = loop(q, t, mode, degree, 32)
+    want = g[f"render/{tag}/mode{mode}"]
+    assert img.shape == (1, 24, 32, 3) and img.shape == want.shape
+    got = img.contiguous().cpu().numpy()
+    assert np.array_equal(np.isnan(got), np.isnan(want)), "NaN masks differ"
+    err = np.abs(np.nan_to_num(got) - np.nan_to_num(want))
+    if mode >= 6:
+        # colour-wheel lookup: a 1-ulp angle difference may move a pixel to the neighbouring LUT
+        # entry; allow 1% of pixels to be one entry off (the LUT is smooth), none further.
+        assert (err > 1e-3).mean() < 0.01 and err.max() < 2e-2
+    else:
+        assert err.max() <= 1e-3, (mode, err.max())
+    # headless display buffer (H,W,4), alpha 1, same pixels
+    rgba = loop.display_frame(q, t, mode, degree, 32)
+    assert rgba.shape == (24, 32, 4) and rgba.is_contiguous()
+    assert torch.equal(rgba[..., 3], torch.ones_like(rgba[..., 3]))
+    e2 = np.abs(np.nan_to_num(rgba[..., :3].cpu().numpy()) - np.nan_to_num(want[0]))
+    assert (e2 > 1e-3).mean() < (0.01 if mode >= 6 else 1e-9)
+
+
+def test_proximity_is_all_nan_on_converged_scene(golden):
+    """On scene2 every ray converges, log-range is 0 and the reference emits 0/0 = NaN."""
+    g = golden("render")
+    assert np.isnan(g["render/scene2/mode2"]).all()
+    loop = _loop(S.make_test_scene2(), 32, 24)
+    with torch.no_grad():
+        img = loop(torch.tensor([[1.0, 0, 0, 0]], device=DEV), torch.tensor([[0.0, 0, 1.0]], device=DEV), 2)
+    assert torch.isnan(img).all()
+
+
+def test_marcher_and_normals_modules(golden):
+    g = golden("render")
+    scene = S.make_test_scene2().to(DEV)
+    pos0, dirs = t32(g["render/scene2/pos0"]).to(DEV), t32(g["render/scene2/dirs"]).to(DEV)
+    with torch.no_grad():
+        pos = SDFMarcher(scene)(pos0, dirs, 32)
+        n, lap = SDFNormals(scene, 5e-2).to(DEV)(pos)
+        pos7 = SDFMarcher(scene)(pos0, dirs, 7)
+    assert pos.shape == pos0.shape and n.shape == pos0.shape and lap.shape == (1, 24, 32, 1)
+    close(pos, g["render/scene2/pos"], 1e-4, 1e-5, "march")
+    close(n, g["render/scene2/normals"], 0, 1e-3, "normals")
+    close(lap, g["render/scene2/lap"], 2e-3, 2e-2, "laplacian")
+    ref7 = O.march(S.make_test_scene2(), pos0.cpu(), dirs.cpu(), 7)
+    close(pos7, ref7.detach(), 1e-4, 1e-5, "march 7 steps")
+    assert SDFMarcher(scene)(pos0, dirs, 0).equal(pos0)
+
+
+def test_early_exit_is_bit_identical():
+    loop = _loop(S.make_test_scene2(), 160, 120)
+    q = torch.tensor([[1.0, 0, 0, 0]], device=DEV)
+    t = torch.tensor([[0.0, 0, 1.0]], device=DEV)
+    a = loop.render_planes(q, t, gbuffer=True, modes=(0, 4))
+    loop.early_exit = True
+    b = loop.render_planes(q, t, gbuffer=True, modes=(0, 4))
+    for x, y in ((a.pos, b.pos), (a.sdf, b.sdf), (a.normals, b.normals), (a.images[0], b.images[0])):
+        assert torch.equal(x, y)
+
+
+def test_multi_view_and_ray_ranges():
+    """N=3 views: per-view vignette (the reference only broadcasts for N=1), and a render split
+    into ray ranges is bit-identical to the one-shot render (rays are independent)."""
+    scene = S.make_synthetic_scene(8, 0, True)
+    loop = _loop(scene, 40, 30, n=3)
+    q = torch.nn.functional.normalize(torch.tensor(
+        [[1.0, 0, 0, 0], [0.9, 0.1, -0.3, 0.05], [0.7, -0.2, 0.6, 0.1]], device=DEV), dim=-1)
+    t = torch.tensor([[0.0, 0, -4.0], [0.5, 0.2, -3.5], [-2.0, 0.3, -3.0]], device=DEV)
+    full = loop.render_planes(q, t, gbuffer=True, modes=(0, 3, 4))
+    orc = O.RenderLoopOracle(S.make_synthetic_scene(8, 0, True), normals_eps=5e-2,
+                             **dict(cases.config1_camera(40, 30), num_cameras=3))
+    with torch.no_grad():
+        gb = orc.gbuffer(q.cpu(), t.cpu(), 32)
+        lam = O.shade_lambertian(gb["dirs"], gb["normals"])
+        vig = torch.stack([O.shade_vignette(gb["dirs"][i:i + 1], gb["frames"][i:i + 1]) for i in range(3)])
+    close(full.pos.reshape(3, 30, 40, 3), gb["pos"], 1e-4, 1e-5, "pos")
+    close(full.images[0].reshape(3, 30, 40, 1), lam, 0, 1e-3, "lambertian")
+    close(full.images[3].reshape(3, 30, 40, 1), vig.reshape(3, 30, 40, 1), 0, 1e-3, "vignette")
+    total = 3 * 30 * 40
+    cuts = [0, 1001, 2402, total]                         # deliberately not multiples of 4
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        part = loop.render_planes(q, t, gbuffer=True, modes=(0, 4), ray_begin=a, n_rays=b - a)
+        assert torch.equal(part.pos, full.pos[a:b])
+        assert torch.equal(part.images[4], full.images[4][a:b])
+        assert torch.equal(part.images[0], full.images[0][a:b])
+
+
+def test_reflected_march_matches_oracle_composition():
+    """Config-3 semantics: B=2 bounces, tau=1e-3, delta=2*eps."""
+    scene = S.make_synthetic_scene(8, 0, True)
+    loop = _loop(scene, 48, 36)
+    loop.fast_math = False
+    q = torch.tensor([[1.0, 0, 0, 0]], device=DEV)
+    t = torch.tensor([[0.0, 0, -4.0]], device=DEV)
+    res = loop.render_planes(q, t, gbuffer=True, modes=(0,), bounces=2)
+    orc = O.RenderLoopOracle(S.make_synthetic_scene(8, 0, True), normals_eps=5e-2,
+                             **cases.config1_camera(48, 36))
+    with torch.no_grad():
+        px, frames, pos0, dirs = O.camera_rays(*orc.base, q.cpu(), t.cpu())
+        pos, dirs2, hit, normals, lap = O.reflected_march(orc.scene, pos0, dirs, 32, 5e-2, 2)
+    # a reflection decision flips if |f| straddles tau within rounding: compare where positions agree
+    got = res.pos.reshape(pos.shape).cpu()
+    same = (got - pos).norm(dim=-1) < 1e-3
+    assert same.float().mean() > 0.97
+    close(res.dirs.reshape(pos.shape)[same], dirs2[same], 0, 2e-3, "reflected dirs")
+    close(res.normals.reshape(pos.shape)[same], normals[same], 0, 2e-3, "normals")
+
+
+def test_config1_full_size_properties():
+    """640x480 config 1: closed scene => every ray converges (|f| < 1e-5), depth of the centre
+    pixel is the SURVEY.md probe value, normals are unit, distance image spans [0,1]."""
+    loop = _loop(S.make_test_scene2(), 640, 480)
+    q = torch.tensor([[1.0, 0, 0, 0]], device=DEV)
+    t = torch.tensor([[0.0, 0, 1.0]], device=DEV)
+    res = loop.render_planes(q, t, gbuffer=True, modes=(1, 2))
+    assert res.sdf.abs().max().item() < 1e-5
+    depth = (res.pos - res.origin).norm(dim=-1).reshape(480, 640)
+    assert abs(depth[240, 320].item() - 0.25000021) < 1e-4 * 0.25
+    assert abs(depth[0, 0].item() - 0.30783942) < 1e-4 * 0.31
+    assert abs(depth[100, 500].item() - 0.27159759) < 1e-4 * 0.27
+    assert (res.normals.norm(dim=-1) - 1).abs().max().item() < 1e-5
+    d = res.images[1]
+    assert d.min().item() == 0.0 and abs(d.max().item() - 1.0) < 1e-6
+    assert torch.isnan(res.images[2]).all()
