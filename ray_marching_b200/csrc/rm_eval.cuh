@@ -72,11 +72,13 @@ __device__ __forceinline__ void eval_scene(const TapeView& T, const float (&px)[
             }
             P += prim_f4(op);
         } else if (op == OP_OPEN_MIN || op == OP_OPEN_SMOOTH) {
-            float* s = stk + sp * (2 * K + 1);
+            if (!(head & HEAD_ROOT)) {
+                float* s = stk + sp * (2 * K + 1);
 #pragma unroll
-            for (int k = 0; k < K; ++k) { s[2 * k] = a0[k]; s[2 * k + 1] = a1[k]; }
-            s[2 * K] = c;
-            ++sp;
+                for (int k = 0; k < K; ++k) { s[2 * k] = a0[k]; s[2 * k + 1] = a1[k]; }
+                s[2 * K] = c;
+                ++sp;
+            }
             if (op == OP_OPEN_MIN) {
 #pragma unroll
                 for (int k = 0; k < K; ++k) a0[k] = CUDART_INF_F;
@@ -94,11 +96,13 @@ __device__ __forceinline__ void eval_scene(const TapeView& T, const float (&px)[
 #pragma unroll
                 for (int k = 0; k < K; ++k) d[k] = M::div(a0[k] + M::log(a1[k]), c);
             }
-            --sp;
-            const float* s = stk + sp * (2 * K + 1);
+            if (!(head & HEAD_ROOT)) {
+                --sp;
+                const float* s = stk + sp * (2 * K + 1);
 #pragma unroll
-            for (int k = 0; k < K; ++k) { a0[k] = s[2 * k]; a1[k] = s[2 * k + 1]; }
-            c = s[2 * K];
+                for (int k = 0; k < K; ++k) { a0[k] = s[2 * k]; a1[k] = s[2 * k + 1]; }
+                c = s[2 * K];
+            }
         }
         // unary value ops attached to this instruction (rounding / onion)
         const int np = head_npost(head);

@@ -13,6 +13,7 @@ enum : int { FOLD_NONE = 0, FOLD_MIN = 1, FOLD_SMOOTH = 2 };
 enum : int { POST_ROUND = 1, POST_ONION = 2 };
 
 constexpr int MAX_DEPTH = 8;
+constexpr int HEAD_ROOT = 1 << 16;   // OPEN/CLOSE of the outermost union: no save/restore of the parent accumulator
 
 __host__ __device__ __forceinline__ int head_op(int h) { return h & 15; }
 __host__ __device__ __forceinline__ int head_frame(int h) { return (h >> 4) & 3; }

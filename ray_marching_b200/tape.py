@@ -4,7 +4,7 @@ The reference evaluates a scene by recursive ``nn.Module`` calls that materialis
 ``(N,H,W,k)`` tensor per torch op (``scene/transformations.py:33-41,67-71,90-94``).  Here the
 tree is walked once and turned into
 
-* ``code``  int32 ``(n_instr, 4)``: ``(head, param_offset/4, ordinal_in_parent, node_id)``
+* ``code``  int32 ``(n_instr, 4)``: ``(head, param_offset/4, ordinal_in_parent, node_id | frame_record)``
 * ``par``   float32 ``(n_par,)``: per-instruction parameter records, 16-byte aligned,
 
 which the per-ray CUDA interpreter (``csrc/rm_eval.cuh``) executes from shared memory.
@@ -46,6 +46,7 @@ FRAME_KEEP, FRAME_WORLD, FRAME_NEW = 0, 1, 2
 FOLD_NONE, FOLD_MIN, FOLD_SMOOTH = 0, 1, 2
 POST_ROUND, POST_ONION = 1, 2
 MAX_POST = 3
+HEAD_ROOT = 1 << 16     # OPEN/CLOSE of the outermost union: no accumulator save/restore
 MAX_DEPTH = 8          # union nesting depth supported by the interpreter's spill stack
 
 _PRIM_OP = {"SDFSphere": OP_SPHERE, "SDFBox": OP_BOX, "SDFPlane": OP_PLANE,
@@ -103,7 +104,8 @@ class Tape:
         self.flops_per_eval = 0
         self.leaf_kinds: List[int] = []
 
-        self._emit(root, frame=-1, fold=FOLD_NONE, ordinal=0, posts=[], depth=0)
+        self._ord = [0]                     # next child ordinal of every open union (root: dummy)
+        self._emit(root, frame=-1, fold=FOLD_NONE, posts=[], depth=0)
 
         self.code = np.asarray(self._code, dtype=np.int32).reshape(-1, 4)
         self.n_instr = self.code.shape[0]
@@ -140,43 +142,57 @@ class Tape:
                 f"more than {MAX_POST} chained rounding/onion ops on one node are not supported")
         return kinds, entries
 
-    def _emit(self, node, frame, fold, ordinal, posts, depth):
+    def _next_ordinal(self) -> int:
+        o = self._ord[-1]
+        self._ord[-1] += 1
+        return o
+
+    def _emit(self, node, frame, fold, posts, depth):
         kind = type(node).__name__
         if kind == "SDFAffineTransformation":
             lvl = 0 if frame < 0 else self._affines[frame].level + 1
             self._affines.append(_Affine(self._slot(node.orientation),
                                          self._slot(node.translation), frame, lvl))
             self.flops_per_eval += AFFINE_FLOPS
-            return self._emit(node.sdf, len(self._affines) - 1, fold, ordinal, posts, depth)
+            return self._emit(node.sdf, len(self._affines) - 1, fold, posts, depth)
         if kind == "SDFRounding":
             self.flops_per_eval += ROUND_FLOPS
-            return self._emit(node.sdf, frame, fold, ordinal,
-                              posts + [(POST_ROUND, node.rounding)], depth)
+            return self._emit(node.sdf, frame, fold, posts + [(POST_ROUND, node.rounding)], depth)
         if kind == "SDFOnion":
             self.flops_per_eval += ONION_FLOPS
-            return self._emit(node.sdf, frame, fold, ordinal,
-                              posts + [(POST_ONION, node.radius)], depth)
+            return self._emit(node.sdf, frame, fold, posts + [(POST_ONION, node.radius)], depth)
         if kind in ("SDFUnion", "SDFSmoothUnion"):
             smooth = kind == "SDFSmoothUnion"
             n = len(node.sdfs)
             if n == 0:
                 raise ValueError(f"{kind} without children")
+            self.flops_per_eval += (5 * n + 1) if smooth else (n - 1)
+            if not smooth and fold == FOLD_MIN and not posts:
+                # a hard union directly inside a hard union: min is associative and the first-index
+                # tie rule is preserved by keeping the order, so the children are folded straight
+                # into the parent's accumulator (no OPEN/CLOSE, no extra nesting level)
+                for child in node.sdfs:
+                    self._emit(child, frame, FOLD_MIN, [], depth)
+                return
             node_id = self.n_nodes
             self.n_nodes += 1
             self.max_depth = max(self.max_depth, depth + 1)
-            self.flops_per_eval += (5 * n + 1) if smooth else (n - 1)
+            ordinal = self._next_ordinal()
+            root = HEAD_ROOT if depth == 0 else 0      # nothing to save / restore around the root union
             if smooth:
                 off4 = self._f4([("neg_theta", self._slot(node.blend_k))])
-                self._code.append([encode_head(OP_OPEN_SMOOTH), off4, 0, node_id])
+                self._code.append([encode_head(OP_OPEN_SMOOTH) | root, off4, 0, node_id])
             else:
-                self._code.append([encode_head(OP_OPEN_MIN), 0, 0, node_id])
+                self._code.append([encode_head(OP_OPEN_MIN) | root, 0, 0, node_id])
             child_fold = FOLD_SMOOTH if smooth else FOLD_MIN
-            for i, child in enumerate(node.sdfs):
-                self._emit(child, frame, child_fold, i, [], depth + 1)
+            self._ord.append(0)
+            for child in node.sdfs:
+                self._emit(child, frame, child_fold, [], depth + 1)
+            self._ord.pop()
             kinds, entries = self._post_record(posts)
             off4 = self._f4(entries) if kinds else 0
             op = OP_CLOSE_SMOOTH if smooth else OP_CLOSE_MIN
-            self._code.append([encode_head(op, 0, fold, kinds), off4, ordinal, node_id])
+            self._code.append([encode_head(op, 0, fold, kinds) | root, off4, ordinal, node_id])
             return
         if kind not in _PRIM_OP:
             raise NotImplementedError(f"cannot lower scene node of type {kind}")
@@ -191,8 +207,11 @@ class Tape:
         else:
             fmode = FRAME_NEW
         self._cur_frame = frame
+        if frame < 0:
+            self._cur_frame_rec = -1
         first = len(self._src) // 4
         if fmode == FRAME_NEW:
+            self._cur_frame_rec = first
             for r in range(3):
                 self._f4([("A", frame * 9 + r * 3 + c) for c in range(3)] + [("b", frame * 3 + r)])
         if op == OP_SPHERE:
@@ -212,7 +231,10 @@ class Tape:
         kinds, entries = self._post_record(posts)
         if kinds:
             self._f4(entries)
-        self._code.append([encode_head(op, fmode, fold, kinds), first, ordinal, 0])
+        # 4th word: float4 offset of the frame record this leaf is evaluated in (-1: world);
+        # lets the reverse sweep of the backward kernel rebuild q without replaying FRAME_KEEP chains
+        self._code.append([encode_head(op, fmode, fold, kinds), first, self._next_ordinal(),
+                           self._cur_frame_rec])
 
     # ------------------------------------------------------------------ lowering recipe
     def _finalise_recipe(self):

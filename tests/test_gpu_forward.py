@@ -133,6 +133,14 @@ def test_shaders_match_reference_fixture(golden, tag, build, mode):
         # colour-wheel lookup: a 1-ulp angle difference may move a pixel to the neighbouring LUT
         # entry; allow 1% of pixels to be one entry off (the LUT is smooth), none further.
         assert (err > 1e-3).mean() < 0.01 and err.max() < 2e-2
+    elif mode in (1, 2, 5):
+        # x^(1/2.33) has unbounded slope at 0: at the arg-min pixel the reference is exactly 0 and
+        # a 1-ulp difference in the global minimum becomes 1e-6^(0.43) = 2.6e-3.  Near zero the
+        # comparison is therefore made before the gamma (x = y^2.33), elsewhere on the pixel.
+        low = np.nan_to_num(want) < 0.05
+        assert err[~low].max(initial=0.0) <= 1e-3, (mode, err[~low].max())
+        pre = np.abs(np.nan_to_num(got) ** 2.33 - np.nan_to_num(want) ** 2.33)
+        assert pre[low].max(initial=0.0) <= 1e-4, (mode, pre[low].max())
     else:
         assert err.max() <= 1e-3, (mode, err.max())
     # headless display buffer (H,W,4), alpha 1, same pixels
@@ -140,7 +148,9 @@ def test_shaders_match_reference_fixture(golden, tag, build, mode):
     assert rgba.shape == (24, 32, 4) and rgba.is_contiguous()
     assert torch.equal(rgba[..., 3], torch.ones_like(rgba[..., 3]))
     e2 = np.abs(np.nan_to_num(rgba[..., :3].cpu().numpy()) - np.nan_to_num(want[0]))
-    assert (e2 > 1e-3).mean() < (0.01 if mode >= 6 else 1e-9)
+    e2 = e2[np.nan_to_num(want[0]) >= 0.05] if mode in (1, 2, 5) else e2
+    assert (e2 > 1e-3).sum() <= (0.01 if mode >= 6 else 0.0) * e2.size
+    assert np.array_equal(np.isnan(rgba[..., :3].cpu().numpy()), np.isnan(want[0]))
 
 
 def test_proximity_is_all_nan_on_converged_scene(golden):

@@ -62,11 +62,12 @@ def test_flops_per_eval_match_survey_table():
 
 def test_tape_structure_and_errors():
     t = T.Tape(S.make_test_scene2())
-    assert t.n_nodes == 2 and t.max_depth == 2 and t.n_leaves == 4
+    assert t.n_nodes == 1 and t.max_depth == 1 and t.n_leaves == 4   # inner hard union is flattened
     assert t.code.dtype == np.int32 and t.code.shape[1] == 4 and t.n_par % 4 == 0
     ops = [h & 15 for h in t.code[:, 0]]
-    assert ops == [T.OP_OPEN_MIN, T.OP_BOX, T.OP_OPEN_MIN, T.OP_SPHERE, T.OP_TORUS, T.OP_LINE,
-                   T.OP_CLOSE_MIN, T.OP_CLOSE_MIN]
+    assert ops == [T.OP_OPEN_MIN, T.OP_BOX, T.OP_SPHERE, T.OP_TORUS, T.OP_LINE, T.OP_CLOSE_MIN]
+    assert list(t.code[1:5, 2]) == [0, 1, 2, 3]            # child ordinals of the merged union
+    assert t.code[0, 0] & T.HEAD_ROOT and t.code[-1, 0] & T.HEAD_ROOT
     # parameter order follows module.parameters(), so optimisers / state_dict carry over
     assert [n for n, _ in S.make_test_scene().named_parameters()][:3] == [
         "blend_k", "sdfs.0.translation", "sdfs.0.orientation"]
@@ -79,7 +80,7 @@ def test_tape_structure_and_errors():
         T.Tape(deep)
     nest = S.SDFSphere(1.0)
     for _ in range(9):
-        nest = S.SDFUnion([nest, S.SDFPlane()])
+        nest = S.SDFSmoothUnion([nest, S.SDFPlane()], 4.0)
     with pytest.raises(NotImplementedError):
         T.Tape(nest)
 
