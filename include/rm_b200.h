@@ -137,6 +137,22 @@ int rm_reduce_init(float* reduce, void* stream);
 int rm_shade_finalize(const float* reduce, uint32_t mode_mask, int64_t n_rays,
                       float* const* image, float* rgba, int32_t display_mode, void* stream);
 
+/* Backward of a scene evaluation (what torch.autograd does through the nn.Module tree of
+ * scene/primitives.py + scene/transformations.py): given d loss / d sdf at n points, writes
+ * d loss / d points [n][3] (may be NULL) and d loss / d par [tape->n_par] (overwritten), with the
+ * reference's sub-gradient conventions.  Supports tapes with at most 16 union nodes. */
+int rm_sdf_vjp(const RmTape* tape, const float* points, const float* grad_sdf, int64_t n_points,
+               float* dpoints, float* dpar, void* stream);
+
+/* Backward of SDFMarcher.forward (rendering/ray_marching.py:72-84), i.e. of the unrolled
+ * `steps`-step graph the reference differentiates: given d loss / d pos_out, writes d loss / d origin,
+ * d loss / d dirs ([n][3] each, may be NULL) and d loss / d par [tape->n_par] (overwritten).
+ * traj_scratch: caller-provided [steps][n][3] floats (the replayed trajectory).  The forward replay
+ * uses IEEE math, i.e. it matches rm_march(..., fast_math = 0). */
+int rm_march_bwd(const RmTape* tape, const float* origin, const float* dirs, const float* grad_pos,
+                 int64_t n_rays, int32_t steps, float* traj_scratch, float* dorigin, float* ddirs,
+                 float* dpar, void* stream);
+
 /* Measurement aid for the FP32 roofline denominator (bench.py): blocks x 256 threads, each issuing
  * iters*128 independent FFMA (256 flop).  Not part of the render path. */
 int rm_probe_ffma(int32_t blocks, int32_t iters, float* sink, void* stream);

@@ -59,6 +59,10 @@ _SIGNATURES = {
     "rm_reduce_init": (C.c_int, [C.c_void_p, C.c_void_p]),
     "rm_shade_finalize": (C.c_int, [C.c_void_p, C.c_uint32, C.c_int64, C.POINTER(C.c_void_p),
                                     C.c_void_p, C.c_int32, C.c_void_p]),
+    "rm_sdf_vjp": (C.c_int, [C.POINTER(RmTape), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
+                             C.c_void_p, C.c_void_p]),
+    "rm_march_bwd": (C.c_int, [C.POINTER(RmTape), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                               C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "rm_probe_ffma": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
 }
 

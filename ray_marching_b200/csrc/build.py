@@ -6,7 +6,7 @@ import subprocess
 import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SOURCES = ["rm_host.cu", "rm_forward.cu", "rm_probe.cu"]
+SOURCES = ["rm_host.cu", "rm_forward.cu", "rm_backward.cu", "rm_probe.cu"]
 LIB = os.path.join(HERE, "librm_b200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

@@ -78,7 +78,10 @@ def march(tape, origin: Tensor, dirs: Tensor, steps: int = 32, fast: bool = Fals
     """``SDFMarcher.forward``: ``p <- f(p) v + p`` repeated ``steps`` times."""
     origin, dirs = torch.broadcast_tensors(origin, dirs)
     _lib.require_cuda(origin, dirs)
-    return _march(tape.code_tensor(origin.device), tape.lowered_params(origin.device), origin, dirs,
+    par = tape.lowered_params(origin.device)
+    if torch.is_grad_enabled() and (par.requires_grad or origin.requires_grad or dirs.requires_grad):
+        fast = False                    # the backward kernel replays the IEEE-math trajectory
+    return _march(tape.code_tensor(origin.device), par, origin, dirs,
                   int(steps), bool(fast), tape.n_nodes, tape.max_depth)
 
 
@@ -217,3 +220,78 @@ def pose_records(orientations: Tensor, translations: Tensor) -> Tensor:
     fwd = torch.stack([2 * (w * y + x * z), 2 * (y * z - w * x), w * w - x * x - y * y + z * z], -1)
     pad = torch.zeros_like(w)[:, None]
     return torch.cat([R, translations, fwd, orientations, pad], dim=-1).contiguous()
+
+
+# ------------------------------------------------------------------------------ backward ops
+@torch.library.custom_op("rm_b200::sdf_vjp", mutates_args=())
+def _sdf_vjp(code: Tensor, par: Tensor, points: Tensor, grad: Tensor, n_nodes: int,
+             max_depth: int) -> Tuple[Tensor, Tensor]:
+    dev = _lib.require_cuda(par, points, grad)
+    pts = _flat3(points)
+    g = grad.reshape(-1).contiguous()
+    dpts = torch.empty_like(pts)
+    dpar = torch.empty_like(par)
+    tape = _tape_struct(code, par, n_nodes, max_depth)
+    check(lib().rm_sdf_vjp(C.byref(tape), ptr(pts), ptr(g), pts.shape[0], ptr(dpts), ptr(dpar),
+                           stream_ptr(dev)), "rm_sdf_vjp")
+    return dpar, dpts.reshape(points.shape)
+
+
+@_sdf_vjp.register_fake
+def _(code, par, points, grad, n_nodes, max_depth):
+    return torch.empty_like(par), torch.empty_like(points)
+
+
+def _sdf_eval_setup(ctx, inputs, output):
+    code, par, points, n_nodes, max_depth = inputs
+    ctx.save_for_backward(code, par, points)
+    ctx.meta = (n_nodes, max_depth)
+
+
+def _sdf_eval_backward(ctx, grad):
+    code, par, points = ctx.saved_tensors
+    dpar, dpts = _sdf_vjp(code, par, points, grad.contiguous(), *ctx.meta)
+    return None, dpar, dpts, None, None
+
+
+_sdf_eval.register_autograd(_sdf_eval_backward, setup_context=_sdf_eval_setup)
+
+
+@torch.library.custom_op("rm_b200::march_bwd", mutates_args=())
+def _march_bwd(code: Tensor, par: Tensor, origin: Tensor, dirs: Tensor, grad_pos: Tensor,
+               steps: int, n_nodes: int, max_depth: int) -> Tuple[Tensor, Tensor, Tensor]:
+    dev = _lib.require_cuda(par, origin, dirs, grad_pos)
+    o, v, g = _flat3(origin), _flat3(dirs), _flat3(grad_pos)
+    n = o.shape[0]
+    traj = torch.empty(max(steps, 1) * n * 3, device=dev, dtype=torch.float32)
+    do, dv = torch.empty_like(o), torch.empty_like(v)
+    dpar = torch.empty_like(par)
+    tape = _tape_struct(code, par, n_nodes, max_depth)
+    check(lib().rm_march_bwd(C.byref(tape), ptr(o), ptr(v), ptr(g), n, steps, ptr(traj), ptr(do),
+                             ptr(dv), ptr(dpar), stream_ptr(dev)), "rm_march_bwd")
+    return dpar, do.reshape(origin.shape), dv.reshape(dirs.shape)
+
+
+@_march_bwd.register_fake
+def _(code, par, origin, dirs, grad_pos, steps, n_nodes, max_depth):
+    return torch.empty_like(par), torch.empty_like(origin), torch.empty_like(dirs)
+
+
+def _march_setup(ctx, inputs, output):
+    code, par, origin, dirs, steps, fast, n_nodes, max_depth = inputs
+    if fast:
+        raise _lib.RmError("march(fast=True) is not differentiable; autograd uses the IEEE-math march")
+    ctx.save_for_backward(code, par, origin, dirs)
+    ctx.meta = (steps, n_nodes, max_depth)
+
+
+def _march_backward(ctx, grad):
+    code, par, origin, dirs = ctx.saved_tensors
+    steps, n_nodes, max_depth = ctx.meta
+    dpar, do, dv = _march_bwd(code, par, origin, dirs, grad.contiguous(), steps, n_nodes, max_depth)
+    return None, dpar, do, dv, None, None, None, None
+
+
+_march.register_autograd(_march_backward, setup_context=_march_setup)
+
+BACKWARD_READY = True
