@@ -154,9 +154,10 @@ using namespace rm;
 extern "C" int rm_sdf_vjp(const RmTape* tape, const float* points, const float* grad_sdf, int64_t n,
                           float* dpoints, float* dpar, void* stream) {
     if (int s = check_backward_tape(tape)) return s;
-    if (n < 0 || dpar == nullptr || (n > 0 && (points == nullptr || grad_sdf == nullptr)))
+    if (n < 0 || (dpar == nullptr && tape->n_par > 0) || (n > 0 && (points == nullptr || grad_sdf == nullptr)))
         return fail(RM_ERR_INVALID, "rm_sdf_vjp: null buffer or negative count");
-    RM_CUDA(cudaMemsetAsync(dpar, 0, (size_t)tape->n_par * sizeof(float), (cudaStream_t)stream));
+    if (tape->n_par > 0)
+        RM_CUDA(cudaMemsetAsync(dpar, 0, (size_t)tape->n_par * sizeof(float), (cudaStream_t)stream));
     if (n == 0) return RM_OK;
     const size_t sm = tape_smem_bytes(tape) + (size_t)tape->n_par * sizeof(float);
     if (int s = prepare_smem(sdf_vjp_kernel, sm)) return s;
@@ -170,10 +171,11 @@ extern "C" int rm_march_bwd(const RmTape* tape, const float* origin, const float
                             const float* grad_pos, int64_t n, int32_t steps, float* traj_scratch,
                             float* dorigin, float* ddirs, float* dpar, void* stream) {
     if (int s = check_backward_tape(tape)) return s;
-    if (n < 0 || steps < 0 || dpar == nullptr ||
+    if (n < 0 || steps < 0 || (dpar == nullptr && tape->n_par > 0) ||
         (n > 0 && (!origin || !dirs || !grad_pos || (steps > 0 && !traj_scratch))))
         return fail(RM_ERR_INVALID, "rm_march_bwd: null buffer or negative count");
-    RM_CUDA(cudaMemsetAsync(dpar, 0, (size_t)tape->n_par * sizeof(float), (cudaStream_t)stream));
+    if (tape->n_par > 0)
+        RM_CUDA(cudaMemsetAsync(dpar, 0, (size_t)tape->n_par * sizeof(float), (cudaStream_t)stream));
     if (n == 0) return RM_OK;
     const size_t sm = tape_smem_bytes(tape) + (size_t)tape->n_par * sizeof(float);
     if (int s = prepare_smem(march_bwd_kernel, sm)) return s;
