@@ -158,7 +158,7 @@ def measure_fp32_peak(device) -> dict:
 # ---------------------------------------------------------------------------- GPU arm
 def run_gpu(args):
     import torch.distributed as dist
-    from ray_marching_b200 import RenderLoop, ops
+    from ray_marching_b200 import RenderLoop, ops, parallel
     from ray_marching_b200.tape import tape_of
 
     rank = int(os.environ.get("RANK", "0"))
@@ -193,13 +193,8 @@ def run_gpu(args):
                                  finalize=False, out=res_holder.get("res"))
         res_holder["res"] = out
         if needs_reduce:
-            if world > 1:      # global min/max over the camera batch (shader.py:35-36,84)
-                r = out.reduce
-                mins, maxs = r[[0, 2]].contiguous(), r[[1, 3, 4, 5, 6, 7]].contiguous()
-                dist.all_reduce(mins, op=dist.ReduceOp.MIN)
-                dist.all_reduce(maxs, op=dist.ReduceOp.MAX)
-                r[[0, 2]] = mins
-                r[[1, 3, 4, 5, 6, 7]] = maxs
+            # global min/max over the whole camera batch (shader.py:35-36,84): NCCL MIN/MAX of 8 floats
+            parallel.allreduce_shader_range(out.reduce)
             mask = 0
             for m in modes:
                 mask |= 1 << m
@@ -343,7 +338,91 @@ def measure_e2e(loop, wl, q, t, dev, args, world, barrier):
 
 
 def make_backward_step(loop, scene, q, t, dev, world):
-    raise SystemExit("workload c4 (fwd+bwd) is wired in once the backward kernels land")
+    """c4: one Adam step of inverse rendering -- forward (camera, march, stencil, lambertian + raw
+    depth), MSE loss against a target rendered from perturbed parameters, backward through the
+    replay kernels, all-reduce of the flat gradient over ranks (one view per rank), Adam update."""
+    import torch.distributed as dist
+    from ray_marching_b200 import ops, parallel
+    from ray_marching_b200.tape import tape_of
+    tape = tape_of(loop.scene)
+    params = list(scene.parameters())
+    q = q.clone().requires_grad_(True)
+    t = t.clone().requires_grad_(True)
+
+    def gbuf():
+        px, frames, pos0, dirs = loop.camera(q, t)
+        pos = loop.marcher(pos0, dirs, STEPS)
+        n, lap = loop.normals(pos)
+        lam = (-(dirs * n).sum(-1, keepdim=True)).clamp(0, 1)
+        depth = (pos - px).norm(dim=-1, keepdim=True)
+        return lam, depth, (pos0, dirs)
+
+    gen = torch.Generator().manual_seed(1)
+    saved = [p.detach().clone() for p in params]
+    with torch.no_grad():
+        for p in params:
+            p.add_(0.05 * torch.randn(p.shape, generator=gen).to(dev))
+    lam_t, depth_t, _ = [x.detach() if isinstance(x, torch.Tensor) else x for x in gbuf()]
+    with torch.no_grad():
+        for p, s0 in zip(params, saved):
+            p.copy_(s0)
+    opt = torch.optim.Adam(params + [q, t], lr=1e-2, foreach=True)
+    state = {}
+
+    def step():
+        opt.zero_grad(set_to_none=True)
+        lam, depth, rays = gbuf()
+        loss = ((lam - lam_t) ** 2).mean() + ((depth - depth_t) ** 2).mean()
+        loss.backward()
+        if world > 1:          # one NCCL SUM over the flat gradient buffer (scene params + q, t)
+            parallel.allreduce_gradients(params + [q, t], average=True)
+        opt.step()
+        state["loss"], state["rays"] = loss, rays
+        return loss
+
+    rays_n = loop.px_width * loop.px_height
+    F = tape.flops_per_eval
+    fwd_flops = 63 + STEPS * (F + 6) + F + 4 * F + 45 + 8 + 10
+
+    def roofline(ms_step, peak):
+        # dominant kernel: march_bwd_kernel, timed alone on the saved rays of the last step
+        pos0, dirs = [x.detach() for x in state["rays"]]
+        par = tape.lowered_params(dev).detach()
+        gp = torch.randn_like(pos0)
+        code = tape.code_tensor(dev)
+        ks = []
+        for _ in range(5):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            ops._march_bwd(code, par, pos0, dirs, gp, STEPS, tape.n_nodes, tape.max_depth)
+            e1.record()
+            e1.synchronize()
+            ks.append(e0.elapsed_time(e1))
+        kms = sum(ks[1:]) / len(ks[1:])
+        alg = 2.0 * STEPS * (F + 6) * rays_n            # backward = 2x the differentiated forward region
+        ach = alg / (kms * 1e-3) / 1e12
+        return {"bound": "fp32", "kernel": "march_bwd_kernel", "achieved": ach, "peak": peak["tflops"],
+                "unit": "TFLOP/s", "frac": ach / peak["tflops"], "traffic": None, "kernel_ms": kms,
+                "algorithmic_flops_per_ray": 2.0 * STEPS * (F + 6),
+                "step_algorithmic_tflops": 3.0 * fwd_flops * rays_n / (ms_step * 1e-3) / 1e12,
+                "peak_source": "measured: FFMA microbenchmark (rm_probe_ffma) on this GPU; "
+                               "nominal 74.5 TFLOP/s at 1965 MHz"}
+
+    def e2e(args, barrier):
+        host = torch.empty(1).pin_memory()
+        for _ in range(2):
+            host.copy_(step().detach().reshape(1), non_blocking=True)
+            torch.cuda.synchronize()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            host.copy_(step().detach().reshape(1), non_blocking=True)      # loss read back every step
+            torch.cuda.synchronize()
+        barrier()
+        return {"ms_total": (time.perf_counter() - t0) * 1e3, "h2d": 0, "d2h": 4}
+
+    # my kernels per step: march, sdf_eval x2 (stencil offsets, centre), sdf_vjp x2, march_bwd
+    return step, {"launches": 6, "roofline": roofline, "e2e": e2e}
 
 
 # ---------------------------------------------------------------------------- CPU arm
