@@ -350,12 +350,10 @@ def make_backward_step(loop, scene, q, t, dev, world):
     t = t.clone().requires_grad_(True)
 
     def gbuf():
-        px, frames, pos0, dirs = loop.camera(q, t)
-        pos = loop.marcher(pos0, dirs, STEPS)
-        n, lap = loop.normals(pos)
-        lam = (-(dirs * n).sum(-1, keepdim=True)).clamp(0, 1)
-        depth = (pos - px).norm(dim=-1, keepdim=True)
-        return lam, depth, (pos0, dirs)
+        gb = loop.gbuffer(q, t, STEPS)          # fused forward kernel; backward = rm_render_bwd
+        lam = (-(gb["dirs"] * gb["normals"]).sum(-1, keepdim=True)).clamp(0, 1)
+        depth = (gb["pos"] - gb["origin"]).norm(dim=-1, keepdim=True)
+        return lam, depth, None
 
     gen = torch.Generator().manual_seed(1)
     saved = [p.detach().clone() for p in params]
@@ -385,25 +383,29 @@ def make_backward_step(loop, scene, q, t, dev, world):
     fwd_flops = 63 + STEPS * (F + 6) + F + 4 * F + 45 + 8 + 10
 
     def roofline(ms_step, peak):
-        # dominant kernel: march_bwd_kernel, timed alone on the saved rays of the last step
-        pos0, dirs = [x.detach() for x in state["rays"]]
+        # dominant kernel: render_bwd_kernel, timed alone with the upstream gradients of this loss
         par = tape.lowered_params(dev).detach()
-        gp = torch.randn_like(pos0)
+        poses = ops.pose_records(q.detach(), t.detach())
+        cam = loop.camera.struct()
+        g3 = torch.randn(rays_n, 3, device=dev)
         code = tape.code_tensor(dev)
         ks = []
         for _ in range(5):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            ops._march_bwd(code, par, pos0, dirs, gp, STEPS, tape.n_nodes, tape.max_depth)
+            ops._render_bwd(code, par, poses, cam.n_views, cam.width, cam.height, cam.focal_length,
+                            cam.sensor_width, cam.sensor_height, STEPS, EPS, g3, g3, g3, None, g3, None,
+                            tape.n_nodes, tape.max_depth)
             e1.record()
             e1.synchronize()
             ks.append(e0.elapsed_time(e1))
         kms = sum(ks[1:]) / len(ks[1:])
-        alg = 2.0 * STEPS * (F + 6) * rays_n            # backward = 2x the differentiated forward region
+        bwd_flops = 2.0 * (63 + STEPS * (F + 6) + F + 4 * F + 45)   # 2x the differentiated forward region
+        alg = bwd_flops * rays_n
         ach = alg / (kms * 1e-3) / 1e12
-        return {"bound": "fp32", "kernel": "march_bwd_kernel", "achieved": ach, "peak": peak["tflops"],
+        return {"bound": "fp32", "kernel": "render_bwd_kernel", "achieved": ach, "peak": peak["tflops"],
                 "unit": "TFLOP/s", "frac": ach / peak["tflops"], "traffic": None, "kernel_ms": kms,
-                "algorithmic_flops_per_ray": 2.0 * STEPS * (F + 6),
+                "algorithmic_flops_per_ray": bwd_flops,
                 "step_algorithmic_tflops": 3.0 * fwd_flops * rays_n / (ms_step * 1e-3) / 1e12,
                 "peak_source": "measured: FFMA microbenchmark (rm_probe_ffma) on this GPU; "
                                "nominal 74.5 TFLOP/s at 1965 MHz"}
@@ -421,8 +423,8 @@ def make_backward_step(loop, scene, q, t, dev, world):
         barrier()
         return {"ms_total": (time.perf_counter() - t0) * 1e3, "h2d": 0, "d2h": 4}
 
-    # my kernels per step: march, sdf_eval x2 (stencil offsets, centre), sdf_vjp x2, march_bwd
-    return step, {"launches": 6, "roofline": roofline, "e2e": e2e}
+    # my kernels per step: render_kernel (G-buffer forward), render_bwd_kernel
+    return step, {"launches": 2, "roofline": roofline, "e2e": e2e}
 
 
 # ---------------------------------------------------------------------------- CPU arm

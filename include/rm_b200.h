@@ -5,7 +5,7 @@
  * nn.Module surface.  Each entry point below names the reference
  * interface whose *body* it replaces.  Conventions:
  *   - plain C, no C++/torch types; every pointer is a DEVICE pointer unless the name ends
- *     in _host; the caller allocates and owns every buffer;
+ *     in _host (read synchronously during the call); the caller allocates and owns every buffer;
  *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream);
  *   - returns 0 on success, a negative RmStatus otherwise; never throws; the message of the
  *     last failure on the calling thread is available from rm_last_error();
@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define RM_B200_ABI_VERSION 1
+#define RM_B200_ABI_VERSION 2
 
 typedef enum RmStatus {
     RM_OK = 0,
@@ -33,12 +33,15 @@ typedef enum RmStatus {
 /* Lowered scene (ray_marching_b200/tape.py).  Replaces the recursive nn.Module tree walk of
  * scene/primitives.py:11-102 and scene/transformations.py:33-132. */
 typedef struct RmTape {
-    const int32_t* code;   /* [n_instr][4]: head, param offset (float4 units), ordinal, node id */
-    const float*   par;    /* [n_par] parameter records, 16-byte aligned                       */
-    int32_t n_instr;
-    int32_t n_par;         /* multiple of 4 */
-    int32_t max_depth;     /* union nesting depth (<= 8) */
-    int32_t n_nodes;       /* number of union nodes */
+    const int32_t* code_host; /* HOST [n_instr][2] instruction words (static per scene structure):
+                                 word0 = op[0:4] frame[4] fold[5:7] root[7] npost[8:10] posts[10:16]
+                                 ordinal[16:32]; word1 = parameter offset in float4 units [0:16],
+                                 union node id [16:32].  Copied into the launch parameters.        */
+    const float*   par;       /* DEVICE [n_par] parameter records, 16-byte aligned (live values)  */
+    int32_t n_instr;          /* <= 1024 */
+    int32_t n_par;            /* multiple of 4 */
+    int32_t max_depth;        /* union nesting depth (<= 8) */
+    int32_t n_nodes;          /* number of union nodes */
 } RmTape;
 
 /* Pinhole camera intrinsics: PinholeCamera.__init__, rendering/ray_marching.py:10-55. */
@@ -51,11 +54,11 @@ typedef struct RmCamera {
     float   sensor_height;
 } RmCamera;
 
-/* Per-view pose record, 20 floats: R[9] row-major (rotation polynomial of the camera quaternion,
- * quaternion.py:55-72), t[3], fwd[3] = third column of QuaternionToSO3(q) (quaternion.py:114-124,
- * used by the vignette shader, shader.py:62-66), q[4] (camera quaternion, spin shader
- * shader.py:157-171), 1 pad. */
-#define RM_POSE_STRIDE 20
+/* Per-view pose record, 8 floats (32-byte aligned rows): camera quaternion q[4] scalar first
+ * (w,x,y,z), translation t[3], 1 pad -- the (orientation, translation) pair RenderLoop.forward
+ * receives (control.py:231-236).  The kernels expand it to the rotation polynomial of
+ * quaternion.py:55-72 and the forward axis of QuaternionToSO3 (quaternion.py:114-124). */
+#define RM_POSE_STRIDE 8
 
 /* Shader mode bits; bit m = mode index m of Shader.forward (rendering/shader.py:204-209). */
 enum {
@@ -147,11 +150,35 @@ int rm_sdf_vjp(const RmTape* tape, const float* points, const float* grad_sdf, i
 /* Backward of SDFMarcher.forward (rendering/ray_marching.py:72-84), i.e. of the unrolled
  * `steps`-step graph the reference differentiates: given d loss / d pos_out, writes d loss / d origin,
  * d loss / d dirs ([n][3] each, may be NULL) and d loss / d par [tape->n_par] (overwritten).
- * traj_scratch: caller-provided [steps][n][3] floats (the replayed trajectory).  The forward replay
- * uses IEEE math, i.e. it matches rm_march(..., fast_math = 0). */
+ * traj_scratch: caller-provided, rm_bwd_scratch_floats(n_rays, steps) floats (the replayed
+ * trajectory).  The forward replay uses IEEE math, i.e. it matches rm_march(..., fast_math = 0). */
 int rm_march_bwd(const RmTape* tape, const float* origin, const float* dirs, const float* grad_pos,
                  int64_t n_rays, int32_t steps, float* traj_scratch, float* dorigin, float* ddirs,
                  float* dpar, void* stream);
+
+/* Upstream gradients of the G-buffer planes for rm_render_bwd, indexed like RmRenderOut (local ray
+ * index); any pointer may be NULL (= zero gradient). */
+typedef struct RmRenderGrads {
+    const float* origin;     /* [n][3] d loss / d ray start        */
+    const float* dirs;       /* [n][3] d loss / d ray direction    */
+    const float* pos;        /* [n][3] d loss / d marched position */
+    const float* sdf;        /* [n]    d loss / d f(pos)           */
+    const float* normals;    /* [n][3] d loss / d normal           */
+    const float* laplacian;  /* [n]    d loss / d laplacian        */
+} RmRenderGrads;
+
+/* Floats of trajectory scratch rm_march_bwd / rm_render_bwd need for `n_rays` rays and `steps`
+ * steps (bounded: the kernels index it by thread slot, not by ray). */
+int64_t rm_bwd_scratch_floats(int64_t n_rays, int32_t steps);
+
+/* Backward of the G-buffer pipeline of RenderLoop.forward (control.py:239-245: camera -> march ->
+ * f(p) -> SDFNormals), i.e. what torch.autograd does through the reference's unrolled graph, in one
+ * kernel.  Uses args->ray_begin, n_rays, steps, normals_eps (bounces must be 0).  Writes
+ * d loss / d par [tape->n_par] and d loss / d poses [n_views][RM_POSE_STRIDE] (dq[4], dt[3], 0),
+ * both overwritten.  The forward that produced the planes must have used fast_math = 0. */
+int rm_render_bwd(const RmTape* tape, const RmCamera* cam, const float* poses,
+                  const RmRenderArgs* args, const RmRenderGrads* grads, float* traj_scratch,
+                  float* dpar, float* dposes, void* stream);
 
 /* Measurement aid for the FP32 roofline denominator (bench.py): blocks x 256 threads, each issuing
  * iters*128 independent FFMA (256 flop).  Not part of the render path. */

@@ -14,13 +14,13 @@ import torch
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "librm_b200.so")
 
-POSE_STRIDE = 20
+POSE_STRIDE = 8
 REDUCE_FLOATS = 8
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 
 class RmTape(C.Structure):
-    _fields_ = [("code", C.c_void_p), ("par", C.c_void_p), ("n_instr", C.c_int32),
+    _fields_ = [("code_host", C.c_void_p), ("par", C.c_void_p), ("n_instr", C.c_int32),
                 ("n_par", C.c_int32), ("max_depth", C.c_int32), ("n_nodes", C.c_int32)]
 
 
@@ -44,6 +44,11 @@ class RmRenderArgs(C.Structure):
                 ("fast_math", C.c_int32), ("cmap", C.c_void_p)]
 
 
+class RmRenderGrads(C.Structure):
+    _fields_ = [("origin", C.c_void_p), ("dirs", C.c_void_p), ("pos", C.c_void_p),
+                ("sdf", C.c_void_p), ("normals", C.c_void_p), ("laplacian", C.c_void_p)]
+
+
 _SIGNATURES = {
     "rm_abi_version": (C.c_int, []),
     "rm_last_error": (C.c_char_p, []),
@@ -63,6 +68,10 @@ _SIGNATURES = {
                              C.c_void_p, C.c_void_p]),
     "rm_march_bwd": (C.c_int, [C.POINTER(RmTape), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "rm_bwd_scratch_floats": (C.c_int64, [C.c_int64, C.c_int32]),
+    "rm_render_bwd": (C.c_int, [C.POINTER(RmTape), C.POINTER(RmCamera), C.c_void_p,
+                                C.POINTER(RmRenderArgs), C.POINTER(RmRenderGrads), C.c_void_p,
+                                C.c_void_p, C.c_void_p, C.c_void_p]),
     "rm_probe_ffma": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
 }
 

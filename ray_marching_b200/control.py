@@ -86,10 +86,21 @@ class RenderLoop(nn.Module):
             res = self.render_planes(orientations, translations, modes=(m,), degree=degree,
                                      marching_steps=marching_steps)
             return res.images[m].reshape(N, H, W, -1).expand(-1, H, W, 3)
-        (pixel_pos, pixel_frames, ray_pos, ray_dirs) = self.camera(orientations, translations)
-        marched = self.marcher(ray_pos, ray_dirs, marching_steps)
-        dists = self.scene(marched)
-        (n, lap) = self.normals(marched)
-        image = self.shader(pixel_pos, orientations, pixel_frames, ray_dirs, marched, n, lap, dists,
-                            mode=mode, degree=degree)
+        # autograd recording: fused differentiable G-buffer (one forward + one backward kernel),
+        # then the reference's per-pixel shader algebra on the planes
+        gb = self.gbuffer(orientations, translations, marching_steps)
+        pixel_frames = self.camera.quaternion_to_so3(orientations[:, None, None, :])
+        image = self.shader(gb["origin"], orientations, pixel_frames, gb["dirs"], gb["pos"], gb["normals"],
+                            gb["laplacian"], gb["sdf"], mode=mode, degree=degree)
         return image.expand(-1, H, W, 3)
+
+    def gbuffer(self, orientations: Tensor, translations: Tensor, marching_steps: int = 32):
+        """Differentiable G-buffer of control.py:239-245 as ``(N,H,W,c)`` tensors: ``origin`` (= pixel
+        positions), ``dirs``, ``pos``, ``sdf``, ``normals``, ``laplacian``."""
+        N, H, W = self.camera.num_cameras, self.px_height, self.px_width
+        o, v, p, f, n, lap = ops.render_gbuffer(tape_of(self.scene), self.camera.struct(), orientations,
+                                                translations, marching_steps, self.normals.normals_eps)
+        r3 = lambda x: x.reshape(N, H, W, 3)
+        r1 = lambda x: x.reshape(N, H, W, 1)
+        return {"origin": r3(o), "dirs": r3(v), "pos": r3(p), "sdf": r1(f), "normals": r3(n),
+                "laplacian": r1(lap)}

@@ -5,50 +5,6 @@ namespace rm {
 
 inline unsigned grid_for(int64_t n) { return (unsigned)((n + (int64_t)BLOCK * K - 1) / ((int64_t)BLOCK * K)); }
 
-inline int make_cam(const RmCamera* c, CamParams* out) {
-    if (c == nullptr || c->n_views <= 0 || c->width <= 0 || c->height <= 0)
-        return fail(RM_ERR_INVALID, "camera is null or has a non-positive size");
-    out->n_views = c->n_views; out->width = c->width; out->height = c->height;
-    out->focal = c->focal_length;
-    out->half_w = c->sensor_width / 2;
-    out->neg_half_h = -c->sensor_height / 2;
-    out->inv_w = 1.0f / (float)c->width;
-    out->inv_h = 1.0f / (float)c->height;
-    return RM_OK;
-}
-
-// SDFNormals.__init__ (ray_marching.py:94-113), float64 on the host, rounded once to float32.
-inline void make_stencil(float eps, Stencil* st) {
-    const double s = sqrt(0.5);
-    const double raw[4][3] = {{1, 0, -s}, {-1, 0, -s}, {0, 1, s}, {0, -1, s}};
-    double off[4][3];
-    for (int j = 0; j < 4; ++j) {
-        const double len = sqrt(raw[j][0] * raw[j][0] + raw[j][1] * raw[j][1] + raw[j][2] * raw[j][2]);
-        for (int c = 0; c < 3; ++c) {
-            off[j][c] = raw[j][c] / len * (double)eps;
-            st->off[j][c] = (float)off[j][c];
-        }
-    }
-    double A[3][3], inv[3][3];
-    for (int r = 0; r < 3; ++r)
-        for (int c = 0; c < 3; ++c) A[r][c] = off[r + 1][c] - off[0][c];
-    const double det = A[0][0] * (A[1][1] * A[2][2] - A[1][2] * A[2][1]) -
-                       A[0][1] * (A[1][0] * A[2][2] - A[1][2] * A[2][0]) +
-                       A[0][2] * (A[1][0] * A[2][1] - A[1][1] * A[2][0]);
-    inv[0][0] = (A[1][1] * A[2][2] - A[1][2] * A[2][1]) / det;
-    inv[0][1] = (A[0][2] * A[2][1] - A[0][1] * A[2][2]) / det;
-    inv[0][2] = (A[0][1] * A[1][2] - A[0][2] * A[1][1]) / det;
-    inv[1][0] = (A[1][2] * A[2][0] - A[1][0] * A[2][2]) / det;
-    inv[1][1] = (A[0][0] * A[2][2] - A[0][2] * A[2][0]) / det;
-    inv[1][2] = (A[0][2] * A[1][0] - A[0][0] * A[1][2]) / det;
-    inv[2][0] = (A[1][0] * A[2][1] - A[1][1] * A[2][0]) / det;
-    inv[2][1] = (A[0][1] * A[2][0] - A[0][0] * A[2][1]) / det;
-    inv[2][2] = (A[0][0] * A[1][1] - A[0][1] * A[1][0]) / det;
-    for (int r = 0; r < 3; ++r)
-        for (int c = 0; c < 3; ++c) st->inv[r * 3 + c] = (float)inv[r][c];
-    st->lap_scale = (float)(6.0 / ((double)eps * (double)eps));
-}
-
 }  // namespace rm
 
 using namespace rm;
@@ -59,9 +15,11 @@ extern "C" int rm_sdf_eval(const RmTape* tape, const float* points, int64_t n, f
         return fail(RM_ERR_INVALID, "rm_sdf_eval: null buffer or negative count");
     if (n == 0) return RM_OK;
     const size_t sm = tape_smem_bytes(tape);
-    if (int s = prepare_smem(sdf_eval_kernel, sm)) return s;
-    sdf_eval_kernel<<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
-        tape->code, tape->par, tape->n_instr, tape->n_par, points, n, out);
+    RM_WITH_CODE(tape, {
+        if (int s = prepare_smem(sdf_eval_kernel<CAP>, sm)) return s;
+        sdf_eval_kernel<CAP><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
+            code, tape->par, tape->n_instr, tape->n_par, points, n, out);
+    });
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }
@@ -86,15 +44,17 @@ extern "C" int rm_march(const RmTape* tape, const float* origin, const float* di
         return fail(RM_ERR_INVALID, "rm_march: null buffer or negative count");
     if (n == 0) return RM_OK;
     const size_t sm = tape_smem_bytes(tape);
-    if (fast_math) {
-        if (int s = prepare_smem(march_kernel<true>, sm)) return s;
-        march_kernel<true><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
-            tape->code, tape->par, tape->n_instr, tape->n_par, origin, dirs, n, steps, pos_out);
-    } else {
-        if (int s = prepare_smem(march_kernel<false>, sm)) return s;
-        march_kernel<false><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
-            tape->code, tape->par, tape->n_instr, tape->n_par, origin, dirs, n, steps, pos_out);
-    }
+    RM_WITH_CODE(tape, {
+        if (fast_math) {
+            if (int s = prepare_smem(march_kernel<true, CAP>, sm)) return s;
+            march_kernel<true, CAP><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
+                code, tape->par, tape->n_instr, tape->n_par, origin, dirs, n, steps, pos_out);
+        } else {
+            if (int s = prepare_smem(march_kernel<false, CAP>, sm)) return s;
+            march_kernel<false, CAP><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
+                code, tape->par, tape->n_instr, tape->n_par, origin, dirs, n, steps, pos_out);
+        }
+    });
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }
@@ -108,9 +68,11 @@ extern "C" int rm_normals(const RmTape* tape, const float* points, int64_t n, fl
     Stencil st;
     make_stencil(eps, &st);
     const size_t sm = tape_smem_bytes(tape);
-    if (int s = prepare_smem(normals_kernel, sm)) return s;
-    normals_kernel<<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
-        tape->code, tape->par, tape->n_instr, tape->n_par, st, points, n, normals, lap);
+    RM_WITH_CODE(tape, {
+        if (int s = prepare_smem(normals_kernel<CAP>, sm)) return s;
+        normals_kernel<CAP><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
+            code, tape->par, tape->n_instr, tape->n_par, st, points, n, normals, lap);
+    });
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }
@@ -152,15 +114,17 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
     P.display_mode = a->display_mode; P.degree = a->degree; P.early_exit = a->early_exit;
     P.cmap = a->cmap; P.out = *out;
     const size_t sm = tape_smem_bytes(tape);
-    if (a->fast_math) {
-        if (int s = prepare_smem(render_kernel<true>, sm)) return s;
-        render_kernel<true><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
-            tape->code, tape->par, tape->n_instr, tape->n_par, poses, P);
-    } else {
-        if (int s = prepare_smem(render_kernel<false>, sm)) return s;
-        render_kernel<false><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
-            tape->code, tape->par, tape->n_instr, tape->n_par, poses, P);
-    }
+    RM_WITH_CODE(tape, {
+        if (a->fast_math) {
+            if (int s = prepare_smem(render_kernel<true, CAP>, sm)) return s;
+            render_kernel<true, CAP><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+                code, tape->par, tape->n_instr, tape->n_par, poses, P);
+        } else {
+            if (int s = prepare_smem(render_kernel<false, CAP>, sm)) return s;
+            render_kernel<false, CAP><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+                code, tape->par, tape->n_instr, tape->n_par, poses, P);
+        }
+    });
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }

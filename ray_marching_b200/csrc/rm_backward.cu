@@ -7,13 +7,20 @@
 //                       g_i = lambda . v,   d par += g_i df/dpar(p_i),   d v += f(p_i) lambda,
 //                       lambda += g_i grad f(p_i)
 //                   which is exactly the chain rule of the unrolled graph.
+//   rm_render_bwd : VJP of the whole G-buffer pipeline of RenderLoop.forward (control.py:239-245):
+//                   camera rays -> march -> f(p) -> tetrahedral stencil, in ONE kernel: rays are
+//                   regenerated from the pixel index, the march is replayed, the stencil and the
+//                   march are reversed, and the adjoints of the ray origin / direction are
+//                   contracted with d(R(q) b + t)/d(q, t) into camera-pose gradients.
 //
 // Per-parameter accumulation: warp butterfly -> shared-memory atomics per block -> one global
-// atomicAdd per parameter per block (rm_sweep.cuh).
+// atomicAdd per parameter per block (rm_sweep.cuh).  Camera gradients: per-thread registers over
+// the grid-stride loop -> warp shuffle reduction -> one global atomicAdd per warp and component.
 #include <cuda_runtime.h>
 
 #include "../../include/rm_b200.h"
 #include "rm_host.h"
+#include "rm_shade.cuh"
 #include "rm_sweep.cuh"
 
 namespace rm {
@@ -25,11 +32,15 @@ __device__ __forceinline__ void load3k(const float* base, int64_t first, int64_t
                                        float (&y)[KB], float (&z)[KB]) {
 #pragma unroll
     for (int k = 0; k < KB; ++k) {
-        const bool ok = first + k < n;
+        const bool ok = base != nullptr && first + k < n;
         x[k] = ok ? __ldg(base + (first + k) * 3 + 0) : 0.f;
         y[k] = ok ? __ldg(base + (first + k) * 3 + 1) : 0.f;
         z[k] = ok ? __ldg(base + (first + k) * 3 + 2) : 0.f;
     }
+}
+__device__ __forceinline__ void load1k(const float* base, int64_t first, int64_t n, float (&x)[KB]) {
+#pragma unroll
+    for (int k = 0; k < KB; ++k) x[k] = (base != nullptr && first + k < n) ? __ldg(base + first + k) : 0.f;
 }
 __device__ __forceinline__ void store3k(float* base, int64_t first, int64_t n, const float (&x)[KB],
                                         const float (&y)[KB], const float (&z)[KB]) {
@@ -43,9 +54,29 @@ __device__ __forceinline__ void store3k(float* base, int64_t first, int64_t n, c
         }
 }
 
-// Shared memory: [tape code | tape par | accumulators (n_par floats)]
-__device__ __forceinline__ float* stage_accumulators(unsigned char* smem, int n_instr, int n_par) {
-    float* sacc = reinterpret_cast<float*>(smem + (size_t)n_instr * sizeof(int4) + (size_t)n_par * sizeof(float));
+// Trajectory scratch, indexed by THREAD SLOT (not by ray): a thread reuses its slots on every
+// iteration of its grid-stride loop, so the footprint is steps x grid x BLOCK_B x KB x 12 bytes
+// (<= ~116 MB, L2-sized) however many rays there are.  A thread writes 24 contiguous bytes per
+// step, a warp 768 contiguous bytes.
+__device__ __forceinline__ float* traj_slot(float* traj, int s) {
+    const size_t n_slots = (size_t)gridDim.x * BLOCK_B;
+    const size_t slot = (size_t)blockIdx.x * BLOCK_B + threadIdx.x;
+    return traj + ((size_t)s * n_slots + slot) * (KB * 3);
+}
+__device__ __forceinline__ void traj_store(float* traj, int s, const float (&x)[KB], const float (&y)[KB],
+                                           const float (&z)[KB]) {
+    float2* p = reinterpret_cast<float2*>(traj_slot(traj, s));
+    p[0] = make_float2(x[0], y[0]); p[1] = make_float2(z[0], x[1]); p[2] = make_float2(y[1], z[1]);
+}
+__device__ __forceinline__ void traj_load(float* traj, int s, float (&x)[KB], float (&y)[KB], float (&z)[KB]) {
+    const float2* p = reinterpret_cast<const float2*>(traj_slot(traj, s));
+    const float2 a = p[0], b = p[1], c = p[2];
+    x[0] = a.x; y[0] = a.y; z[0] = b.x; x[1] = b.y; y[1] = c.x; z[1] = c.y;
+}
+
+// Shared memory: [tape par (n_par floats) | accumulators (n_par floats)]
+__device__ __forceinline__ float* stage_accumulators(unsigned char* smem, int n_par) {
+    float* sacc = reinterpret_cast<float*>(smem + (size_t)n_par * sizeof(float));
     for (int i = threadIdx.x; i < n_par; i += blockDim.x) sacc[i] = 0.f;
     return sacc;
 }
@@ -57,14 +88,57 @@ __device__ __forceinline__ void flush_accumulators(const float* sacc, float* dpa
     }
 }
 
+// Replays the march with IEEE math, storing the position before every step.
+template <int CAP>
+__device__ __forceinline__ void replay_march(const TapeCode<CAP>& code, int n_instr, const float4* spar,
+                                             int steps, float* traj, float (&px)[KB], float (&py)[KB],
+                                             float (&pz)[KB], const float (&vx)[KB],
+                                             const float (&vy)[KB], const float (&vz)[KB]) {
+    for (int s = 0; s < steps; ++s) {
+        traj_store(traj, s, px, py, pz);
+        float d[KB];
+        eval_scene<KB, false, CAP>(code, n_instr, spar, px, py, pz, d);
+#pragma unroll
+        for (int k = 0; k < KB; ++k) {
+            px[k] = fmaf(d[k], vx[k], px[k]); py[k] = fmaf(d[k], vy[k], py[k]); pz[k] = fmaf(d[k], vz[k], pz[k]);
+        }
+    }
+}
+
+// Reverse of the march: on entry l* = adjoint of p_S, on exit l* = adjoint of p_0; dv* accumulates
+// the adjoint of the direction.
+template <int CAP>
+__device__ __forceinline__ void reverse_march(const TapeCode<CAP>& code, int n_instr, const float4* spar,
+                                              int steps, float* traj, float* sacc,
+                                              const float (&vx)[KB], const float (&vy)[KB],
+                                              const float (&vz)[KB], float (&lx)[KB], float (&ly)[KB],
+                                              float (&lz)[KB], float (&dvx)[KB], float (&dvy)[KB],
+                                              float (&dvz)[KB]) {
+    for (int s = steps - 1; s >= 0; --s) {
+        float px[KB], py[KB], pz[KB], a[KB], f[KB], gx[KB], gy[KB], gz[KB];
+        traj_load(traj, s, px, py, pz);
+#pragma unroll
+        for (int k = 0; k < KB; ++k) a[k] = lx[k] * vx[k] + ly[k] * vy[k] + lz[k] * vz[k];
+        NodeRecords<KB> rec;
+        eval_record<KB, CAP>(code, n_instr, spar, px, py, pz, rec, f);
+        sweep_vjp<KB, CAP>(code, n_instr, spar, px, py, pz, a, rec, sacc, gx, gy, gz);
+#pragma unroll
+        for (int k = 0; k < KB; ++k) {
+            dvx[k] = fmaf(f[k], lx[k], dvx[k]); dvy[k] = fmaf(f[k], ly[k], dvy[k]); dvz[k] = fmaf(f[k], lz[k], dvz[k]);
+            lx[k] += gx[k]; ly[k] += gy[k]; lz[k] += gz[k];
+        }
+    }
+}
+
 // Grid-stride over sample groups so the number of blocks (and global atomics) stays bounded.
+template <int CAP>
 __global__ void __launch_bounds__(BLOCK_B)
-sdf_vjp_kernel(const int32_t* code, const float* par, int n_instr, int n_par,
+sdf_vjp_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
                const float* __restrict__ pts, const float* __restrict__ gout, int64_t n,
                float* __restrict__ dpts, float* __restrict__ dpar) {
     extern __shared__ __align__(16) unsigned char smem[];
-    float* sacc = stage_accumulators(smem, n_instr, n_par);
-    const TapeView T = stage_tape(code, par, n_instr, n_par, smem);     // syncs
+    float* sacc = stage_accumulators(smem, n_par);
+    const float4* spar = stage_params(par, n_par, smem);                // syncs
     const int64_t groups = (n + KB - 1) / KB;
     const int64_t warp_groups = (groups + 31) / 32 * 32;                // whole warps iterate together
     for (int64_t g = (int64_t)blockIdx.x * BLOCK_B + threadIdx.x; g < warp_groups;
@@ -72,24 +146,24 @@ sdf_vjp_kernel(const int32_t* code, const float* par, int n_instr, int n_par,
         const int64_t first = g * KB;
         float x[KB], y[KB], z[KB], a[KB], f[KB], gx[KB], gy[KB], gz[KB];
         load3k(pts, first, n, x, y, z);
-#pragma unroll
-        for (int k = 0; k < KB; ++k) a[k] = first + k < n ? __ldg(gout + first + k) : 0.f;
+        load1k(gout, first, n, a);
         NodeRecords<KB> rec;
-        eval_record<KB>(T, x, y, z, rec, f);
-        sweep_vjp<KB>(T, x, y, z, a, rec, sacc, gx, gy, gz);
+        eval_record<KB, CAP>(code, n_instr, spar, x, y, z, rec, f);
+        sweep_vjp<KB, CAP>(code, n_instr, spar, x, y, z, a, rec, sacc, gx, gy, gz);
         store3k(dpts, first, n, gx, gy, gz);
     }
     flush_accumulators(sacc, dpar, n_par);
 }
 
+template <int CAP>
 __global__ void __launch_bounds__(BLOCK_B)
-march_bwd_kernel(const int32_t* code, const float* par, int n_instr, int n_par,
+march_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
                  const float* __restrict__ origin, const float* __restrict__ dirs,
                  const float* __restrict__ gpos, int64_t n, int steps, float* __restrict__ traj,
                  float* __restrict__ dorigin, float* __restrict__ ddirs, float* __restrict__ dpar) {
     extern __shared__ __align__(16) unsigned char smem[];
-    float* sacc = stage_accumulators(smem, n_instr, n_par);
-    const TapeView T = stage_tape(code, par, n_instr, n_par, smem);
+    float* sacc = stage_accumulators(smem, n_par);
+    const float4* spar = stage_params(par, n_par, smem);
     const int64_t groups = (n + KB - 1) / KB;
     const int64_t warp_groups = (groups + 31) / 32 * 32;
     for (int64_t g = (int64_t)blockIdx.x * BLOCK_B + threadIdx.x; g < warp_groups;
@@ -98,40 +172,214 @@ march_bwd_kernel(const int32_t* code, const float* par, int n_instr, int n_par,
         float px[KB], py[KB], pz[KB], vx[KB], vy[KB], vz[KB];
         load3k(origin, first, n, px, py, pz);
         load3k(dirs, first, n, vx, vy, vz);
-        // ---- replay forward, storing the position before every step (IEEE math, as the
-        // forward op used when autograd is recording) ----
-        for (int s = 0; s < steps; ++s) {
-            store3k(traj + (size_t)s * n * 3, first, n, px, py, pz);
-            float d[KB];
-            eval_scene<KB, false>(T, px, py, pz, d);
-#pragma unroll
-            for (int k = 0; k < KB; ++k) {
-                px[k] = fmaf(d[k], vx[k], px[k]); py[k] = fmaf(d[k], vy[k], py[k]); pz[k] = fmaf(d[k], vz[k], pz[k]);
-            }
-        }
-        // ---- reverse ----
+        replay_march<CAP>(code, n_instr, spar, steps, traj, px, py, pz, vx, vy, vz);
         float lx[KB], ly[KB], lz[KB], dvx[KB], dvy[KB], dvz[KB];
         load3k(gpos, first, n, lx, ly, lz);
 #pragma unroll
         for (int k = 0; k < KB; ++k) dvx[k] = dvy[k] = dvz[k] = 0.f;
-        for (int s = steps - 1; s >= 0; --s) {
-            load3k(traj + (size_t)s * n * 3, first, n, px, py, pz);
-            float a[KB], f[KB], gx[KB], gy[KB], gz[KB];
-#pragma unroll
-            for (int k = 0; k < KB; ++k) a[k] = lx[k] * vx[k] + ly[k] * vy[k] + lz[k] * vz[k];
-            NodeRecords<KB> rec;
-            eval_record<KB>(T, px, py, pz, rec, f);
-            sweep_vjp<KB>(T, px, py, pz, a, rec, sacc, gx, gy, gz);
-#pragma unroll
-            for (int k = 0; k < KB; ++k) {
-                dvx[k] = fmaf(f[k], lx[k], dvx[k]); dvy[k] = fmaf(f[k], ly[k], dvy[k]); dvz[k] = fmaf(f[k], lz[k], dvz[k]);
-                lx[k] += gx[k]; ly[k] += gy[k]; lz[k] += gz[k];
-            }
-        }
+        reverse_march<CAP>(code, n_instr, spar, steps, traj, sacc, vx, vy, vz, lx, ly, lz, dvx, dvy, dvz);
         store3k(dorigin, first, n, lx, ly, lz);
         store3k(ddirs, first, n, dvx, dvy, dvz);
     }
     flush_accumulators(sacc, dpar, n_par);
+}
+
+// ---- fused G-buffer backward ------------------------------------------------------------------
+struct RenderBwdParams {
+    CamParams cam;
+    Stencil st;
+    int64_t ray_begin, n_rays;
+    int steps;
+    RmRenderGrads g;
+    float* traj;
+    float* dpar;
+    float* dposes;
+};
+
+// Adjoint of w = R(q) b w.r.t. q for an upstream adjoint l of w (R = rotation polynomial):
+//   d/dw   = 2 l . (v x b)
+//   d/dv   = 2 w (b x l) + 2 [ (v.b) l + (l.v) b - 2 (l.b) v ]          (v = vector part of q)
+__device__ __forceinline__ void rotation_vjp(const float (&q)[4], const float (&b)[3], const float (&l)[3],
+                                             float (&dq)[4]) {
+    const float w = q[0], vx = q[1], vy = q[2], vz = q[3];
+    const float cx = vy * b[2] - vz * b[1], cy = vz * b[0] - vx * b[2], cz = vx * b[1] - vy * b[0];   // v x b
+    dq[0] += 2.f * (l[0] * cx + l[1] * cy + l[2] * cz);
+    const float bx = b[1] * l[2] - b[2] * l[1], by = b[2] * l[0] - b[0] * l[2], bz = b[0] * l[1] - b[1] * l[0]; // b x l
+    const float vb = vx * b[0] + vy * b[1] + vz * b[2];
+    const float lv = l[0] * vx + l[1] * vy + l[2] * vz;
+    const float lb = l[0] * b[0] + l[1] * b[1] + l[2] * b[2];
+    dq[1] += 2.f * (w * bx + vb * l[0] + lv * b[0] - 2.f * lb * vx);
+    dq[2] += 2.f * (w * by + vb * l[1] + lv * b[1] - 2.f * lb * vy);
+    dq[3] += 2.f * (w * bz + vb * l[2] + lv * b[2] - 2.f * lb * vz);
+}
+
+// Called by whole, converged warps at kernel end.  Lanes may hold different views only across a
+// view boundary, so the loop below runs once in almost every warp.
+__device__ __forceinline__ void flush_pose_grad(float* dposes, int view, const float (&acc)[7]) {
+    const int lane = threadIdx.x & 31;
+    unsigned todo = 0xffffffffu;
+    while (todo) {
+        const int leader = __ffs(todo) - 1;
+        const int v = __shfl_sync(0xffffffffu, view, leader);
+        const bool mine = view == v;
+#pragma unroll
+        for (int i = 0; i < 7; ++i) {
+            const float x = warp_sum(mine ? acc[i] : 0.f);
+            if (lane == 0 && v >= 0 && x != 0.f) atomicAdd(dposes + (size_t)v * POSE_STRIDE + i, x);
+        }
+        todo &= ~__ballot_sync(0xffffffffu, mine);
+    }
+}
+
+template <int CAP>
+__global__ void __launch_bounds__(BLOCK_B)
+render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
+                  const float* __restrict__ poses, const __grid_constant__ RenderBwdParams P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    float* sacc = stage_accumulators(smem, n_par);
+    const float4* spar = stage_params(par, n_par, smem);
+    const int64_t n = P.n_rays;
+    const int64_t groups = (n + KB - 1) / KB;
+    const int64_t warp_groups = (groups + 31) / 32 * 32;
+    const bool need_stencil = P.g.normals != nullptr || P.g.laplacian != nullptr;
+    const int64_t per_view = (int64_t)P.cam.width * P.cam.height;
+
+    float cam_acc[7];                       // dq[4], dt[3] of `acc_view`, summed over this thread's rays
+#pragma unroll
+    for (int i = 0; i < 7; ++i) cam_acc[i] = 0.f;
+    int acc_view = -1;
+
+    for (int64_t g = (int64_t)blockIdx.x * BLOCK_B + threadIdx.x; g < warp_groups;
+         g += (int64_t)gridDim.x * BLOCK_B) {
+        const int64_t first = g * KB;
+        // ---- rays from the pixel index (PinholeCamera.forward) ----
+        float ob[KB][3], vb[KB][3];
+        float px[KB], py[KB], pz[KB], vx[KB], vy[KB], vz[KB];
+        Pose pose;
+        int cur_view = -1;
+#pragma unroll
+        for (int k = 0; k < KB; ++k) {
+            float ow[3], vw[3];
+            world_ray(P.cam, poses, P.ray_begin + first + k, pose, cur_view, ob[k], vb[k], ow, vw);
+            px[k] = ow[0]; py[k] = ow[1]; pz[k] = ow[2];
+            vx[k] = vw[0]; vy[k] = vw[1]; vz[k] = vw[2];
+        }
+        // ---- replay the march ----
+        replay_march<CAP>(code, n_instr, spar, P.steps, P.traj, px, py, pz, vx, vy, vz);
+
+        // ---- adjoint of p_S: upstream + stencil (SDFNormals.forward, ray_marching.py:115-125)
+        //      + f(p_S) (control.py:244) ----
+        float lx[KB], ly[KB], lz[KB];
+        load3k(P.g.pos, first, n, lx, ly, lz);
+        float a_c[KB];                                      // adjoint of the centre sample f(p_S)
+        load1k(P.g.sdf, first, n, a_c);
+        if (need_stencil) {
+            float o[4][KB];
+            for (int j = 0; j < 4; ++j) {                   // the normal needs the four offset samples
+                float x[KB], y[KB], z[KB], d[KB];
+#pragma unroll
+                for (int k = 0; k < KB; ++k) {
+                    x[k] = px[k] + P.st.off[j][0]; y[k] = py[k] + P.st.off[j][1]; z[k] = pz[k] + P.st.off[j][2];
+                }
+                eval_scene<KB, false, CAP>(code, n_instr, spar, x, y, z, d);
+#pragma unroll
+                for (int k = 0; k < KB; ++k) {
+                    if (j == 0) o[0][k] = d[k];
+                    else if (j == 1) o[1][k] = d[k];
+                    else if (j == 2) o[2][k] = d[k];
+                    else o[3][k] = d[k];
+                }
+            }
+            float gnx[KB], gny[KB], gnz[KB], glap[KB];
+            load3k(P.g.normals, first, n, gnx, gny, gnz);
+            load1k(P.g.laplacian, first, n, glap);
+            float a_o[4][KB];
+#pragma unroll
+            for (int k = 0; k < KB; ++k) {
+                // forward: u = Ainv (o[1..3] - o[0]); nrm = u / |u|; lap = (fc - mean o) * 6/eps^2
+                const float d0 = o[1][k] - o[0][k], d1 = o[2][k] - o[0][k], d2 = o[3][k] - o[0][k];
+                const float ux = (P.st.inv[0] * d0 + P.st.inv[1] * d1) + P.st.inv[2] * d2;
+                const float uy = (P.st.inv[3] * d0 + P.st.inv[4] * d1) + P.st.inv[5] * d2;
+                const float uz = (P.st.inv[6] * d0 + P.st.inv[7] * d1) + P.st.inv[8] * d2;
+                const float len = __fsqrt_rn(ux * ux + uy * uy + uz * uz);
+                const float il = __fdiv_rn(1.f, len);
+                const float nx = ux * il, ny = uy * il, nz = uz * il;
+                // d nrm / d u = (I - nrm nrm^T) / |u|
+                const float gn = gnx[k] * nx + gny[k] * ny + gnz[k] * nz;
+                const bool has_n = P.g.normals != nullptr;
+                const float gux = has_n ? (gnx[k] - gn * nx) * il : 0.f;
+                const float guy = has_n ? (gny[k] - gn * ny) * il : 0.f;
+                const float guz = has_n ? (gnz[k] - gn * nz) * il : 0.f;
+                const float gd0 = P.st.inv[0] * gux + P.st.inv[3] * guy + P.st.inv[6] * guz;   // Ainv^T g_u
+                const float gd1 = P.st.inv[1] * gux + P.st.inv[4] * guy + P.st.inv[7] * guz;
+                const float gd2 = P.st.inv[2] * gux + P.st.inv[5] * guy + P.st.inv[8] * guz;
+                const float gm = glap[k] * P.st.lap_scale;                                     // d lap / d fc
+                a_o[0][k] = -(gd0 + gd1 + gd2) - 0.25f * gm;
+                a_o[1][k] = gd0 - 0.25f * gm;
+                a_o[2][k] = gd1 - 0.25f * gm;
+                a_o[3][k] = gd2 - 0.25f * gm;
+                a_c[k] += gm;
+            }
+            for (int j = 0; j < 4; ++j) {
+                float x[KB], y[KB], z[KB], a[KB], f[KB], gx[KB], gy[KB], gz[KB];
+#pragma unroll
+                for (int k = 0; k < KB; ++k) {
+                    x[k] = px[k] + P.st.off[j][0]; y[k] = py[k] + P.st.off[j][1]; z[k] = pz[k] + P.st.off[j][2];
+                    a[k] = j == 0 ? a_o[0][k] : (j == 1 ? a_o[1][k] : (j == 2 ? a_o[2][k] : a_o[3][k]));
+                }
+                NodeRecords<KB> rec;
+                eval_record<KB, CAP>(code, n_instr, spar, x, y, z, rec, f);
+                sweep_vjp<KB, CAP>(code, n_instr, spar, x, y, z, a, rec, sacc, gx, gy, gz);
+#pragma unroll
+                for (int k = 0; k < KB; ++k) { lx[k] += gx[k]; ly[k] += gy[k]; lz[k] += gz[k]; }
+            }
+        }
+        if (need_stencil || P.g.sdf != nullptr) {
+            float f[KB], gx[KB], gy[KB], gz[KB];
+            NodeRecords<KB> rec;
+            eval_record<KB, CAP>(code, n_instr, spar, px, py, pz, rec, f);
+            sweep_vjp<KB, CAP>(code, n_instr, spar, px, py, pz, a_c, rec, sacc, gx, gy, gz);
+#pragma unroll
+            for (int k = 0; k < KB; ++k) { lx[k] += gx[k]; ly[k] += gy[k]; lz[k] += gz[k]; }
+        }
+
+        // ---- reverse the march ----
+        float dvx[KB], dvy[KB], dvz[KB];
+        load3k(P.g.dirs, first, n, dvx, dvy, dvz);
+        reverse_march<CAP>(code, n_instr, spar, P.steps, P.traj, sacc, vx, vy, vz, lx, ly, lz, dvx, dvy, dvz);
+        float gox[KB], goy[KB], goz[KB];
+        load3k(P.g.origin, first, n, gox, goy, goz);
+
+        // ---- camera pose: origin = R(q) o_b + t, dir = R(q) v_b ----
+#pragma unroll
+        for (int k = 0; k < KB; ++k) {
+            const int64_t r = P.ray_begin + first + k;
+            const bool valid = first + k < n;
+            const int view = valid ? (int)(r / per_view) : acc_view;
+            if (view != acc_view) {                           // rare: view boundary inside a thread's stream
+                if (acc_view >= 0) {
+#pragma unroll
+                    for (int i = 0; i < 7; ++i)
+                        if (cam_acc[i] != 0.f) atomicAdd(P.dposes + (size_t)acc_view * POSE_STRIDE + i, cam_acc[i]);
+                }
+#pragma unroll
+                for (int i = 0; i < 7; ++i) cam_acc[i] = 0.f;
+                acc_view = view;
+            }
+            if (valid) {
+                const Pose ps = load_pose(poses, view);
+                const float lo[3] = {lx[k] + gox[k], ly[k] + goy[k], lz[k] + goz[k]};
+                const float lv[3] = {dvx[k], dvy[k], dvz[k]};
+                float dq[4] = {0.f, 0.f, 0.f, 0.f};
+                rotation_vjp(ps.q, ob[k], lo, dq);
+                rotation_vjp(ps.q, vb[k], lv, dq);
+                cam_acc[0] += dq[0]; cam_acc[1] += dq[1]; cam_acc[2] += dq[2]; cam_acc[3] += dq[3];
+                cam_acc[4] += lo[0]; cam_acc[5] += lo[1]; cam_acc[6] += lo[2];
+            }
+        }
+    }
+    flush_pose_grad(P.dposes, acc_view, cam_acc);
+    flush_accumulators(sacc, P.dpar, n_par);
 }
 
 inline int check_backward_tape(const RmTape* t) {
@@ -146,10 +394,16 @@ inline unsigned backward_grid(int64_t n) {
     const int64_t cap = 148 * 8;                      // bounded: one global atomic per parameter per block
     return (unsigned)(want < cap ? (want > 0 ? want : 1) : cap);
 }
+inline size_t backward_smem(const RmTape* t) { return 2 * (size_t)t->n_par * sizeof(float); }
 
 }  // namespace rm
 
 using namespace rm;
+
+extern "C" int64_t rm_bwd_scratch_floats(int64_t n_rays, int32_t steps) {
+    if (n_rays <= 0 || steps <= 0) return 0;
+    return (int64_t)steps * backward_grid(n_rays) * BLOCK_B * KB * 3;
+}
 
 extern "C" int rm_sdf_vjp(const RmTape* tape, const float* points, const float* grad_sdf, int64_t n,
                           float* dpoints, float* dpar, void* stream) {
@@ -159,10 +413,12 @@ extern "C" int rm_sdf_vjp(const RmTape* tape, const float* points, const float* 
     if (tape->n_par > 0)
         RM_CUDA(cudaMemsetAsync(dpar, 0, (size_t)tape->n_par * sizeof(float), (cudaStream_t)stream));
     if (n == 0) return RM_OK;
-    const size_t sm = tape_smem_bytes(tape) + (size_t)tape->n_par * sizeof(float);
-    if (int s = prepare_smem(sdf_vjp_kernel, sm)) return s;
-    sdf_vjp_kernel<<<backward_grid(n), BLOCK_B, sm, (cudaStream_t)stream>>>(
-        tape->code, tape->par, tape->n_instr, tape->n_par, points, grad_sdf, n, dpoints, dpar);
+    const size_t sm = backward_smem(tape);
+    RM_WITH_CODE(tape, {
+        if (int s = prepare_smem(sdf_vjp_kernel<CAP>, sm)) return s;
+        sdf_vjp_kernel<CAP><<<backward_grid(n), BLOCK_B, sm, (cudaStream_t)stream>>>(
+            code, tape->par, tape->n_instr, tape->n_par, points, grad_sdf, n, dpoints, dpar);
+    });
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }
@@ -177,11 +433,48 @@ extern "C" int rm_march_bwd(const RmTape* tape, const float* origin, const float
     if (tape->n_par > 0)
         RM_CUDA(cudaMemsetAsync(dpar, 0, (size_t)tape->n_par * sizeof(float), (cudaStream_t)stream));
     if (n == 0) return RM_OK;
-    const size_t sm = tape_smem_bytes(tape) + (size_t)tape->n_par * sizeof(float);
-    if (int s = prepare_smem(march_bwd_kernel, sm)) return s;
-    march_bwd_kernel<<<backward_grid(n), BLOCK_B, sm, (cudaStream_t)stream>>>(
-        tape->code, tape->par, tape->n_instr, tape->n_par, origin, dirs, grad_pos, n, steps,
-        traj_scratch, dorigin, ddirs, dpar);
+    const size_t sm = backward_smem(tape);
+    RM_WITH_CODE(tape, {
+        if (int s = prepare_smem(march_bwd_kernel<CAP>, sm)) return s;
+        march_bwd_kernel<CAP><<<backward_grid(n), BLOCK_B, sm, (cudaStream_t)stream>>>(
+            code, tape->par, tape->n_instr, tape->n_par, origin, dirs, grad_pos, n, steps,
+            traj_scratch, dorigin, ddirs, dpar);
+    });
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+}
+
+extern "C" int rm_render_bwd(const RmTape* tape, const RmCamera* cam, const float* poses,
+                             const RmRenderArgs* a, const RmRenderGrads* grads, float* traj_scratch,
+                             float* dpar, float* dposes, void* stream) {
+    if (int s = check_backward_tape(tape)) return s;
+    RenderBwdParams P;
+    if (int s = make_cam(cam, &P.cam)) return s;
+    if (a == nullptr || grads == nullptr || poses == nullptr || dposes == nullptr ||
+        (dpar == nullptr && tape->n_par > 0))
+        return fail(RM_ERR_INVALID, "rm_render_bwd: null argument");
+    const int64_t total = (int64_t)cam->n_views * cam->width * cam->height;
+    if (a->ray_begin < 0 || a->n_rays < 0 || a->ray_begin + a->n_rays > total)
+        return fail(RM_ERR_INVALID, "rm_render_bwd: ray range outside the camera batch");
+    if (a->steps < 0 || !(a->normals_eps > 0.f))
+        return fail(RM_ERR_INVALID, "rm_render_bwd: negative steps or eps <= 0");
+    if (a->bounces != 0)
+        return fail(RM_ERR_UNSUPPORTED, "rm_render_bwd: reflected segments are not differentiable here");
+    if (a->n_rays > 0 && a->steps > 0 && traj_scratch == nullptr)
+        return fail(RM_ERR_INVALID, "rm_render_bwd: trajectory scratch is null");
+    if (tape->n_par > 0)
+        RM_CUDA(cudaMemsetAsync(dpar, 0, (size_t)tape->n_par * sizeof(float), (cudaStream_t)stream));
+    RM_CUDA(cudaMemsetAsync(dposes, 0, (size_t)cam->n_views * RM_POSE_STRIDE * sizeof(float), (cudaStream_t)stream));
+    if (a->n_rays == 0) return RM_OK;
+    make_stencil(a->normals_eps, &P.st);
+    P.ray_begin = a->ray_begin; P.n_rays = a->n_rays; P.steps = a->steps;
+    P.g = *grads; P.traj = traj_scratch; P.dpar = dpar; P.dposes = dposes;
+    const size_t sm = backward_smem(tape);
+    RM_WITH_CODE(tape, {
+        if (int s = prepare_smem(render_bwd_kernel<CAP>, sm)) return s;
+        render_bwd_kernel<CAP><<<backward_grid(a->n_rays), BLOCK_B, sm, (cudaStream_t)stream>>>(
+            code, tape->par, tape->n_instr, tape->n_par, poses, P);
+    });
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }

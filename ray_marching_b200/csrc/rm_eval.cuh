@@ -1,77 +1,90 @@
 // Register-resident tape interpreter: evaluates the scene SDF at K points per thread.
 //
-// Every lane of a warp executes the same tape instruction with the same parameter address
-// (the reference evaluates the whole tree for every ray, transformations.py:69,92), so
-// instruction fetch and parameter loads are shared-memory broadcasts and there is no opcode
-// divergence; decoding one instruction is amortised over the K points a thread owns.
+// The reference evaluates the whole tree for every ray (transformations.py:69,92), so every lane
+// of a warp executes the same tape instruction.  The instruction words come from the kernel
+// parameter block (rm_tape.h): the program counter, the decode and every branch below are
+// warp-uniform and run on the uniform datapath; parameter records are shared-memory broadcasts;
+// the cost of one decode is amortised over the K points a thread owns.
 #pragma once
 #include "rm_prims.cuh"
 
 namespace rm {
 
+// Leaf distance at the frame-local point (x, y, z); `op` is warp-uniform.
+template <bool FAST>
+__device__ __forceinline__ float prim_eval(int op, const float4* P, float x, float y, float z) {
+    switch (op) {
+        case OP_SPHERE: return prim_sphere<FAST>(P[0], x, y, z);
+        case OP_BOX: return prim_box<FAST>(P[0], x, y, z);
+        case OP_TORUS: return prim_torus<FAST>(P[0], x, y, z);
+        case OP_LINE: return prim_line<FAST>(P[0], P[1], P[2], x, y, z);
+        case OP_DISK: return prim_disk<FAST>(P[0], x, y, z);
+        default: return x;                                 // OP_PLANE   (primitives.py:40-41)
+    }
+}
+
 // One accumulator per open union: hard union keeps the running min in a0; smooth union keeps
 // an online log-sum-exp of x_i = c * f_i (c = -k, or -k*log2(e) in FAST mode): a0 = running
 // max, a1 = sum of exp(x_i - a0).  Equals the reference's max-shifted logsumexp
 // (transformations.py:69-70) up to rounding.
-template <int K, bool FAST>
-__device__ __forceinline__ void eval_scene(const TapeView& T, const float (&px)[K],
+template <int K, bool FAST, int CAP>
+__device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_instr,
+                                           const float4* __restrict__ spar, const float (&px)[K],
                                            const float (&py)[K], const float (&pz)[K],
                                            float (&out)[K]) {
     using M = Math<FAST>;
-    float qx[K], qy[K], qz[K];
     float a0[K], a1[K], d[K];
     float c = 0.f;                                   // scale of the innermost open smooth union
     float stk[MAX_DEPTH * (2 * K + 1)];              // spilled accumulators of enclosing unions
     int sp = 0;
 #pragma unroll
-    for (int k = 0; k < K; ++k) { qx[k] = px[k]; qy[k] = py[k]; qz[k] = pz[k]; a0[k] = 0.f; a1[k] = 0.f; d[k] = 0.f; }
+    for (int k = 0; k < K; ++k) { a0[k] = 0.f; a1[k] = 0.f; d[k] = 0.f; }
 
-    for (int pc = 0; pc < T.n_instr; ++pc) {
-        const int4 ins = T.code[pc];
+    for (int pc = 0; pc < n_instr; ++pc) {
+        const int2 ins = C.ins[pc];
         const int head = ins.x;
-        const float4* P = T.par + ins.y;
+        const float4* P = spar + word_par(ins.y);
         const int op = head_op(head);
         if (op < OP_OPEN_MIN) {
-            const int fm = head_frame(head);
-            if (fm == FRAME_NEW) {                   // q = A p + b  (composed affine chain)
+            if (head & HEAD_FRAME) {                 // q = A p + b  (composed affine chain)
                 const float4 r0 = P[0], r1 = P[1], r2 = P[2];
                 P += 3;
-#pragma unroll
-                for (int k = 0; k < K; ++k) {
-                    qx[k] = fmaf(r0.x, px[k], fmaf(r0.y, py[k], fmaf(r0.z, pz[k], r0.w)));
-                    qy[k] = fmaf(r1.x, px[k], fmaf(r1.y, py[k], fmaf(r1.z, pz[k], r1.w)));
-                    qz[k] = fmaf(r2.x, px[k], fmaf(r2.y, py[k], fmaf(r2.z, pz[k], r2.w)));
+                // the switch sits outside the K loop: one uniform jump per instruction
+#define RM_LEAF_FRAME(EXPR)                                                                     \
+    _Pragma("unroll") for (int k = 0; k < K; ++k) {                                             \
+        const float x = fmaf(r0.x, px[k], fmaf(r0.y, py[k], fmaf(r0.z, pz[k], r0.w)));          \
+        const float y = fmaf(r1.x, px[k], fmaf(r1.y, py[k], fmaf(r1.z, pz[k], r1.w)));          \
+        const float z = fmaf(r2.x, px[k], fmaf(r2.y, py[k], fmaf(r2.z, pz[k], r2.w)));          \
+        d[k] = EXPR;                                                                            \
+    }
+                switch (op) {
+                    case OP_SPHERE: { const float4 p0 = P[0]; RM_LEAF_FRAME(prim_sphere<FAST>(p0, x, y, z)) } break;
+                    case OP_BOX: { const float4 p0 = P[0]; RM_LEAF_FRAME(prim_box<FAST>(p0, x, y, z)) } break;
+                    case OP_TORUS: { const float4 p0 = P[0]; RM_LEAF_FRAME(prim_torus<FAST>(p0, x, y, z)) } break;
+                    case OP_LINE: { const float4 p0 = P[0], p1 = P[1], p2 = P[2]; RM_LEAF_FRAME(prim_line<FAST>(p0, p1, p2, x, y, z)) } break;
+                    case OP_DISK: { const float4 p0 = P[0]; RM_LEAF_FRAME(prim_disk<FAST>(p0, x, y, z)) } break;
+                    default: { RM_LEAF_FRAME(x) } break;
                 }
-            } else if (fm == FRAME_WORLD) {
-#pragma unroll
-                for (int k = 0; k < K; ++k) { qx[k] = px[k]; qy[k] = py[k]; qz[k] = pz[k]; }
-            }
-            if (op == OP_SPHERE) {
-                const float4 p0 = P[0];
-#pragma unroll
-                for (int k = 0; k < K; ++k) d[k] = prim_sphere<FAST>(p0, qx[k], qy[k], qz[k]);
-            } else if (op == OP_BOX) {
-                const float4 p0 = P[0];
-#pragma unroll
-                for (int k = 0; k < K; ++k) d[k] = prim_box<FAST>(p0, qx[k], qy[k], qz[k]);
-            } else if (op == OP_TORUS) {
-                const float4 p0 = P[0];
-#pragma unroll
-                for (int k = 0; k < K; ++k) d[k] = prim_torus<FAST>(p0, qx[k], qy[k], qz[k]);
-            } else if (op == OP_LINE) {
-                const float4 p0 = P[0], p1 = P[1], p2 = P[2];
-#pragma unroll
-                for (int k = 0; k < K; ++k) d[k] = prim_line<FAST>(p0, p1, p2, qx[k], qy[k], qz[k]);
-            } else if (op == OP_DISK) {
-                const float4 p0 = P[0];
-#pragma unroll
-                for (int k = 0; k < K; ++k) d[k] = prim_disk<FAST>(p0, qx[k], qy[k], qz[k]);
-            } else {                                  // OP_PLANE: q.x   (primitives.py:40-41)
-#pragma unroll
-                for (int k = 0; k < K; ++k) d[k] = qx[k];
+#undef RM_LEAF_FRAME
+            } else {
+#define RM_LEAF_WORLD(EXPR)                                                                     \
+    _Pragma("unroll") for (int k = 0; k < K; ++k) {                                             \
+        const float x = px[k], y = py[k], z = pz[k];                                            \
+        (void)y; (void)z;                                                                       \
+        d[k] = EXPR;                                                                            \
+    }
+                switch (op) {
+                    case OP_SPHERE: { const float4 p0 = P[0]; RM_LEAF_WORLD(prim_sphere<FAST>(p0, x, y, z)) } break;
+                    case OP_BOX: { const float4 p0 = P[0]; RM_LEAF_WORLD(prim_box<FAST>(p0, x, y, z)) } break;
+                    case OP_TORUS: { const float4 p0 = P[0]; RM_LEAF_WORLD(prim_torus<FAST>(p0, x, y, z)) } break;
+                    case OP_LINE: { const float4 p0 = P[0], p1 = P[1], p2 = P[2]; RM_LEAF_WORLD(prim_line<FAST>(p0, p1, p2, x, y, z)) } break;
+                    case OP_DISK: { const float4 p0 = P[0]; RM_LEAF_WORLD(prim_disk<FAST>(p0, x, y, z)) } break;
+                    default: { RM_LEAF_WORLD(x) } break;
+                }
+#undef RM_LEAF_WORLD
             }
             P += prim_f4(op);
-        } else if (op == OP_OPEN_MIN || op == OP_OPEN_SMOOTH) {
+        } else if (op <= OP_OPEN_SMOOTH) {
             if (!(head & HEAD_ROOT)) {
                 float* s = stk + sp * (2 * K + 1);
 #pragma unroll
@@ -112,9 +125,13 @@ __device__ __forceinline__ void eval_scene(const TapeView& T, const float (&px)[
 #pragma unroll
             for (int i = 0; i < 3; ++i) {
                 if (i < np) {
-                    const bool onion = head_post(head, i) == POST_ONION;
+                    if (head_post(head, i) == POST_ONION) {
 #pragma unroll
-                    for (int k = 0; k < K; ++k) d[k] = (onion ? fabsf(d[k]) : d[k]) - pv[i];
+                        for (int k = 0; k < K; ++k) d[k] = fabsf(d[k]) - pv[i];
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < K; ++k) d[k] = d[k] - pv[i];
+                    }
                 }
             }
         }
@@ -136,21 +153,14 @@ __device__ __forceinline__ void eval_scene(const TapeView& T, const float (&px)[
     for (int k = 0; k < K; ++k) out[k] = d[k];
 }
 
-// Cooperative copy of the tape from global into dynamic shared memory.
-__device__ __forceinline__ TapeView stage_tape(const int32_t* code, const float* par, int n_instr,
-                                               int n_par, unsigned char* smem) {
-    int4* scode = reinterpret_cast<int4*>(smem);
-    float4* spar = reinterpret_cast<float4*>(smem + (size_t)n_instr * sizeof(int4));
-    const int4* gcode = reinterpret_cast<const int4*>(code);
+// Cooperative copy of the tape parameters from global into dynamic shared memory.
+__device__ __forceinline__ const float4* stage_params(const float* par, int n_par,
+                                                      unsigned char* smem) {
+    float4* spar = reinterpret_cast<float4*>(smem);
     const float4* gpar = reinterpret_cast<const float4*>(par);
-    for (int i = threadIdx.x; i < n_instr; i += blockDim.x) scode[i] = __ldg(gcode + i);
     for (int i = threadIdx.x; i < n_par / 4; i += blockDim.x) spar[i] = __ldg(gpar + i);
     __syncthreads();
-    TapeView T;
-    T.code = scode;
-    T.par = spar;
-    T.n_instr = n_instr;
-    return T;
+    return spar;
 }
 
 }  // namespace rm

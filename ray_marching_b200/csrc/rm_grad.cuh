@@ -127,47 +127,36 @@ struct NodeRecords {
 };
 
 // Pass 1: forward evaluation (IEEE math) that fills the node records.  Returns f(p_k).
-template <int K>
-__device__ __forceinline__ void eval_record(const TapeView& T, const float (&px)[K],
+template <int K, int CAP>
+__device__ __forceinline__ void eval_record(const TapeCode<CAP>& C, const int n_instr,
+                                            const float4* __restrict__ spar, const float (&px)[K],
                                             const float (&py)[K], const float (&pz)[K],
                                             NodeRecords<K>& rec, float (&out)[K]) {
     using M = Math<false>;
-    float qx[K], qy[K], qz[K], a0[K], a1[K], d[K];
+    float a0[K], a1[K], d[K];
     float c = 0.f;
     float stk[MAX_DEPTH * (2 * K + 1)];
     int sp = 0;
 #pragma unroll
-    for (int k = 0; k < K; ++k) { qx[k] = px[k]; qy[k] = py[k]; qz[k] = pz[k]; a0[k] = a1[k] = d[k] = 0.f; }
-    for (int pc = 0; pc < T.n_instr; ++pc) {
-        const int4 ins = T.code[pc];
+    for (int k = 0; k < K; ++k) { a0[k] = a1[k] = d[k] = 0.f; }
+    for (int pc = 0; pc < n_instr; ++pc) {
+        const int2 ins = C.ins[pc];
         const int head = ins.x, op = head_op(head);
-        const float4* P = T.par + ins.y;
+        const int node = word_node(ins.y);
+        const float4* P = spar + word_par(ins.y);
         if (op < OP_OPEN_MIN) {
-            const int fm = head_frame(head);
-            if (fm == FRAME_NEW) {
-                const float4 r0 = P[0], r1 = P[1], r2 = P[2];
-                P += 3;
-#pragma unroll
-                for (int k = 0; k < K; ++k) {
-                    qx[k] = fmaf(r0.x, px[k], fmaf(r0.y, py[k], fmaf(r0.z, pz[k], r0.w)));
-                    qy[k] = fmaf(r1.x, px[k], fmaf(r1.y, py[k], fmaf(r1.z, pz[k], r1.w)));
-                    qz[k] = fmaf(r2.x, px[k], fmaf(r2.y, py[k], fmaf(r2.z, pz[k], r2.w)));
-                }
-            } else if (fm == FRAME_WORLD) {
-#pragma unroll
-                for (int k = 0; k < K; ++k) { qx[k] = px[k]; qy[k] = py[k]; qz[k] = pz[k]; }
-            }
+            float4 r0 = make_float4(1.f, 0.f, 0.f, 0.f), r1 = make_float4(0.f, 1.f, 0.f, 0.f),
+                   r2 = make_float4(0.f, 0.f, 1.f, 0.f);
+            if (head & HEAD_FRAME) { r0 = P[0]; r1 = P[1]; r2 = P[2]; P += 3; }
 #pragma unroll
             for (int k = 0; k < K; ++k) {
-                if (op == OP_SPHERE) d[k] = prim_sphere<false>(P[0], qx[k], qy[k], qz[k]);
-                else if (op == OP_BOX) d[k] = prim_box<false>(P[0], qx[k], qy[k], qz[k]);
-                else if (op == OP_TORUS) d[k] = prim_torus<false>(P[0], qx[k], qy[k], qz[k]);
-                else if (op == OP_LINE) d[k] = prim_line<false>(P[0], P[1], P[2], qx[k], qy[k], qz[k]);
-                else if (op == OP_DISK) d[k] = prim_disk<false>(P[0], qx[k], qy[k], qz[k]);
-                else d[k] = qx[k];
+                const float x = fmaf(r0.x, px[k], fmaf(r0.y, py[k], fmaf(r0.z, pz[k], r0.w)));
+                const float y = fmaf(r1.x, px[k], fmaf(r1.y, py[k], fmaf(r1.z, pz[k], r1.w)));
+                const float z = fmaf(r2.x, px[k], fmaf(r2.y, py[k], fmaf(r2.z, pz[k], r2.w)));
+                d[k] = prim_eval<false>(op, P, x, y, z);
             }
             P += prim_f4(op);
-        } else if (op == OP_OPEN_MIN || op == OP_OPEN_SMOOTH) {
+        } else if (op <= OP_OPEN_SMOOTH) {
             if (!(head & HEAD_ROOT)) {
                 float* s = stk + sp * (2 * K + 1);
 #pragma unroll
@@ -180,7 +169,7 @@ __device__ __forceinline__ void eval_record(const TapeView& T, const float (&px)
                 for (int k = 0; k < K; ++k) { a0[k] = CUDART_INF_F; a1[k] = __int_as_float(0); }
             } else {
                 c = P[0].x;
-                rec.c[ins.w] = c;
+                rec.c[node] = c;
 #pragma unroll
                 for (int k = 0; k < K; ++k) { a0[k] = -CUDART_INF_F; a1[k] = 0.f; }
             }
@@ -188,9 +177,9 @@ __device__ __forceinline__ void eval_record(const TapeView& T, const float (&px)
         } else {
 #pragma unroll
             for (int k = 0; k < K; ++k) {
-                if (op == OP_CLOSE_MIN) { d[k] = a0[k]; rec.win[ins.w][k] = __float_as_int(a1[k]); }
+                if (op == OP_CLOSE_MIN) { d[k] = a0[k]; rec.win[node][k] = __float_as_int(a1[k]); }
                 else d[k] = M::div(a0[k] + M::log(a1[k]), c);
-                rec.d[ins.w][k] = d[k];
+                rec.d[node][k] = d[k];
             }
             if (!(head & HEAD_ROOT)) {
                 --sp;
@@ -214,9 +203,10 @@ __device__ __forceinline__ void eval_record(const TapeView& T, const float (&px)
         }
         const int fold = head_fold(head);
         if (fold == FOLD_MIN) {
+            const int ordinal = head_ordinal(head);
 #pragma unroll
             for (int k = 0; k < K; ++k)
-                if (d[k] < a0[k]) { a0[k] = d[k]; a1[k] = __int_as_float(ins.z); }   // strict: first wins ties
+                if (d[k] < a0[k]) { a0[k] = d[k]; a1[k] = __int_as_float(ordinal); }   // strict: first wins ties
         } else if (fold == FOLD_SMOOTH) {
 #pragma unroll
             for (int k = 0; k < K; ++k) {

@@ -64,16 +64,19 @@ __device__ __forceinline__ void block_minmax(MinMax m, float* gmin, float* gmax,
     }
 }
 
-template <bool FAST>
+template <bool FAST, int CAP>
 __global__ void __launch_bounds__(BLOCK)
-render_kernel(const int32_t* code, const float* par, int n_instr, int n_par,
-              const float* __restrict__ poses, const RenderParams P) {
+render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
+              const float* __restrict__ poses, const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ float red[BLOCK / 32][3];
-    const TapeView T = stage_tape(code, par, n_instr, n_par, smem);
+    const float4* spar = stage_params(par, n_par, smem);
     const int64_t n = P.n_rays;
     const int64_t first = ((int64_t)blockIdx.x * BLOCK + threadIdx.x) * K;
-    const bool active = first < n;          // whole thread out of range: still joins reductions
+    // warp-uniform: a warp is active if its first lane has rays; tail lanes of an active warp
+    // march a clamped duplicate ray (never stored) so that the warp stays converged, and a warp
+    // that is entirely out of range still joins the block reductions below
+    const bool active = ((int64_t)blockIdx.x * BLOCK + (threadIdx.x & ~31)) * K < n;
     const unsigned mask = P.mode_mask | (P.display_mode >= 0 ? (1u << P.display_mode) : 0u);
     const bool need_stencil =
         (mask & (RM_MODE_LAMBERTIAN | RM_MODE_NORMAL | RM_MODE_LAPLACIAN | RM_MODE_TANGENT |
@@ -91,8 +94,8 @@ render_kernel(const int32_t* code, const float* par, int n_instr, int n_par,
         for (int k = 0; k < K; ++k) { px[k] = ox[k]; py[k] = oy[k]; pz[k] = oz[k]; }
 
         for (int b = 0;; ++b) {
-            march_rays<FAST>(T, P.steps, P.early_exit != 0, px, py, pz, vx, vy, vz);
-            stencil_eval(T, P.st, need_stencil, px, py, pz, f, nx, ny, nz, lap);
+            march_rays<FAST, CAP>(code, n_instr, spar, P.steps, P.early_exit != 0, px, py, pz, vx, vy, vz);
+            stencil_eval<CAP>(code, n_instr, spar, P.st, need_stencil, px, py, pz, f, nx, ny, nz, lap);
             if (b >= P.bounces) break;
             // reflected-ray branch (reflect = control.py:179-194)
 #pragma unroll

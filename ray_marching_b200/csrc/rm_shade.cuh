@@ -1,10 +1,13 @@
 // Camera ray generation, the tetrahedral stencil and the per-pixel shaders (device functions).
 #pragma once
+#include <math.h>
+
+#include "rm_host.h"
 #include "rm_math.cuh"
 
 namespace rm {
 
-constexpr int POSE_STRIDE = 20;   // R[9], t[3], fwd[3], q[4], pad
+constexpr int POSE_STRIDE = 8;    // q[4] (w,x,y,z), t[3], pad
 constexpr int CMAP_SIZE = 4096;
 constexpr float TAU_F = 6.283185307179586f;
 
@@ -14,6 +17,10 @@ struct CamParams {
     float inv_w, inv_h;
 };
 
+// Per-view pose, expanded in registers from the 8-float record.
+//   R   = I + 2w[v]x + 2(v v^T - |v|^2 I): the polynomial Q.rotation evaluates (quaternion.py:55-72),
+//         valid for non-unit q, so d/dq matches the reference's autograd;
+//   fwd = third column of QuaternionToSO3(q) (quaternion.py:114-124; vignette shader.py:62-66).
 struct Pose {
     float R[9];
     float t[3];
@@ -23,13 +30,17 @@ struct Pose {
 
 __device__ __forceinline__ Pose load_pose(const float* poses, int view) {
     Pose p;
-    const float* s = poses + (size_t)view * POSE_STRIDE;
-#pragma unroll
-    for (int i = 0; i < 9; ++i) p.R[i] = __ldg(s + i);
-#pragma unroll
-    for (int i = 0; i < 3; ++i) { p.t[i] = __ldg(s + 9 + i); p.fwd[i] = __ldg(s + 12 + i); }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) p.q[i] = __ldg(s + 15 + i);
+    const float4 a = __ldg(reinterpret_cast<const float4*>(poses + (size_t)view * POSE_STRIDE));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(poses + (size_t)view * POSE_STRIDE) + 1);
+    const float w = a.x, x = a.y, y = a.z, z = a.w;
+    p.q[0] = w; p.q[1] = x; p.q[2] = y; p.q[3] = z;
+    p.t[0] = b.x; p.t[1] = b.y; p.t[2] = b.z;
+    const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, xz = x * z, yz = y * z;
+    const float wx = w * x, wy = w * y, wz = w * z;
+    p.R[0] = 1.f - 2.f * (yy + zz); p.R[1] = 2.f * (xy - wz);       p.R[2] = 2.f * (xz + wy);
+    p.R[3] = 2.f * (xy + wz);       p.R[4] = 1.f - 2.f * (xx + zz); p.R[5] = 2.f * (yz - wx);
+    p.R[6] = 2.f * (xz - wy);       p.R[7] = 2.f * (yz + wx);       p.R[8] = 1.f - 2.f * (xx + yy);
+    p.fwd[0] = 2.f * (wy + xz); p.fwd[1] = 2.f * (yz - wx); p.fwd[2] = w * w - xx - yy + zz;
     return p;
 }
 
@@ -56,6 +67,25 @@ __device__ __forceinline__ void mat_apply_t(const float (&R)[9], const float (&x
     y[0] = fmaf(R[0], x[0], fmaf(R[3], x[1], R[6] * x[2]));
     y[1] = fmaf(R[1], x[0], fmaf(R[4], x[1], R[7] * x[2]));
     y[2] = fmaf(R[2], x[0], fmaf(R[5], x[1], R[8] * x[2]));
+}
+
+// World-space ray of global ray index r (clamped to the batch): origin = R o_b + t, dir = R v_b
+// (PinholeCamera.forward, ray_marching.py:57-64).  `pose`/`cur_view` cache the expanded pose across
+// consecutive rays of one thread.  ob/vb return the camera-frame ray (backward needs them).
+__device__ __forceinline__ void world_ray(const CamParams& cam, const float* poses, int64_t r,
+                                          Pose& pose, int& cur_view, float (&ob)[3], float (&vb)[3],
+                                          float (&ow)[3], float (&vw)[3]) {
+    const int64_t per_view = (int64_t)cam.width * cam.height;
+    const int64_t total = per_view * cam.n_views;
+    if (r >= total) r = total - 1;                     // tail lanes recompute the last ray
+    const int view = (int)(r / per_view);
+    const int pix = (int)(r - (int64_t)view * per_view);
+    const int row = pix / cam.width, col = pix - row * cam.width;
+    if (view != cur_view) { pose = load_pose(poses, view); cur_view = view; }
+    base_ray(cam, row, col, ob, vb);
+    mat_apply(pose.R, ob, ow);
+    mat_apply(pose.R, vb, vw);
+    ow[0] += pose.t[0]; ow[1] += pose.t[1]; ow[2] += pose.t[2];
 }
 
 // Tetrahedral stencil constants (ray_marching.py:94-113): offsets eps*normalize((+-1,0,-s),(0,+-1,s)),
@@ -140,6 +170,51 @@ __device__ __forceinline__ void shade_spin(const Pose& cam, const float (&n)[3],
     const float re = a * a - m2;
     const float im = __fsqrt_rn(m2) * a * 2.f;
     domain_colour(im, re, cmap, degree, rgb);
+}
+
+// ---- host-side construction of the kernel constants ------------------------------------------
+inline int make_cam(const RmCamera* c, CamParams* out) {
+    if (c == nullptr || c->n_views <= 0 || c->width <= 0 || c->height <= 0)
+        return fail(RM_ERR_INVALID, "camera is null or has a non-positive size");
+    out->n_views = c->n_views; out->width = c->width; out->height = c->height;
+    out->focal = c->focal_length;
+    out->half_w = c->sensor_width / 2;
+    out->neg_half_h = -c->sensor_height / 2;
+    out->inv_w = 1.0f / (float)c->width;
+    out->inv_h = 1.0f / (float)c->height;
+    return RM_OK;
+}
+
+// SDFNormals.__init__ (ray_marching.py:94-113), float64 on the host, rounded once to float32.
+inline void make_stencil(float eps, Stencil* st) {
+    const double s = sqrt(0.5);
+    const double raw[4][3] = {{1, 0, -s}, {-1, 0, -s}, {0, 1, s}, {0, -1, s}};
+    double off[4][3];
+    for (int j = 0; j < 4; ++j) {
+        const double len = sqrt(raw[j][0] * raw[j][0] + raw[j][1] * raw[j][1] + raw[j][2] * raw[j][2]);
+        for (int c = 0; c < 3; ++c) {
+            off[j][c] = raw[j][c] / len * (double)eps;
+            st->off[j][c] = (float)off[j][c];
+        }
+    }
+    double A[3][3], inv[3][3];
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) A[r][c] = off[r + 1][c] - off[0][c];
+    const double det = A[0][0] * (A[1][1] * A[2][2] - A[1][2] * A[2][1]) -
+                       A[0][1] * (A[1][0] * A[2][2] - A[1][2] * A[2][0]) +
+                       A[0][2] * (A[1][0] * A[2][1] - A[1][1] * A[2][0]);
+    inv[0][0] = (A[1][1] * A[2][2] - A[1][2] * A[2][1]) / det;
+    inv[0][1] = (A[0][2] * A[2][1] - A[0][1] * A[2][2]) / det;
+    inv[0][2] = (A[0][1] * A[1][2] - A[0][2] * A[1][1]) / det;
+    inv[1][0] = (A[1][2] * A[2][0] - A[1][0] * A[2][2]) / det;
+    inv[1][1] = (A[0][0] * A[2][2] - A[0][2] * A[2][0]) / det;
+    inv[1][2] = (A[0][2] * A[1][0] - A[0][0] * A[1][2]) / det;
+    inv[2][0] = (A[1][0] * A[2][1] - A[1][1] * A[2][0]) / det;
+    inv[2][1] = (A[0][1] * A[2][0] - A[0][0] * A[2][1]) / det;
+    inv[2][2] = (A[0][0] * A[1][1] - A[0][1] * A[1][0]) / det;
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) st->inv[r * 3 + c] = (float)inv[r][c];
+    st->lap_scale = (float)(6.0 / ((double)eps * (double)eps));
 }
 
 }  // namespace rm

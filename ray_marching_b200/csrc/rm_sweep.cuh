@@ -66,8 +66,9 @@ __device__ __forceinline__ void child_adjoint(int fold, int ordinal, OpenNode<K>
 
 // The reverse sweep.  `sacc` = per-block shared accumulators, one float per tape parameter.
 // Outputs g{x,y,z}[k] = abar[k] * grad_p f(p_k).  All 32 lanes of the warp must call this together.
-template <int K>
-__device__ __forceinline__ void sweep_vjp(const TapeView& T, const float (&px)[K],
+template <int K, int CAP>
+__device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_instr,
+                                          const float4* __restrict__ spar, const float (&px)[K],
                                           const float (&py)[K], const float (&pz)[K],
                                           const float (&abar)[K], const NodeRecords<K>& rec,
                                           float* sacc, float (&gx)[K], float (&gy)[K],
@@ -80,10 +81,11 @@ __device__ __forceinline__ void sweep_vjp(const TapeView& T, const float (&px)[K
     for (int k = 0; k < K; ++k) { gx[k] = gy[k] = gz[k] = 0.f; cur.a[k] = cur.d[k] = cur.s[k] = 0.f; cur.win[k] = -1; }
     cur.c = 0.f;
 
-    for (int pc = T.n_instr - 1; pc >= 0; --pc) {
-        const int4 ins = T.code[pc];
+    for (int pc = n_instr - 1; pc >= 0; --pc) {
+        const int2 ins = C.ins[pc];
         const int head = ins.x, op = head_op(head);
         const int fold = head_fold(head), np = head_npost(head);
+        const int off = word_par(ins.y), node = word_node(ins.y), ordinal = head_ordinal(head);
         if (op == OP_OPEN_MIN || op == OP_OPEN_SMOOTH) {
             // all children of this union have been visited: finish d/dk, return to the parent
             if (op == OP_OPEN_SMOOTH) {
@@ -91,7 +93,7 @@ __device__ __forceinline__ void sweep_vjp(const TapeView& T, const float (&px)[K
 #pragma unroll
                 for (int k = 0; k < K; ++k) g += cur.a[k] != 0.f ? __fdiv_rn(cur.s[k] - cur.a[k] * cur.d[k], cur.c) : 0.f;
                 g = warp_sum(g);
-                if (lane == 0 && g != 0.f) atomicAdd(sacc + ins.y * 4, g);
+                if (lane == 0 && g != 0.f) atomicAdd(sacc + off * 4, g);
             }
             if (!(head & HEAD_ROOT)) cur = stk[--sp];
             continue;
@@ -100,38 +102,38 @@ __device__ __forceinline__ void sweep_vjp(const TapeView& T, const float (&px)[K
         float gpost[3] = {0.f, 0.f, 0.f};
         if (op >= OP_CLOSE_MIN) {
             // ---- union close: value from the records, descend into the node ----
-            const float4 pp = np ? T.par[ins.y] : make_float4(0.f, 0.f, 0.f, 0.f);
+            const float4 pp = np ? spar[off] : make_float4(0.f, 0.f, 0.f, 0.f);
             const float pv[3] = {pp.x, pp.y, pp.z};
 #pragma unroll
-            for (int k = 0; k < K; ++k) raw[k] = rec.d[ins.w][k];
+            for (int k = 0; k < K; ++k) raw[k] = rec.d[node][k];
             posts_forward<K>(head, pv, raw, y, sg);
-            child_adjoint<K>(fold, ins.z, cur, abar, y, a);
+            child_adjoint<K>(fold, ordinal, cur, abar, y, a);
             posts_backward<K>(head, sg, a, gpost);
             if (np) {
 #pragma unroll
                 for (int i = 0; i < 3; ++i)
                     if (i < np) {
                         const float g = warp_sum(gpost[i]);
-                        if (lane == 0 && g != 0.f) atomicAdd(sacc + ins.y * 4 + i, g);
+                        if (lane == 0 && g != 0.f) atomicAdd(sacc + off * 4 + i, g);
                     }
             }
             if (!(head & HEAD_ROOT)) stk[sp++] = cur;
 #pragma unroll
             for (int k = 0; k < K; ++k) {
                 cur.a[k] = a[k]; cur.d[k] = raw[k]; cur.s[k] = 0.f;
-                cur.win[k] = op == OP_CLOSE_MIN ? rec.win[ins.w][k] : -1;
+                cur.win[k] = op == OP_CLOSE_MIN ? rec.win[node][k] : -1;
             }
-            cur.c = op == OP_CLOSE_SMOOTH ? rec.c[ins.w] : 0.f;
+            cur.c = op == OP_CLOSE_SMOOTH ? rec.c[node] : 0.f;
             continue;
         }
         // ---- leaf: recompute q, value and local gradients --------------------------------
-        const int frame_rec = ins.w;
-        const int prim_rec = ins.y + (head_frame(head) == FRAME_NEW ? 3 : 0);
+        const int frame_rec = (head & HEAD_FRAME) ? off : -1;
+        const int prim_rec = off + ((head & HEAD_FRAME) ? 3 : 0);
         const int post_rec = prim_rec + prim_f4(op);
         float4 r0 = make_float4(1.f, 0.f, 0.f, 0.f), r1 = make_float4(0.f, 1.f, 0.f, 0.f),
                r2 = make_float4(0.f, 0.f, 1.f, 0.f);
-        if (frame_rec >= 0) { r0 = T.par[frame_rec]; r1 = T.par[frame_rec + 1]; r2 = T.par[frame_rec + 2]; }
-        const float4 pp = np ? T.par[post_rec] : make_float4(0.f, 0.f, 0.f, 0.f);
+        if (frame_rec >= 0) { r0 = spar[frame_rec]; r1 = spar[frame_rec + 1]; r2 = spar[frame_rec + 2]; }
+        const float4 pp = np ? spar[post_rec] : make_float4(0.f, 0.f, 0.f, 0.f);
         const float pv[3] = {pp.x, pp.y, pp.z};
         float gq[K][3], gp[K][12];
 #pragma unroll
@@ -139,10 +141,10 @@ __device__ __forceinline__ void sweep_vjp(const TapeView& T, const float (&px)[K
             const float qx = fmaf(r0.x, px[k], fmaf(r0.y, py[k], fmaf(r0.z, pz[k], r0.w)));
             const float qy = fmaf(r1.x, px[k], fmaf(r1.y, py[k], fmaf(r1.z, pz[k], r1.w)));
             const float qz = fmaf(r2.x, px[k], fmaf(r2.y, py[k], fmaf(r2.z, pz[k], r2.w)));
-            raw[k] = prim_grad(op, T.par + prim_rec, qx, qy, qz, gq[k], gp[k]);
+            raw[k] = prim_grad(op, spar + prim_rec, qx, qy, qz, gq[k], gp[k]);
         }
         posts_forward<K>(head, pv, raw, y, sg);
-        child_adjoint<K>(fold, ins.z, cur, abar, y, a);
+        child_adjoint<K>(fold, ordinal, cur, abar, y, a);
         posts_backward<K>(head, sg, a, gpost);
         // a[k] is now the adjoint of the leaf's raw value.  Record layout of the 32 partials:
         // [0,12) frame rows (A_r0 A_r1 A_r2 b_r), [12,24) primitive record, [24,27) post params.

@@ -1,8 +1,9 @@
 """``torch.library`` custom ops over the C ABI (``include/rm_b200.h``).
 
-Forward ops take the lowered tape as two tensors (``code`` int32, ``par`` float32) so that
-autograd sees ``par`` as an ordinary differentiable input; ``tape.lower_theta`` connects it to
-the scene's ``nn.Parameter`` objects.  Backward ops are registered with ``register_autograd``
+Forward ops take the lowered tape as two tensors (``code``: HOST int32 instruction words that the
+library copies into the launch parameters; ``par``: device float32) so that autograd sees ``par``
+as an ordinary differentiable input; ``tape.lower_theta`` connects it to the scene's
+``nn.Parameter`` objects.  Backward ops are registered with ``register_autograd``
 (see the bottom of this file).  Nothing here computes on the CPU: non-CUDA tensors raise.
 """
 from __future__ import annotations
@@ -14,7 +15,8 @@ import torch
 from torch import Tensor
 
 from . import _lib
-from ._lib import RmCamera, RmRenderArgs, RmRenderOut, RmTape, check, lib, ptr, stream_ptr
+from ._lib import (RmCamera, RmRenderArgs, RmRenderGrads, RmRenderOut, RmTape, check, lib, ptr,
+                   stream_ptr)
 
 MODES = ["lambertian", "distance", "proximity", "vignette", "normal", "laplacian",
          "tangent", "spin"]
@@ -23,6 +25,8 @@ NORMALISED_MODES = (1 << 1) | (1 << 2) | (1 << 5)
 
 
 def _tape_struct(code: Tensor, par: Tensor, n_nodes: int, max_depth: int) -> RmTape:
+    if code.is_cuda or code.dtype != torch.int32 or not code.is_contiguous():
+        raise _lib.RmError("tape code must be a contiguous int32 HOST tensor (tape.code_tensor())")
     return RmTape(ptr(code), ptr(par), code.shape[0], par.numel(), max_depth, n_nodes)
 
 
@@ -209,17 +213,12 @@ def shade_finalize(res: RenderResult, mode_mask: int, display_mode: int = -1) ->
 
 
 def pose_records(orientations: Tensor, translations: Tensor) -> Tensor:
-    """``(N,4),(N,3) -> (N,20)`` pose records: R(q) row-major, t, forward axis, q, pad.
-
-    ``R`` is the rotation polynomial of ``Q.rotation`` (ray_marching.py:58-63); ``fwd`` is the
-    third column of ``QuaternionToSO3(q)`` (quaternion.py:114-124) used by the vignette shader."""
-    from . import quaternion as Q
+    """``(N,4),(N,3) -> (N,8)`` pose records ``(q, t, 0)`` (differentiable: one concatenate).  The
+    kernels expand them to the rotation polynomial of ``Q.rotation`` (ray_marching.py:58-63) and
+    the forward axis of ``QuaternionToSO3`` (quaternion.py:114-124)."""
     _lib.require_cuda(orientations, translations)
-    R = Q.rotation_matrix(orientations).reshape(-1, 9)
-    w, x, y, z = orientations.unbind(-1)
-    fwd = torch.stack([2 * (w * y + x * z), 2 * (y * z - w * x), w * w - x * x - y * y + z * z], -1)
-    pad = torch.zeros_like(w)[:, None]
-    return torch.cat([R, translations, fwd, orientations, pad], dim=-1).contiguous()
+    pad = torch.zeros_like(orientations[:, :1])
+    return torch.cat([orientations, translations, pad], dim=-1).contiguous()
 
 
 # ------------------------------------------------------------------------------ backward ops
@@ -263,7 +262,7 @@ def _march_bwd(code: Tensor, par: Tensor, origin: Tensor, dirs: Tensor, grad_pos
     dev = _lib.require_cuda(par, origin, dirs, grad_pos)
     o, v, g = _flat3(origin), _flat3(dirs), _flat3(grad_pos)
     n = o.shape[0]
-    traj = torch.empty(max(steps, 1) * n * 3, device=dev, dtype=torch.float32)
+    traj = torch.empty(max(int(lib().rm_bwd_scratch_floats(n, steps)), 1), device=dev, dtype=torch.float32)
     do, dv = torch.empty_like(o), torch.empty_like(v)
     dpar = torch.empty_like(par)
     tape = _tape_struct(code, par, n_nodes, max_depth)
@@ -293,5 +292,93 @@ def _march_backward(ctx, grad):
 
 
 _march.register_autograd(_march_backward, setup_context=_march_setup)
+
+
+# ------------------------------------------------------------------------------ fused G-buffer
+@torch.library.custom_op("rm_b200::render_gbuffer", mutates_args=())
+def _render_gbuffer(code: Tensor, par: Tensor, poses: Tensor, n_views: int, width: int, height: int,
+                    focal: float, sensor_w: float, sensor_h: float, steps: int, eps: float,
+                    n_nodes: int, max_depth: int) -> Tuple[Tensor, Tensor, Tensor, Tensor, Tensor, Tensor]:
+    dev = _lib.require_cuda(par, poses)
+    n = n_views * width * height
+    new = lambda *shape: torch.empty(*shape, device=dev, dtype=torch.float32)
+    origin, dirs, pos, nrm = new(n, 3), new(n, 3), new(n, 3), new(n, 3)
+    sdf, lap = new(n), new(n)
+    o = RmRenderOut()
+    o.origin, o.dirs, o.pos, o.sdf, o.normals, o.laplacian = (ptr(origin), ptr(dirs), ptr(pos), ptr(sdf),
+                                                              ptr(nrm), ptr(lap))
+    poses = poses.contiguous()
+    a = RmRenderArgs(0, n, int(steps), 0, float(eps), 0.0, 0.0, 0, -1, 1, 0, 0, 0)   # IEEE math
+    cam = camera_struct(n_views, width, height, focal, sensor_w, sensor_h)
+    t = _tape_struct(code, par, n_nodes, max_depth)
+    check(lib().rm_render(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(o),
+                          stream_ptr(dev)), "rm_render")
+    return origin, dirs, pos, sdf, nrm, lap
+
+
+@_render_gbuffer.register_fake
+def _(code, par, poses, n_views, width, height, focal, sensor_w, sensor_h, steps, eps, n_nodes, max_depth):
+    n = n_views * width * height
+    v3 = lambda: poses.new_empty(n, 3)
+    return v3(), v3(), v3(), poses.new_empty(n), v3(), poses.new_empty(n)
+
+
+@torch.library.custom_op("rm_b200::render_bwd", mutates_args=())
+def _render_bwd(code: Tensor, par: Tensor, poses: Tensor, n_views: int, width: int, height: int,
+                focal: float, sensor_w: float, sensor_h: float, steps: int, eps: float,
+                g_origin: Optional[Tensor], g_dirs: Optional[Tensor], g_pos: Optional[Tensor],
+                g_sdf: Optional[Tensor], g_normals: Optional[Tensor], g_lap: Optional[Tensor],
+                n_nodes: int, max_depth: int) -> Tuple[Tensor, Tensor]:
+    dev = _lib.require_cuda(par, poses, g_origin, g_dirs, g_pos, g_sdf, g_normals, g_lap)
+    n = n_views * width * height
+    cont = lambda g: None if g is None else g.contiguous()
+    gs = [cont(g) for g in (g_origin, g_dirs, g_pos, g_sdf, g_normals, g_lap)]
+    grads = RmRenderGrads(*[ptr(g) for g in gs])
+    traj = torch.empty(max(int(lib().rm_bwd_scratch_floats(n, steps)), 1), device=dev, dtype=torch.float32)
+    dpar = torch.empty_like(par)
+    poses = poses.contiguous()
+    dposes = torch.empty_like(poses)
+    a = RmRenderArgs(0, n, int(steps), 0, float(eps), 0.0, 0.0, 0, -1, 1, 0, 0, 0)
+    cam = camera_struct(n_views, width, height, focal, sensor_w, sensor_h)
+    t = _tape_struct(code, par, n_nodes, max_depth)
+    check(lib().rm_render_bwd(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(grads),
+                              ptr(traj), ptr(dpar), ptr(dposes), stream_ptr(dev)), "rm_render_bwd")
+    return dpar, dposes
+
+
+@_render_bwd.register_fake
+def _(code, par, poses, n_views, width, height, focal, sensor_w, sensor_h, steps, eps, g_origin, g_dirs,
+      g_pos, g_sdf, g_normals, g_lap, n_nodes, max_depth):
+    return torch.empty_like(par), torch.empty_like(poses)
+
+
+def _gbuffer_setup(ctx, inputs, output):
+    ctx.set_materialize_grads(False)            # unused planes arrive as None -> skipped in the kernel
+    ctx.save_for_backward(inputs[0], inputs[1], inputs[2])
+    ctx.meta = inputs[3:]
+
+
+def _gbuffer_backward(ctx, g_origin, g_dirs, g_pos, g_sdf, g_normals, g_lap):
+    code, par, poses = ctx.saved_tensors
+    (n_views, width, height, focal, sw, sh, steps, eps, n_nodes, max_depth) = ctx.meta
+    dpar, dposes = _render_bwd(code, par, poses, n_views, width, height, focal, sw, sh, steps, eps,
+                               g_origin, g_dirs, g_pos, g_sdf, g_normals, g_lap, n_nodes, max_depth)
+    return (None, dpar, dposes) + (None,) * 10
+
+
+_render_gbuffer.register_autograd(_gbuffer_backward, setup_context=_gbuffer_setup)
+
+
+def render_gbuffer(tape, cam: RmCamera, orientations: Tensor, translations: Tensor, steps: int = 32,
+                   normals_eps: float = 5e-2):
+    """Differentiable fused G-buffer: ``(origin, dirs, pos, sdf, normals, laplacian)``, flat ray-major.
+    One forward kernel (IEEE math) and one backward kernel (``rm_render_bwd``) that returns the
+    gradients of the scene parameters and of the camera quaternion / translation."""
+    dev = _lib.require_cuda(orientations, translations)
+    poses = pose_records(orientations, translations)
+    return _render_gbuffer(tape.code_tensor(dev), tape.lowered_params(dev), poses, cam.n_views, cam.width,
+                           cam.height, cam.focal_length, cam.sensor_width, cam.sensor_height, int(steps),
+                           float(normals_eps), tape.n_nodes, tape.max_depth)
+
 
 BACKWARD_READY = True

@@ -4,10 +4,13 @@ The reference evaluates a scene by recursive ``nn.Module`` calls that materialis
 ``(N,H,W,k)`` tensor per torch op (``scene/transformations.py:33-41,67-71,90-94``).  Here the
 tree is walked once and turned into
 
-* ``code``  int32 ``(n_instr, 4)``: ``(head, param_offset/4, ordinal_in_parent, node_id | frame_record)``
-* ``par``   float32 ``(n_par,)``: per-instruction parameter records, 16-byte aligned,
+* ``code``  int32 ``(n_instr, 2)``: ``(head | ordinal << 16, param_offset/4 | node_id << 16)``
+* ``par``   float32 ``(n_par,)``: per-instruction parameter records, 16-byte aligned.
 
-which the per-ray CUDA interpreter (``csrc/rm_eval.cuh``) executes from shared memory.
+``code`` is static host data: the C ABI copies it into the kernel-parameter block of every
+launch (constant bank), so the per-ray CUDA interpreter (``csrc/rm_eval.cuh``) decodes it on the
+warp-uniform datapath; ``par`` changes under an optimiser, lives on the device and is staged
+into shared memory by each block.
 
 Lowering rules
 --------------
@@ -15,7 +18,8 @@ Lowering rules
   world->local frame ``q = A p + b`` (``A = R(conj(q_n)) ... R(conj(q_1))``).  ``R`` is the same
   polynomial in the (un-normalised) quaternion as ``quaternion.rotation``
   (``quaternion.py:55-72``), so values *and* d/dq agree with the reference for non-unit q.
-  A leaf loads a new frame only when it differs from the one currently held in registers.
+  Every leaf below an affine carries its own copy of the composed frame (3 float4 rows), so an
+  instruction is self-contained; autograd sums the copies' gradients through the gather.
 * **Unary value ops** (rounding ``f - rho``, onion ``|f| - r``; ``transformations.py:117-118``,
   ``:131-132``) are attached as post-ops to the leaf / union-close instruction they act on.
 * **Unions** become ``OPEN`` ... children ... ``CLOSE``; every child instruction carries the fold
@@ -42,12 +46,15 @@ from . import quaternion as Q
 # ---- instruction encoding (mirrored in csrc/rm_tape.h) -------------------------------------
 OP_SPHERE, OP_BOX, OP_PLANE, OP_LINE, OP_DISK, OP_TORUS = 1, 2, 3, 4, 5, 6
 OP_OPEN_MIN, OP_OPEN_SMOOTH, OP_CLOSE_MIN, OP_CLOSE_SMOOTH = 8, 9, 10, 11
-FRAME_KEEP, FRAME_WORLD, FRAME_NEW = 0, 1, 2
 FOLD_NONE, FOLD_MIN, FOLD_SMOOTH = 0, 1, 2
 POST_ROUND, POST_ONION = 1, 2
 MAX_POST = 3
-HEAD_ROOT = 1 << 16     # OPEN/CLOSE of the outermost union: no accumulator save/restore
-MAX_DEPTH = 8          # union nesting depth supported by the interpreter's spill stack
+HEAD_FRAME = 1 << 4     # leaf: a world->local frame record (3 float4) precedes the primitive record
+HEAD_ROOT = 1 << 7      # OPEN/CLOSE of the outermost union: no accumulator save/restore
+MAX_DEPTH = 8           # union nesting depth supported by the interpreter's spill stack
+MAX_INSTR = 1024        # largest kernel-parameter code block (csrc/rm_tape.h)
+MAX_ORDINAL = 0xFFFF    # children per union
+MAX_PAR_F4 = 0xFFFF     # parameter records addressable by an instruction (float4 units)
 
 _PRIM_OP = {"SDFSphere": OP_SPHERE, "SDFBox": OP_BOX, "SDFPlane": OP_PLANE,
             "SDFLine": OP_LINE, "SDFDisk": OP_DISK, "SDFTorus": OP_TORUS}
@@ -57,11 +64,22 @@ _PRIM_FLOPS = {OP_SPHERE: 7, OP_BOX: 19, OP_PLANE: 0, OP_LINE: 23, OP_DISK: 10, 
 AFFINE_FLOPS, ROUND_FLOPS, ONION_FLOPS = 33, 1, 2
 
 
-def encode_head(op, frame=0, fold=0, posts=()):
-    head = op | (frame << 4) | (fold << 6) | (len(posts) << 8)
+def encode_head(op, frame=False, fold=0, posts=()):
+    """Low 16 bits of word 0: op[0:4] frame[4] fold[5:7] root[7] npost[8:10] post kinds[10:16]."""
+    head = op | (HEAD_FRAME if frame else 0) | (fold << 5) | (len(posts) << 8)
     for i, kind in enumerate(posts):
         head |= kind << (10 + 2 * i)
     return head
+
+
+def decode(word0: int, word1: int):
+    """(op, has_frame, fold, root, post kinds, ordinal, par offset in float4, node id)."""
+    word0 &= 0xFFFFFFFF
+    word1 &= 0xFFFFFFFF
+    npost = (word0 >> 8) & 3
+    posts = [(word0 >> (10 + 2 * i)) & 3 for i in range(npost)]
+    return (word0 & 15, bool(word0 & HEAD_FRAME), (word0 >> 5) & 3, bool(word0 & HEAD_ROOT), posts,
+            word0 >> 16, word1 & 0xFFFF, word1 >> 16)
 
 
 class _Src:
@@ -97,7 +115,6 @@ class Tape:
         self._src: List[tuple] = []        # per par float: (piece, index)
         self._affines: List[_Affine] = []
         self._lines: List[tuple] = []      # (start_slot, end_slot)
-        self._cur_frame: Optional[int] = None   # None: nothing loaded yet; -1: world
         self.n_nodes = 0
         self.n_leaves = 0
         self.max_depth = 0
@@ -107,16 +124,29 @@ class Tape:
         self._ord = [0]                     # next child ordinal of every open union (root: dummy)
         self._emit(root, frame=-1, fold=FOLD_NONE, posts=[], depth=0)
 
-        self.code = np.asarray(self._code, dtype=np.int32).reshape(-1, 4)
-        self.n_instr = self.code.shape[0]
+        self.n_instr = len(self._code)
         self.n_par = len(self._src)
         assert self.n_par % 4 == 0
+        if self.n_instr > MAX_INSTR:
+            raise NotImplementedError(
+                f"scene lowers to {self.n_instr} instructions; the kernels take at most {MAX_INSTR}")
+        if self.n_par // 4 > MAX_PAR_F4:
+            raise NotImplementedError("scene parameter block exceeds the 16-bit record offsets")
+        words = []
+        for head, off4, ordinal, node in self._code:
+            if ordinal > MAX_ORDINAL:
+                raise NotImplementedError(f"a union with more than {MAX_ORDINAL} children")
+            words.append([head | (ordinal << 16), off4 | (node << 16)])
+        # uint32 bit patterns stored as int32 (two's complement), contiguous (n_instr, 2)
+        self.code = np.ascontiguousarray(np.asarray(words, dtype=np.uint32).reshape(-1, 2)
+                                         .view(np.int32))
         if self.max_depth > MAX_DEPTH:
             raise NotImplementedError(
                 f"union nesting depth {self.max_depth} exceeds the interpreter limit {MAX_DEPTH}")
         self._finalise_recipe()
         self._dev_cache = {}
         self._par_cache = None
+        self._code_host = None
 
     # ------------------------------------------------------------------ tree walk
     def _slot(self, p: nn.Parameter) -> int:
@@ -192,7 +222,7 @@ class Tape:
             kinds, entries = self._post_record(posts)
             off4 = self._f4(entries) if kinds else 0
             op = OP_CLOSE_SMOOTH if smooth else OP_CLOSE_MIN
-            self._code.append([encode_head(op, 0, fold, kinds) | root, off4, ordinal, node_id])
+            self._code.append([encode_head(op, False, fold, kinds) | root, off4, ordinal, node_id])
             return
         if kind not in _PRIM_OP:
             raise NotImplementedError(f"cannot lower scene node of type {kind}")
@@ -200,18 +230,8 @@ class Tape:
         self.flops_per_eval += _PRIM_FLOPS[op]
         self.n_leaves += 1
         self.leaf_kinds.append(op)
-        if frame == self._cur_frame:
-            fmode = FRAME_KEEP
-        elif frame < 0:
-            fmode = FRAME_WORLD
-        else:
-            fmode = FRAME_NEW
-        self._cur_frame = frame
-        if frame < 0:
-            self._cur_frame_rec = -1
         first = len(self._src) // 4
-        if fmode == FRAME_NEW:
-            self._cur_frame_rec = first
+        if frame >= 0:
             for r in range(3):
                 self._f4([("A", frame * 9 + r * 3 + c) for c in range(3)] + [("b", frame * 3 + r)])
         if op == OP_SPHERE:
@@ -231,10 +251,7 @@ class Tape:
         kinds, entries = self._post_record(posts)
         if kinds:
             self._f4(entries)
-        # 4th word: float4 offset of the frame record this leaf is evaluated in (-1: world);
-        # lets the reverse sweep of the backward kernel rebuild q without replaying FRAME_KEEP chains
-        self._code.append([encode_head(op, fmode, fold, kinds), first, self._next_ordinal(),
-                           self._cur_frame_rec])
+        self._code.append([encode_head(op, frame >= 0, fold, kinds), first, self._next_ordinal(), 0])
 
     # ------------------------------------------------------------------ lowering recipe
     def _finalise_recipe(self):
@@ -271,7 +288,6 @@ class Tape:
                 perm=mv(self._perm), q_idx=mv(self._q_idx), t_idx=mv(self._t_idx),
                 ls_idx=mv(self._ls_idx), le_idx=mv(self._le_idx),
                 levels=[(mv(a), mv(b)) for a, b in self._levels],
-                code=torch.from_numpy(self.code.copy()).to(device).contiguous(),
             )
         return self._dev_cache[key]
 
@@ -280,7 +296,11 @@ class Tape:
         return self.params[0].device if self.params else torch.device("cpu")
 
     def code_tensor(self, device=None) -> torch.Tensor:
-        return self._on(device or self.device)["code"]
+        """The instruction words as a HOST int32 tensor ``(n_instr, 2)`` (``device`` is ignored: the
+        C ABI reads the code on the host and passes it to the kernels by value)."""
+        if self._code_host is None:
+            self._code_host = torch.from_numpy(self.code)
+        return self._code_host
 
     def theta(self, device=None) -> torch.Tensor:
         """Flat view of the current raw parameters (autograd-connected)."""

@@ -19,22 +19,19 @@ def run(tape, par, pts):
     code = tape.code
     f4 = par.reshape(-1, 4)
     x, y, z = pts.unbind(-1)
-    qx, qy, qz = x, y, z
     stack, acc = [], None
     d = None
-    for head, off, ordinal, node in code.tolist():
-        op = head & 15
+    for w0, w1 in code.tolist():
+        op, has_frame, fold, _root, posts, _ordinal, off, _node = T.decode(w0, w1)
         P = off
         if op < T.OP_OPEN_MIN:
-            fm = (head >> 4) & 3
-            if fm == T.FRAME_NEW:
+            qx, qy, qz = x, y, z
+            if has_frame:
                 r0, r1, r2 = f4[P], f4[P + 1], f4[P + 2]
                 P += 3
                 qx = r0[0] * x + r0[1] * y + r0[2] * z + r0[3]
                 qy = r1[0] * x + r1[1] * y + r1[2] * z + r1[3]
                 qz = r2[0] * x + r2[1] * y + r2[2] * z + r2[3]
-            elif fm == T.FRAME_WORLD:
-                qx, qy, qz = x, y, z
             if op == T.OP_SPHERE:
                 d = _len(qx, qy, qz) - f4[P][0]
             elif op == T.OP_BOX:
@@ -73,11 +70,8 @@ def run(tape, par, pts):
             else:
                 d = (acc[1] + torch.log(acc[2])) / acc[3]
             acc = stack.pop()
-        npost = (head >> 8) & 3
-        for i in range(npost):
-            kind = (head >> (10 + 2 * i)) & 3
+        for i, kind in enumerate(posts):
             d = (d.abs() if kind == T.POST_ONION else d) - f4[P][i]
-        fold = (head >> 6) & 3
         if fold == T.FOLD_MIN:
             acc[1] = d if acc[1] is None else torch.where(d < acc[1], d, acc[1])   # first child wins ties
         elif fold == T.FOLD_SMOOTH:

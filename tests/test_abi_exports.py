@@ -29,6 +29,7 @@ def test_struct_layout_matches_header():
     assert ctypes.sizeof(_lib.RmCamera) == 24
     assert ctypes.sizeof(_lib.RmRenderOut) == 16 * 8
     assert ctypes.sizeof(_lib.RmRenderArgs) == 64
+    assert ctypes.sizeof(_lib.RmRenderGrads) == 48
 
 
 def test_argument_errors_do_not_need_a_gpu():

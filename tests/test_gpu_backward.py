@@ -170,3 +170,74 @@ def test_render_loop_forward_is_differentiable_in_every_finite_mode():
             assert rel_err(t.grad, tr.grad) < 2e-3, mode
             assert rel_err(flat_grads(list(scene.parameters())),
                            flat_grads(list(ref_scene.parameters()))) < 2e-3, mode
+
+
+@pytest.mark.parametrize("tag,build", [("scene2", S.make_test_scene2),
+                                       ("syn8", lambda: S.make_synthetic_scene(8, 0, True))])
+def test_fused_render_bwd_matches_reference_fixture(golden, tag, build):
+    """Same config-4 loss through the FUSED path (RenderLoop.gbuffer: one forward kernel + one
+    rm_render_bwd kernel that also produces the camera quaternion / translation gradients)."""
+    g = golden("grads")
+    scene = build()
+    loop = RenderLoop(scene, normals_eps=5e-2, **cases.config1_camera(16, 16)).to(DEV)
+    q = t32(g[f"grads/{tag}/q"]).to(DEV).requires_grad_(True)
+    t = t32(g[f"grads/{tag}/t"]).to(DEV).requires_grad_(True)
+    gb = loop.gbuffer(q, t, 32)
+    lam = (-(gb["dirs"] * gb["normals"]).sum(-1, keepdim=True)).clamp(0, 1)
+    depth = (gb["pos"] - gb["origin"]).norm(dim=-1, keepdim=True)
+    loss = ((lam - t32(g[f"grads/{tag}/lam_target"]).to(DEV)) ** 2).mean() + \
+           ((depth - t32(g[f"grads/{tag}/depth_target"]).to(DEV)) ** 2).mean()
+    assert abs(loss.item() - float(g[f"grads/{tag}/loss"])) < 1e-4 * max(1.0, float(g[f"grads/{tag}/loss"]))
+    loss.backward()
+    assert rel_err(q.grad, g[f"grads/{tag}/dq"]) < 1e-3
+    assert rel_err(t.grad, g[f"grads/{tag}/dt"]) < 1e-3
+    assert rel_err(flat_grads(list(scene.parameters())), g[f"grads/{tag}/dparams_flat"]) < 1e-3
+
+
+def test_fused_render_bwd_every_plane_and_two_views():
+    """Random upstream gradients on every G-buffer plane, two cameras (per-view dq/dt), odd image
+    size (tail lanes): fused backward vs torch.autograd through the oracle."""
+    intr = dict(cases.config1_camera(23, 9))
+    intr["num_cameras"] = 2
+    scene, ref_scene = S.make_test_scene2(), S.make_test_scene2()
+    loop = RenderLoop(scene, normals_eps=5e-2, **intr).to(DEV)
+    orc = O.RenderLoopOracle(ref_scene, normals_eps=5e-2, **intr)
+    q0 = torch.nn.functional.normalize(torch.tensor([[0.99, 0.03, -0.08, 0.05], [0.97, -0.1, 0.12, 0.02]]), dim=-1)
+    t0 = torch.tensor([[0.05, 0.1, 1.0], [-0.1, 0.0, 0.9]])
+    q, t = q0.to(DEV).requires_grad_(True), t0.to(DEV).requires_grad_(True)
+    qr, tr = q0.clone().requires_grad_(True), t0.clone().requires_grad_(True)
+    gb = loop.gbuffer(q, t, 32)
+    ref = orc.gbuffer(qr, tr, 32)
+    ref = {"origin": ref["px"], "dirs": ref["dirs"], "pos": ref["pos"], "sdf": ref["dists"],
+           "normals": ref["normals"], "laplacian": ref["lap"]}
+    gen = torch.Generator().manual_seed(11)
+    loss = loss_ref = 0.0
+    for name, scale in [("origin", 1.0), ("dirs", 1.0), ("pos", 1.0), ("sdf", 1.0), ("normals", 1.0),
+                        ("laplacian", 1e-3)]:
+        w = torch.randn(ref[name].shape, generator=gen) * scale
+        np.testing.assert_allclose(gb[name].detach().cpu().numpy(), ref[name].detach().numpy(),
+                                   rtol=2e-3 if name == "laplacian" else 1e-4,
+                                   atol=2e-2 if name == "laplacian" else 1e-5)
+        loss = loss + (gb[name] * w.to(DEV)).sum()
+        loss_ref = loss_ref + (ref[name] * w).sum()
+    loss.backward()
+    loss_ref.backward()
+    assert rel_err(q.grad, qr.grad) < 2e-3
+    assert rel_err(t.grad, tr.grad) < 2e-3
+    assert rel_err(flat_grads(list(scene.parameters())), flat_grads(list(ref_scene.parameters()))) < 2e-3
+
+
+def test_fused_render_bwd_unused_planes_are_skipped():
+    """Only the marched position is used: gradients still match (stencil sweeps skipped)."""
+    intr = cases.config1_camera(32, 20)
+    scene, ref_scene = S.make_test_scene2(), S.make_test_scene2()
+    loop = RenderLoop(scene, normals_eps=5e-2, **intr).to(DEV)
+    orc = O.RenderLoopOracle(ref_scene, normals_eps=5e-2, **intr)
+    q0 = torch.nn.functional.normalize(torch.tensor([[0.99, 0.03, -0.08, 0.05]]), dim=-1)
+    t0 = torch.tensor([[0.05, 0.1, 1.0]])
+    q, t = q0.to(DEV).requires_grad_(True), t0.to(DEV).requires_grad_(True)
+    qr, tr = q0.clone().requires_grad_(True), t0.clone().requires_grad_(True)
+    (loop.gbuffer(q, t, 32)["pos"] ** 2).mean().backward()
+    (orc.gbuffer(qr, tr, 32)["pos"] ** 2).mean().backward()
+    assert rel_err(q.grad, qr.grad) < 2e-3 and rel_err(t.grad, tr.grad) < 2e-3
+    assert rel_err(flat_grads(list(scene.parameters())), flat_grads(list(ref_scene.parameters()))) < 2e-3

@@ -63,11 +63,15 @@ def test_flops_per_eval_match_survey_table():
 def test_tape_structure_and_errors():
     t = T.Tape(S.make_test_scene2())
     assert t.n_nodes == 1 and t.max_depth == 1 and t.n_leaves == 4   # inner hard union is flattened
-    assert t.code.dtype == np.int32 and t.code.shape[1] == 4 and t.n_par % 4 == 0
-    ops = [h & 15 for h in t.code[:, 0]]
-    assert ops == [T.OP_OPEN_MIN, T.OP_BOX, T.OP_SPHERE, T.OP_TORUS, T.OP_LINE, T.OP_CLOSE_MIN]
-    assert list(t.code[1:5, 2]) == [0, 1, 2, 3]            # child ordinals of the merged union
-    assert t.code[0, 0] & T.HEAD_ROOT and t.code[-1, 0] & T.HEAD_ROOT
+    assert t.code.dtype == np.int32 and t.code.shape[1] == 2 and t.n_par % 4 == 0
+    dec = [T.decode(w0, w1) for w0, w1 in t.code.tolist()]
+    assert [d[0] for d in dec] == [T.OP_OPEN_MIN, T.OP_BOX, T.OP_SPHERE, T.OP_TORUS, T.OP_LINE,
+                                   T.OP_CLOSE_MIN]
+    assert [d[5] for d in dec[1:5]] == [0, 1, 2, 3]        # child ordinals of the merged union
+    assert dec[0][3] and dec[-1][3]                        # root flag on the outermost OPEN/CLOSE
+    assert dec[1][4] == [T.POST_ONION] and not dec[1][1]   # onion post-op on the box, world frame
+    a = T.Tape(S.make_test_scene())
+    assert sum(T.decode(*w)[1] for w in a.code.tolist()) == 3     # three leaves carry a frame record
     # parameter order follows module.parameters(), so optimisers / state_dict carry over
     assert [n for n, _ in S.make_test_scene().named_parameters()][:3] == [
         "blend_k", "sdfs.0.translation", "sdfs.0.orientation"]
