@@ -12,7 +12,8 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "librm_b200.so")
+# RM_B200_LIB: alternative build of the same ABI (kernel tuning experiments)
+LIB_PATH = os.environ.get("RM_B200_LIB") or os.path.join(_HERE, "csrc", "librm_b200.so")
 
 POSE_STRIDE = 8
 REDUCE_FLOATS = 8

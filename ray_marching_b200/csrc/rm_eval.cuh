@@ -40,8 +40,10 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
 #pragma unroll
     for (int k = 0; k < K; ++k) { a0[k] = 0.f; a1[k] = 0.f; d[k] = 0.f; }
 
+    int2 nxt = C.ins[0];
     for (int pc = 0; pc < n_instr; ++pc) {
-        const int2 ins = C.ins[pc];
+        const int2 ins = nxt;
+        nxt = C.ins[pc + 1 < n_instr ? pc + 1 : pc];   // prefetch: hides the constant-load latency
         const int head = ins.x;
         const float4* P = spar + word_par(ins.y);
         const int op = head_op(head);

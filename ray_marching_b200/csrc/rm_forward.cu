@@ -2,7 +2,11 @@
 //
 // Thread mapping: every thread owns K consecutive rays (pixels), so a warp covers 32*K
 // consecutive pixels of a row: coherent rays, 128-bit stores for 1-channel planes and three
-// 128-bit stores per 4 rays for 3-channel planes.  The tape's instruction words arrive in the
+// 128-bit stores per 4 rays for 3-channel planes.  K = 4 rays x 128 threads with the register
+// budget capped at 64 (8 resident blocks = 32 warps per SM) measured best on B200: the path is
+// bound by the latency of the decode -> parameter load -> MUFU chains, which resident warps hide
+// (profiles/r01: K=4/154 regs 0.65 ms, K=8/229 regs 0.60 ms, K=2/64 regs 0.59 ms, K=4/64 regs
+// 0.45 ms on config 2).  The tape's instruction words arrive in the
 // kernel-parameter block (uniform-datapath decode), its parameters are staged once per block
 // into shared memory, and the interpreter (rm_eval.cuh) keeps all ray state in registers.
 #include <cuda_runtime.h>
@@ -15,21 +19,39 @@
 #include "rm_host.h"
 #include "rm_shade.cuh"
 
+#ifndef RM_K
+#define RM_K 4
+#endif
+#ifndef RM_BLOCK
+#define RM_BLOCK 128
+#endif
+#ifndef RM_MINB
+#define RM_MINB 8
+#endif
+
 namespace rm {
 
-constexpr int K = 4;            // rays per thread (multiple of 4: float4 plane I/O)
-constexpr int BLOCK = 128;      // threads per block -> 512 rays per block
+constexpr int K = RM_K;         // rays per thread (multiple of 4: float4 plane I/O)
+constexpr int BLOCK = RM_BLOCK; // threads per block
 
 // ---- small vector I/O helpers: thread t owns elements [K t, K t + K) ------------------------
+// K = 4g: 128-bit accesses; K = 2: 64-bit accesses (still fully coalesced across the warp).
 __device__ __forceinline__ void load3(const float* base, int64_t first, int64_t n, float (&x)[K],
                                       float (&y)[K], float (&z)[K]) {
     if (first + K <= n) {
+        if constexpr (K % 4 == 0) {
 #pragma unroll
-        for (int g = 0; g < K; g += 4) {
-            const float4* p = reinterpret_cast<const float4*>(base + (first + g) * 3);
-            const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
-            x[g] = a.x; y[g] = a.y; z[g] = a.z; x[g + 1] = a.w; y[g + 1] = b.x; z[g + 1] = b.y;
-            x[g + 2] = b.z; y[g + 2] = b.w; z[g + 2] = c.x; x[g + 3] = c.y; y[g + 3] = c.z; z[g + 3] = c.w;
+            for (int g = 0; g < K; g += 4) {
+                const float4* p = reinterpret_cast<const float4*>(base + (first + g) * 3);
+                const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+                x[g] = a.x; y[g] = a.y; z[g] = a.z; x[g + 1] = a.w; y[g + 1] = b.x; z[g + 1] = b.y;
+                x[g + 2] = b.z; y[g + 2] = b.w; z[g + 2] = c.x; x[g + 3] = c.y; y[g + 3] = c.z; z[g + 3] = c.w;
+            }
+        } else {
+            static_assert(K % 4 == 0 || K == 2, "K must be 2 or a multiple of 4");
+            const float2* p = reinterpret_cast<const float2*>(base + first * 3);
+            const float2 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+            x[0] = a.x; y[0] = a.y; z[0] = b.x; x[K - 1] = b.y; y[K - 1] = c.x; z[K - 1] = c.y;
         }
     } else {
 #pragma unroll
@@ -45,12 +67,17 @@ __device__ __forceinline__ void store3(float* base, int64_t first, int64_t n, co
                                        const float (&y)[K], const float (&z)[K]) {
     if (base == nullptr) return;
     if (first + K <= n) {
+        if constexpr (K % 4 == 0) {
 #pragma unroll
-        for (int g = 0; g < K; g += 4) {
-            float4* p = reinterpret_cast<float4*>(base + (first + g) * 3);
-            p[0] = make_float4(x[g], y[g], z[g], x[g + 1]);
-            p[1] = make_float4(y[g + 1], z[g + 1], x[g + 2], y[g + 2]);
-            p[2] = make_float4(z[g + 2], x[g + 3], y[g + 3], z[g + 3]);
+            for (int g = 0; g < K; g += 4) {
+                float4* p = reinterpret_cast<float4*>(base + (first + g) * 3);
+                p[0] = make_float4(x[g], y[g], z[g], x[g + 1]);
+                p[1] = make_float4(y[g + 1], z[g + 1], x[g + 2], y[g + 2]);
+                p[2] = make_float4(z[g + 2], x[g + 3], y[g + 3], z[g + 3]);
+            }
+        } else {
+            float2* p = reinterpret_cast<float2*>(base + first * 3);
+            p[0] = make_float2(x[0], y[0]); p[1] = make_float2(z[0], x[K - 1]); p[2] = make_float2(y[K - 1], z[K - 1]);
         }
     } else {
 #pragma unroll
@@ -65,9 +92,13 @@ __device__ __forceinline__ void store3(float* base, int64_t first, int64_t n, co
 __device__ __forceinline__ void store1(float* base, int64_t first, int64_t n, const float (&x)[K]) {
     if (base == nullptr) return;
     if (first + K <= n) {
+        if constexpr (K % 4 == 0) {
 #pragma unroll
-        for (int g = 0; g < K; g += 4)
-            *reinterpret_cast<float4*>(base + first + g) = make_float4(x[g], x[g + 1], x[g + 2], x[g + 3]);
+            for (int g = 0; g < K; g += 4)
+                *reinterpret_cast<float4*>(base + first + g) = make_float4(x[g], x[g + 1], x[g + 2], x[g + 3]);
+        } else {
+            *reinterpret_cast<float2*>(base + first) = make_float2(x[0], x[K - 1]);
+        }
     } else {
 #pragma unroll
         for (int k = 0; k < K; ++k)
@@ -126,19 +157,7 @@ __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_inst
                                            const float (&vx)[K], const float (&vy)[K],
                                            const float (&vz)[K]) {
     float d[K];
-    if (!early_exit) {
-        for (int s = 0; s < steps; ++s) {
-            eval_scene<K, FAST, CAP>(code, n_instr, spar, px, py, pz, d);
-#pragma unroll
-            for (int k = 0; k < K; ++k) {
-                px[k] = fmaf(d[k], vx[k], px[k]);
-                py[k] = fmaf(d[k], vy[k], py[k]);
-                pz[k] = fmaf(d[k], vz[k], pz[k]);
-            }
-        }
-        return;
-    }
-    for (int s = 0; s < steps; ++s) {
+    for (int s = 0; s < steps; ++s) {                 // one interpreter instance (instruction cache)
         eval_scene<K, FAST, CAP>(code, n_instr, spar, px, py, pz, d);
         bool moved = false;
 #pragma unroll
@@ -146,12 +165,13 @@ __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_inst
             const float nx = fmaf(d[k], vx[k], px[k]);
             const float ny = fmaf(d[k], vy[k], py[k]);
             const float nz = fmaf(d[k], vz[k], pz[k]);
-            moved |= (nx != px[k]) | (ny != py[k]) | (nz != pz[k]);
+            if (early_exit) moved |= (nx != px[k]) | (ny != py[k]) | (nz != pz[k]);
             px[k] = nx; py[k] = ny; pz[k] = nz;
         }
         // A ray whose position did not change is at a fixed point of the update: all further
-        // steps reproduce it bit for bit, so leaving the loop does not change the result.
-        if (!__any_sync(0xffffffffu, moved)) break;
+        // steps reproduce it bit for bit, so leaving the loop (when the whole warp is there) does
+        // not change the result.
+        if (early_exit && !__any_sync(0xffffffffu, moved)) break;
     }
 }
 
@@ -171,7 +191,10 @@ march_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n
     store3(out, first, n, px, py, pz);
 }
 
-// ---- stencil: f at p and at the four tetrahedral offsets -------------------------------------
+// ---- stencil: f at the four tetrahedral offsets, then at p ------------------------------------
+// One call site of the interpreter; the samples are folded into the normal / Laplacian on the fly
+// (o_0, the running sum, and Ainv (o_j - o_0) accumulated column by column, in the reference's
+// summation order) so that no per-sample storage and no sample-dependent branch is needed.
 template <int CAP>
 __device__ __forceinline__ void stencil_eval(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                              const Stencil& st, bool need_offsets,
@@ -179,35 +202,36 @@ __device__ __forceinline__ void stencil_eval(const TapeCode<CAP>& code, int n_in
                                              const float (&pz)[K], float (&f)[K],
                                              float (&nx)[K], float (&ny)[K], float (&nz)[K],
                                              float (&lap)[K]) {
-    float o[4][K];
-    const int first_j = need_offsets ? 0 : 4;
-    for (int j = first_j; j < 5; ++j) {               // one call site: j == 4 is the centre
+    float o0[K], sum[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) { o0[k] = sum[k] = nx[k] = ny[k] = nz[k] = f[k] = 0.f; }
+    for (int j = need_offsets ? 0 : 4; j < 5; ++j) {  // j == 4 is the centre (zero offset / weights)
         float x[K], y[K], z[K], d[K];
-        const float dx = j < 4 ? st.off[j & 3][0] : 0.f;
-        const float dy = j < 4 ? st.off[j & 3][1] : 0.f;
-        const float dz = j < 4 ? st.off[j & 3][2] : 0.f;
+        const float dx = st.off[j][0], dy = st.off[j][1], dz = st.off[j][2];
 #pragma unroll
         for (int k = 0; k < K; ++k) { x[k] = px[k] + dx; y[k] = py[k] + dy; z[k] = pz[k] + dz; }
         eval_scene<K, false, CAP>(code, n_instr, spar, x, y, z, d);
+        const float wx = st.w[j][0], wy = st.w[j][1], wz = st.w[j][2];
+        const float first = st.first[j], in_sum = st.in_sum[j];
 #pragma unroll
         for (int k = 0; k < K; ++k) {
-            if (j == 0) o[0][k] = d[k];
-            else if (j == 1) o[1][k] = d[k];
-            else if (j == 2) o[2][k] = d[k];
-            else if (j == 3) o[3][k] = d[k];
-            else f[k] = d[k];
+            o0[k] = first != 0.f ? d[k] : o0[k];
+            const float dj = d[k] - o0[k];             // o_j - o_0 (ray_marching.py:117)
+            nx[k] = fmaf(wx, dj, nx[k]);
+            ny[k] = fmaf(wy, dj, ny[k]);
+            nz[k] = fmaf(wz, dj, nz[k]);
+            sum[k] = in_sum != 0.f ? sum[k] + d[k] : sum[k];
+            f[k] = d[k];
         }
     }
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-        if (need_offsets) {
-            const float ok[4] = {o[0][k], o[1][k], o[2][k], o[3][k]};
-            float n3[3];
-            stencil_finish(st, ok, f[k], n3, lap[k]);
-            nx[k] = n3[0]; ny[k] = n3[1]; nz[k] = n3[2];
-        } else {
-            nx[k] = ny[k] = nz[k] = lap[k] = 0.f;
-        }
+        // n = normalize(Ainv d, eps=0): 0/0 = NaN for missed rays, as F.normalize gives (:119)
+        const float len = __fsqrt_rn(nx[k] * nx[k] + ny[k] * ny[k] + nz[k] * nz[k]);
+        nx[k] = __fdiv_rn(nx[k], len);
+        ny[k] = __fdiv_rn(ny[k], len);
+        nz[k] = __fdiv_rn(nz[k], len);
+        lap[k] = (f[k] - sum[k] * 0.25f) * st.lap_scale;    // (:120-124)
     }
 }
 

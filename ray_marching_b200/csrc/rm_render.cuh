@@ -65,7 +65,7 @@ __device__ __forceinline__ void block_minmax(MinMax m, float* gmin, float* gmax,
 }
 
 template <bool FAST, int CAP>
-__global__ void __launch_bounds__(BLOCK)
+__global__ void __launch_bounds__(BLOCK, RM_MINB)
 render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
               const float* __restrict__ poses, const __grid_constant__ RenderParams P) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -73,10 +73,9 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
     const float4* spar = stage_params(par, n_par, smem);
     const int64_t n = P.n_rays;
     const int64_t first = ((int64_t)blockIdx.x * BLOCK + threadIdx.x) * K;
-    // warp-uniform: a warp is active if its first lane has rays; tail lanes of an active warp
-    // march a clamped duplicate ray (never stored) so that the warp stays converged, and a warp
-    // that is entirely out of range still joins the block reductions below
-    const bool active = ((int64_t)blockIdx.x * BLOCK + (threadIdx.x & ~31)) * K < n;
+    // No thread-dependent control flow around the march: every thread marches K rays (tail threads
+    // march clamped duplicates that are never stored), so the interpreter's decode stays on the
+    // uniform datapath and all threads reach the block reductions below.
     const unsigned mask = P.mode_mask | (P.display_mode >= 0 ? (1u << P.display_mode) : 0u);
     const bool need_stencil =
         (mask & (RM_MODE_LAMBERTIAN | RM_MODE_NORMAL | RM_MODE_LAPLACIAN | RM_MODE_TANGENT |
@@ -87,7 +86,7 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
     MinMax mm_dist, mm_prox, mm_lap;
     mm_dist.init(); mm_prox.init(); mm_lap.init();
 
-    if (active) {
+    {
         make_rays(P.cam, poses, P.ray_begin + first, ox, oy, oz, vx, vy, vz);
         store3(P.out.origin, first, n, ox, oy, oz);
 #pragma unroll

@@ -94,25 +94,13 @@ __device__ __forceinline__ void world_ray(const CamParams& cam, const float* pos
 // Ainv = [[-1/(2a),0,0],[-1/(4a),1/(2a),-1/(2a)],[-1/(4b),1/(4b),1/(4b)]]... computed on the host in
 // float64 and passed in, so the kernel uses exactly the reference's float32 constants.
 struct Stencil {
-    float off[4][3];
-    float inv[9];
+    float off[5][3];      // sample offsets; [4] = centre (0,0,0)
+    float w[5][3];        // column of Ainv applied to (o_j - o_0): w[0] = w[4] = 0, w[j] = Ainv[:, j-1]
+    float first[5];       // 1 for j == 0 (defines o_0)
+    float in_sum[5];      // 1 for the four offset samples (Laplacian mean)
+    float inv[9];         // Ainv, row-major (backward kernel)
     float lap_scale;      // 6 / eps^2
 };
-
-// n = normalize(Ainv (o[1..3] - o[0]), eps=0); lap = (f - mean(o)) * 6/eps^2   (ray_marching.py:115-125)
-__device__ __forceinline__ void stencil_finish(const Stencil& st, const float (&o)[4], float f,
-                                               float (&n)[3], float& lap) {
-    const float d0 = o[1] - o[0], d1 = o[2] - o[0], d2 = o[3] - o[0];
-    const float nx = (st.inv[0] * d0 + st.inv[1] * d1) + st.inv[2] * d2;
-    const float ny = (st.inv[3] * d0 + st.inv[4] * d1) + st.inv[5] * d2;
-    const float nz = (st.inv[6] * d0 + st.inv[7] * d1) + st.inv[8] * d2;
-    const float len = __fsqrt_rn(nx * nx + ny * ny + nz * nz);
-    n[0] = __fdiv_rn(nx, len);      // 0/0 = NaN for missed rays, as F.normalize(eps=0) gives
-    n[1] = __fdiv_rn(ny, len);
-    n[2] = __fdiv_rn(nz, len);
-    const float mean = (((o[0] + o[1]) + o[2]) + o[3]) * 0.25f;
-    lap = (f - mean) * st.lap_scale;
-}
 
 // ---- shaders (rendering/shader.py) ----------------------------------------------------------
 __device__ __forceinline__ float shade_lambertian(const float (&v)[3], const float (&n)[3]) {  // :16-20
@@ -214,6 +202,14 @@ inline void make_stencil(float eps, Stencil* st) {
     inv[2][2] = (A[0][0] * A[1][1] - A[0][1] * A[1][0]) / det;
     for (int r = 0; r < 3; ++r)
         for (int c = 0; c < 3; ++c) st->inv[r * 3 + c] = (float)inv[r][c];
+    for (int j = 0; j < 5; ++j) {
+        st->first[j] = j == 0 ? 1.f : 0.f;
+        st->in_sum[j] = j < 4 ? 1.f : 0.f;
+        for (int c = 0; c < 3; ++c) {
+            st->w[j][c] = (j >= 1 && j <= 3) ? (float)inv[c][j - 1] : 0.f;
+            if (j == 4) st->off[j][c] = 0.f;
+        }
+    }
     st->lap_scale = (float)(6.0 / ((double)eps * (double)eps));
 }
 
