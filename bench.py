@@ -26,6 +26,10 @@ for _p in (ROOT, os.path.join(ROOT, "tests")):
     if _p not in sys.path:
         sys.path.insert(0, _p)
 
+if "reference" in sys.argv or int(os.environ.get("WORLD_SIZE", "1")) == 1:
+    # the CPU arm uses every host core (torchrun exports OMP_NUM_THREADS=1 to its workers)
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
+
 import torch  # noqa: E402
 
 PX = 3.45e-6            # main.py:25
@@ -187,19 +191,23 @@ def run_gpu(args):
     q, t = ring_pose(rank, world, wl["cam_t"], dev)
     res_holder = {}
 
-    def gpu_step():
-        """One frame with everything resident in HBM.  Kernels: reduce_init, render, [finalize]."""
-        out = loop.render_planes(q, t, modes=modes, marching_steps=STEPS, bounces=wl["bounces"],
-                                 finalize=False, out=res_holder.get("res"))
-        res_holder["res"] = out
+    mode_mask = sum(1 << m for m in modes)
+
+    def frame(qd, td, out):
+        """One frame.  Kernels: [reduce_init], render, [finalize]; collective: one 8-float MAX
+        all-reduce when a normalising shader runs on a sharded batch."""
+        out = loop.render_planes(qd, td, modes=modes, marching_steps=STEPS, bounces=wl["bounces"],
+                                 finalize=False, out=out)
         if needs_reduce:
-            # global min/max over the whole camera batch (shader.py:35-36,84): NCCL MIN/MAX of 8 floats
+            # global min/max over the whole camera batch (shader.py:35-36,84)
             parallel.allreduce_shader_range(out.reduce)
-            mask = 0
-            for m in modes:
-                mask |= 1 << m
-            ops.shade_finalize(out, mask)
+            ops.shade_finalize(out, mode_mask)
         return out
+
+    def gpu_step():
+        """One frame with everything resident in HBM."""
+        res_holder["res"] = frame(q, t, res_holder.get("res"))
+        return res_holder["res"]
 
     if wl["backward"]:
         gpu_step, extra = make_backward_step(loop, scene, q, t, dev, world)
@@ -257,7 +265,7 @@ def run_gpu(args):
         kern_ms = sum(ks) / len(ks)
 
     # end-to-end: pinned host pose in, images out to pinned host memory, every step
-    e2e = measure_e2e(loop, wl, q, t, dev, args, world, barrier) if not wl["backward"] else \
+    e2e = measure_e2e(frame, wl, q, t, dev, args, barrier) if not wl["backward"] else \
         extra["e2e"](args, barrier)
 
     # sustained repeat of the same step while the clock sampler runs (>= 1.5 s under load)
@@ -303,36 +311,52 @@ def run_gpu(args):
             }
         else:
             line["roofline"] = extra["roofline"](total_ms / args.steps, peak)
-        line["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
+        # CPU baseline: rank 0 at N = 1 only (the host cores are shared by the ranks otherwise)
+        line["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget) if world == 1 else None
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
-def measure_e2e(loop, wl, q, t, dev, args, world, barrier):
-    """Public API with HOST buffers: pose H2D from pinned memory, render, images D2H to pinned."""
+def measure_e2e(frame, wl, q, t, dev, args, barrier):
+    """Public API with HOST buffers: every step copies the pose from pinned host memory, renders, and
+    copies every image plane back to pinned host memory.  Two result buffers and a copy stream let
+    the device->host copy of frame i overlap the render of frame i+1 (ordinary double buffering; all
+    copies have landed when the timed region ends)."""
     from ray_marching_b200 import ops
     modes = wl["modes"]
     q_h, t_h = q.cpu().pin_memory(), t.cpu().pin_memory()
     rays = wl["width"] * wl["height"]
-    host = {m: torch.empty(rays, ops.MODE_CHANNELS[m]).pin_memory() for m in modes}
-    d2h = sum(h.numel() * 4 for h in host.values())
+    host = [{m: torch.empty(rays, ops.MODE_CHANNELS[m]).pin_memory() for m in modes} for _ in range(2)]
+    d2h = sum(h.numel() * 4 for h in host[0].values())
     h2d = (q_h.numel() + t_h.numel()) * 4
+    main, side = torch.cuda.current_stream(dev), torch.cuda.Stream(dev)
+    bufs, copied = [None, None], [None, None]
 
-    def step():
+    def step(i):
+        b = i & 1
+        if copied[b] is not None:
+            main.wait_event(copied[b])               # buffer b is free once its last copy finished
         qd, td = q_h.to(dev, non_blocking=True), t_h.to(dev, non_blocking=True)
-        res = loop.render_planes(qd, td, modes=modes, marching_steps=STEPS, bounces=wl["bounces"])
-        for m in modes:
-            host[m].copy_(res.images[m], non_blocking=True)
-        torch.cuda.synchronize()
+        bufs[b] = frame(qd, td, bufs[b])
+        rendered = torch.cuda.Event()
+        rendered.record(main)
+        with torch.cuda.stream(side):
+            side.wait_event(rendered)
+            for m in modes:
+                host[b][m].copy_(bufs[b].images[m], non_blocking=True)
+            copied[b] = torch.cuda.Event()
+            copied[b].record(side)
 
-    for _ in range(3):
-        step()
+    for i in range(4):
+        step(i)
+    torch.cuda.synchronize()
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        step()
+    for i in range(args.steps):
+        step(i)
+    torch.cuda.synchronize()
     barrier()
     return {"ms_total": (time.perf_counter() - t0) * 1e3, "h2d": h2d, "d2h": d2h}
 
@@ -395,7 +419,7 @@ def make_backward_step(loop, scene, q, t, dev, world):
             e0.record()
             ops._render_bwd(code, par, poses, cam.n_views, cam.width, cam.height, cam.focal_length,
                             cam.sensor_width, cam.sensor_height, STEPS, EPS, g3, g3, g3, None, g3, None,
-                            tape.n_nodes, tape.max_depth)
+                            tape.n_nodes, tape.max_depth, ops.BWD_CONVERGE_TOL)
             e1.record()
             e1.synchronize()
             ks.append(e0.elapsed_time(e1))

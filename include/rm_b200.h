@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define RM_B200_ABI_VERSION 2
+#define RM_B200_ABI_VERSION 3
 
 typedef enum RmStatus {
     RM_OK = 0,
@@ -68,9 +68,10 @@ enum {
 };
 
 /* Global-reduction scratch written by rm_render and consumed by rm_shade_finalize (8 floats):
- * [0] min, [1] max of the distance-shader log, [2] min, [3] max of the proximity-shader log,
+ * [0] -min, [1] max of the distance-shader log, [2] -min, [3] max of the proximity-shader log,
  * [4] max |laplacian|, [5] NaN seen in distance log, [6] in proximity log, [7] in laplacian.
- * Plain floats so a tile- or view-sharded job can all-reduce them (MIN/MAX) between the calls. */
+ * Minima are stored negated so that EVERY entry combines with MAX: a tile- or view-sharded job
+ * needs one 8-float MAX all-reduce between the two calls. */
 #define RM_REDUCE_FLOATS 8
 
 /* Output planes of the fused render; any pointer may be NULL (plane not produced).
@@ -103,6 +104,7 @@ typedef struct RmRenderArgs {
     int32_t early_exit;     /* 1: stop marching a ray once p stops changing (bit-identical) */
     int32_t fast_math;      /* 1: approximate sqrt/exp inside march steps (stencil stays IEEE) */
     const float* cmap;      /* [4096][3] cyclic colour LUT for modes 6,7 (may be NULL otherwise) */
+    float   bwd_converge_tol; /* rm_render_bwd only: see rm_march_bwd (0 = reverse every step) */
 } RmRenderArgs;
 
 int rm_abi_version(void);
@@ -151,10 +153,14 @@ int rm_sdf_vjp(const RmTape* tape, const float* points, const float* grad_sdf, i
  * `steps`-step graph the reference differentiates: given d loss / d pos_out, writes d loss / d origin,
  * d loss / d dirs ([n][3] each, may be NULL) and d loss / d par [tape->n_par] (overwritten).
  * traj_scratch: caller-provided, rm_bwd_scratch_floats(n_rays, steps) floats (the replayed
- * trajectory).  The forward replay uses IEEE math, i.e. it matches rm_march(..., fast_math = 0). */
+ * trajectory).  The forward replay uses IEEE math, i.e. it matches rm_march(..., fast_math = 0).
+ * converge_tol = 0 reverses every step of the unrolled graph.  converge_tol > 0: the steps after a
+ * ray has settled (every later step length <= converge_tol * (1 + |p|_inf)) are reversed in closed
+ * form (geometric series of the fixed-point recurrence = implicit-surface adjoint truncated to the
+ * same step count); the result differs from the step-by-step sum by O(converge_tol). */
 int rm_march_bwd(const RmTape* tape, const float* origin, const float* dirs, const float* grad_pos,
-                 int64_t n_rays, int32_t steps, float* traj_scratch, float* dorigin, float* ddirs,
-                 float* dpar, void* stream);
+                 int64_t n_rays, int32_t steps, float converge_tol, float* traj_scratch,
+                 float* dorigin, float* ddirs, float* dpar, void* stream);
 
 /* Upstream gradients of the G-buffer planes for rm_render_bwd, indexed like RmRenderOut (local ray
  * index); any pointer may be NULL (= zero gradient). */

@@ -17,7 +17,7 @@ LIB_PATH = os.environ.get("RM_B200_LIB") or os.path.join(_HERE, "csrc", "librm_b
 
 POSE_STRIDE = 8
 REDUCE_FLOATS = 8
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 
 class RmTape(C.Structure):
@@ -42,7 +42,7 @@ class RmRenderArgs(C.Structure):
                 ("bounces", C.c_int32), ("normals_eps", C.c_float), ("hit_tau", C.c_float),
                 ("lift_delta", C.c_float), ("mode_mask", C.c_uint32),
                 ("display_mode", C.c_int32), ("degree", C.c_int32), ("early_exit", C.c_int32),
-                ("fast_math", C.c_int32), ("cmap", C.c_void_p)]
+                ("fast_math", C.c_int32), ("cmap", C.c_void_p), ("bwd_converge_tol", C.c_float)]
 
 
 class RmRenderGrads(C.Structure):
@@ -68,7 +68,8 @@ _SIGNATURES = {
     "rm_sdf_vjp": (C.c_int, [C.POINTER(RmTape), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                              C.c_void_p, C.c_void_p]),
     "rm_march_bwd": (C.c_int, [C.POINTER(RmTape), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
-                               C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+                               C.c_int32, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                               C.c_void_p]),
     "rm_bwd_scratch_floats": (C.c_int64, [C.c_int64, C.c_int32]),
     "rm_render_bwd": (C.c_int, [C.POINTER(RmTape), C.POINTER(RmCamera), C.c_void_p,
                                 C.POINTER(RmRenderArgs), C.POINTER(RmRenderGrads), C.c_void_p,

@@ -25,6 +25,10 @@
 
 namespace rm {
 
+#ifndef RM_MINB_BWD
+#define RM_MINB_BWD 3
+#endif
+
 constexpr int KB = 2;            // samples per thread in the backward kernels
 constexpr int BLOCK_B = 128;
 
@@ -74,70 +78,202 @@ __device__ __forceinline__ void traj_load(float* traj, int s, float (&x)[KB], fl
     x[0] = a.x; y[0] = a.y; z[0] = b.x; x[1] = b.y; y[1] = c.x; z[1] = c.y;
 }
 
-// Shared memory: [tape par (n_par floats) | accumulators (n_par floats)]
-__device__ __forceinline__ float* stage_accumulators(unsigned char* smem, int n_par) {
-    float* sacc = reinterpret_cast<float*>(smem + (size_t)n_par * sizeof(float));
-    for (int i = threadIdx.x; i < n_par; i += blockDim.x) sacc[i] = 0.f;
-    return sacc;
+// Shared memory: [tape par (n_par floats) | accumulators (n_par x cols floats)], see GradAcc.
+__device__ __forceinline__ GradAcc stage_accumulators(unsigned char* smem, int n_par, int shift) {
+    GradAcc acc;
+    acc.base = reinterpret_cast<float*>(smem + (size_t)n_par * sizeof(float));
+    acc.shift = shift;
+    acc.cmask = (1 << shift) - 1;
+    const int total = n_par << shift;
+    for (int i = threadIdx.x; i < total; i += blockDim.x) acc.base[i] = 0.f;
+    return acc;
 }
-__device__ __forceinline__ void flush_accumulators(const float* sacc, float* dpar, int n_par) {
+// One pass per block: column sums (rotated start -> conflict-free) and one global atomic per
+// parameter.
+__device__ __forceinline__ void flush_accumulators(const GradAcc acc, float* dpar, int n_par) {
     __syncthreads();
     for (int i = threadIdx.x; i < n_par; i += blockDim.x) {
-        const float v = sacc[i];
+        float v = 0.f;
+        for (int j = 0; j <= acc.cmask; ++j) v += acc.base[(i << acc.shift) + ((j + threadIdx.x) & acc.cmask)];
         if (v != 0.f) atomicAdd(dpar + i, v);
     }
 }
 
-// Replays the march with IEEE math, storing the position before every step.
+// ---- the two passes every backward kernel is made of ------------------------------------------
+// Each pass has exactly ONE call site of the interpreter (forward: eval_scene; reverse:
+// eval_record + sweep_vjp), driven by a warp-uniform task counter, so the kernel holds one copy of
+// each and its hot code stays instruction-cache resident.
+
+struct StencilAdjoint {          // per-sample inputs of the stencil's reverse tasks
+    float gux[KB], guy[KB], guz[KB];   // adjoint of u = Ainv (o[1..3] - o_0)
+    float gm[KB];                      // g_lap * 6/eps^2
+    float gs[KB];                      // g_sdf
+};
+
+// Forward pass: replays the march with IEEE math (storing the position before every step in the
+// slot scratch), then -- if `stencil` -- samples the four tetrahedral offsets at p_S and folds them
+// into u = Ainv (o_j - o_0) like the forward kernel does.
+// conv[k] = first step from which every step length stayed within tol * (1 + |p|_inf) (= steps when
+// the ray never settles, or when tol == 0): the tail [conv, steps) is a stationary point of the
+// iteration to first order in tol.
 template <int CAP>
-__device__ __forceinline__ void replay_march(const TapeCode<CAP>& code, int n_instr, const float4* spar,
-                                             int steps, float* traj, float (&px)[KB], float (&py)[KB],
-                                             float (&pz)[KB], const float (&vx)[KB],
-                                             const float (&vy)[KB], const float (&vz)[KB]) {
-    for (int s = 0; s < steps; ++s) {
-        traj_store(traj, s, px, py, pz);
-        float d[KB];
-        eval_scene<KB, false, CAP>(code, n_instr, spar, px, py, pz, d);
+__device__ __forceinline__ void forward_pass(const TapeCode<CAP>& code, int n_instr, const float4* spar,
+                                             int steps, float tol, const Stencil* st, float* traj,
+                                             float (&px)[KB], float (&py)[KB], float (&pz)[KB],
+                                             const float (&vx)[KB], const float (&vy)[KB],
+                                             const float (&vz)[KB], int (&conv)[KB],
+                                             float (&ux)[KB], float (&uy)[KB], float (&uz)[KB]) {
+    float o0[KB];
 #pragma unroll
-        for (int k = 0; k < KB; ++k) {
-            px[k] = fmaf(d[k], vx[k], px[k]); py[k] = fmaf(d[k], vy[k], py[k]); pz[k] = fmaf(d[k], vz[k], pz[k]);
+    for (int k = 0; k < KB; ++k) { conv[k] = 0; ux[k] = uy[k] = uz[k] = o0[k] = 0.f; }
+    const int n_tasks = steps + (st != nullptr ? 4 : 0);
+    for (int task = 0; task < n_tasks; ++task) {
+        const bool marching = task < steps;
+        const int j = marching ? 4 : task - steps;            // stencil sample (4 = zero offset)
+        float x[KB], y[KB], z[KB], d[KB];
+        float dx = 0.f, dy = 0.f, dz = 0.f;
+        if (!marching) { dx = st->off[j][0]; dy = st->off[j][1]; dz = st->off[j][2]; }
+        else traj_store(traj, task, px, py, pz);
+#pragma unroll
+        for (int k = 0; k < KB; ++k) { x[k] = px[k] + dx; y[k] = py[k] + dy; z[k] = pz[k] + dz; }
+        eval_scene<KB, false, CAP>(code, n_instr, spar, x, y, z, d);
+        if (marching) {
+#pragma unroll
+            for (int k = 0; k < KB; ++k) {
+                const float scale = 1.f + fmaxf(fabsf(px[k]), fmaxf(fabsf(py[k]), fabsf(pz[k])));
+                if (!(fabsf(d[k]) <= tol * scale)) conv[k] = task + 1;       // also catches NaN
+                px[k] = fmaf(d[k], vx[k], px[k]); py[k] = fmaf(d[k], vy[k], py[k]); pz[k] = fmaf(d[k], vz[k], pz[k]);
+            }
+        } else {
+            const float wx = st->w[j][0], wy = st->w[j][1], wz = st->w[j][2], first = st->first[j];
+#pragma unroll
+            for (int k = 0; k < KB; ++k) {
+                o0[k] = first != 0.f ? d[k] : o0[k];
+                const float dj = d[k] - o0[k];
+                ux[k] = fmaf(wx, dj, ux[k]); uy[k] = fmaf(wy, dj, uy[k]); uz[k] = fmaf(wz, dj, uz[k]);
+            }
         }
     }
 }
 
-// Reverse of the march: on entry l* = adjoint of p_S, on exit l* = adjoint of p_0; dv* accumulates
-// the adjoint of the direction.
+// Reverse pass.  On entry l* = upstream adjoint of p_S and dv* = upstream adjoint of the direction;
+// on exit l* = adjoint of p_0, dv* = adjoint of the direction.  Tasks, in order:
+//   0..4   stencil samples j (offset j, centre for j = 4) with adjoint
+//          wb[j].g_u + lap_w[j] g_m + sdf_w[j] g_s            (skipped when sa == nullptr)
+//   5, 6   converged tail: the steps [conv, S) all sit at the stationary point q = p_conv, where the
+//          recurrence  a = l.v; dpar += a df/dpar; dv += f l; l += a grad f  has the closed form
+//          a_j = a_0 c^j, c = 1 + grad f(q).v.  Task 5 sweeps with a_0 (which also yields c), task 6
+//          with a_0 (S_n - 1), S_n = sum_{j<n} c^j, n = S - conv: the implicit-surface adjoint of the
+//          hit point truncated to the n steps the reference unrolls; O(tol) from the step-by-step sum.
+//   7..    exact steps s = max_warp(conv) - 1 .. 0 of the unrolled graph.
 template <int CAP>
-__device__ __forceinline__ void reverse_march(const TapeCode<CAP>& code, int n_instr, const float4* spar,
-                                              int steps, float* traj, float* sacc,
-                                              const float (&vx)[KB], const float (&vy)[KB],
-                                              const float (&vz)[KB], float (&lx)[KB], float (&ly)[KB],
-                                              float (&lz)[KB], float (&dvx)[KB], float (&dvy)[KB],
-                                              float (&dvz)[KB]) {
-    for (int s = steps - 1; s >= 0; --s) {
-        float px[KB], py[KB], pz[KB], a[KB], f[KB], gx[KB], gy[KB], gz[KB];
-        traj_load(traj, s, px, py, pz);
+__device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_instr, const float4* spar,
+                                             int steps, const Stencil* st, const StencilAdjoint* sa,
+                                             float* traj, const GradAcc sacc, const int (&conv)[KB],
+                                             const float (&psx)[KB], const float (&psy)[KB],
+                                             const float (&psz)[KB],
+                                             const float (&vx)[KB], const float (&vy)[KB],
+                                             const float (&vz)[KB], float (&lx)[KB], float (&ly)[KB],
+                                             float (&lz)[KB], float (&dvx)[KB], float (&dvy)[KB],
+                                             float (&dvz)[KB]) {
+    bool any_tail = false;
+    int first_exact = 0;
 #pragma unroll
-        for (int k = 0; k < KB; ++k) a[k] = lx[k] * vx[k] + ly[k] * vy[k] + lz[k] * vz[k];
-        NodeRecords<KB> rec;
-        eval_record<KB, CAP>(code, n_instr, spar, px, py, pz, rec, f);
-        sweep_vjp<KB, CAP>(code, n_instr, spar, px, py, pz, a, rec, sacc, gx, gy, gz);
+    for (int k = 0; k < KB; ++k) { any_tail |= conv[k] < steps; first_exact = max(first_exact, conv[k]); }
+    const bool tail = __any_sync(0xffffffffu, any_tail);
+    for (int o = 16; o > 0; o >>= 1) first_exact = max(first_exact, __shfl_xor_sync(0xffffffffu, first_exact, o));
+
+    float qx[KB], qy[KB], qz[KB];          // stationary points (tail tasks)
+    float g1x[KB], g1y[KB], g1z[KB], a0[KB], rest[KB], tsum[KB];
 #pragma unroll
-        for (int k = 0; k < KB; ++k) {
-            dvx[k] = fmaf(f[k], lx[k], dvx[k]); dvy[k] = fmaf(f[k], ly[k], dvy[k]); dvz[k] = fmaf(f[k], lz[k], dvz[k]);
-            lx[k] += gx[k]; ly[k] += gy[k]; lz[k] += gz[k];
+    for (int k = 0; k < KB; ++k) {
+        const int sc = conv[k] < steps ? conv[k] : 0;
+        const float* slot = traj_slot(traj, sc) + 3 * k;
+        const bool has = tail && steps > 0;
+        qx[k] = has ? slot[0] : 0.f; qy[k] = has ? slot[1] : 0.f; qz[k] = has ? slot[2] : 0.f;
+        g1x[k] = g1y[k] = g1z[k] = a0[k] = rest[k] = tsum[k] = 0.f;
+    }
+    int task = sa != nullptr ? 0 : 5;
+    if (task == 5 && !tail) task = 7;
+    const int n_tasks = 7 + first_exact;
+    while (task < n_tasks) {
+        float x[KB], y[KB], z[KB], a[KB], f[KB], gx[KB], gy[KB], gz[KB];
+        const int s = first_exact - 1 - (task - 7);           // exact step of tasks >= 7
+        if (task < 5) {
+            const float ox = st->off[task][0], oy = st->off[task][1], oz = st->off[task][2];
+            const float w0 = st->wb[task][0], w1 = st->wb[task][1], w2 = st->wb[task][2];
+            const float wl = st->lap_w[task], ws = st->sdf_w[task];
+#pragma unroll
+            for (int k = 0; k < KB; ++k) {
+                x[k] = psx[k] + ox; y[k] = psy[k] + oy; z[k] = psz[k] + oz;
+                a[k] = fmaf(w0, sa->gux[k], fmaf(w1, sa->guy[k], w2 * sa->guz[k])) + wl * sa->gm[k] + ws * sa->gs[k];
+            }
+        } else if (task < 7) {
+#pragma unroll
+            for (int k = 0; k < KB; ++k) {
+                x[k] = qx[k]; y[k] = qy[k]; z[k] = qz[k];
+                if (task == 5) a0[k] = conv[k] < steps ? lx[k] * vx[k] + ly[k] * vy[k] + lz[k] * vz[k] : 0.f;
+                a[k] = task == 5 ? a0[k] : rest[k];
+            }
+        } else {
+            traj_load(traj, s, x, y, z);
+#pragma unroll
+            for (int k = 0; k < KB; ++k)
+                a[k] = s < conv[k] ? lx[k] * vx[k] + ly[k] * vy[k] + lz[k] * vz[k] : 0.f;
         }
+        NodeRecords<KB> rec;
+        eval_record<KB, CAP>(code, n_instr, spar, x, y, z, rec, f);
+        sweep_vjp<KB, CAP>(code, n_instr, spar, x, y, z, a, rec, sacc, gx, gy, gz);
+        if (task < 5) {
+#pragma unroll
+            for (int k = 0; k < KB; ++k) { lx[k] += gx[k]; ly[k] += gy[k]; lz[k] += gz[k]; }
+            if (task == 4 && !tail) task = 6;                  // no lane has a tail: skip tasks 5, 6
+        } else if (task == 5) {
+#pragma unroll
+            for (int k = 0; k < KB; ++k) {
+                const int n = steps - conv[k];
+                // c from the sweep: (a0 grad f).v / a0
+                const float gv = a0[k] != 0.f ? __fdiv_rn(gx[k] * vx[k] + gy[k] * vy[k] + gz[k] * vz[k], a0[k]) : 0.f;
+                const float c = 1.f + gv;
+                float cn = 1.f, sn = 0.f, tn = 0.f;            // c^j, S_j, T_j = sum_{i<j} S_i
+                for (int j = 0; j < n; ++j) { tn += sn; sn += cn; cn *= c; }
+                rest[k] = a0[k] != 0.f ? a0[k] * (sn - 1.f) : 0.f;
+                tsum[k] = tn;
+                g1x[k] = gx[k]; g1y[k] = gy[k]; g1z[k] = gz[k];
+            }
+        } else if (task == 6) {
+#pragma unroll
+            for (int k = 0; k < KB; ++k) {
+                if (conv[k] < steps) {
+                    const float n = (float)(steps - conv[k]);
+                    // dv += f(q) * sum_j l_j,  l_j = l_0 + S_j (a0 grad f)
+                    dvx[k] += f[k] * fmaf(n, lx[k], tsum[k] * g1x[k]);
+                    dvy[k] += f[k] * fmaf(n, ly[k], tsum[k] * g1y[k]);
+                    dvz[k] += f[k] * fmaf(n, lz[k], tsum[k] * g1z[k]);
+                    lx[k] += g1x[k] + gx[k]; ly[k] += g1y[k] + gy[k]; lz[k] += g1z[k] + gz[k];
+                }
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < KB; ++k) {
+                if (s < conv[k]) {
+                    dvx[k] = fmaf(f[k], lx[k], dvx[k]); dvy[k] = fmaf(f[k], ly[k], dvy[k]); dvz[k] = fmaf(f[k], lz[k], dvz[k]);
+                    lx[k] += gx[k]; ly[k] += gy[k]; lz[k] += gz[k];
+                }
+            }
+        }
+        ++task;
     }
 }
 
 // Grid-stride over sample groups so the number of blocks (and global atomics) stays bounded.
 template <int CAP>
-__global__ void __launch_bounds__(BLOCK_B)
+__global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
 sdf_vjp_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
-               const float* __restrict__ pts, const float* __restrict__ gout, int64_t n,
+               int acc_shift, const float* __restrict__ pts, const float* __restrict__ gout, int64_t n,
                float* __restrict__ dpts, float* __restrict__ dpar) {
     extern __shared__ __align__(16) unsigned char smem[];
-    float* sacc = stage_accumulators(smem, n_par);
+    const GradAcc sacc = stage_accumulators(smem, n_par, acc_shift);
     const float4* spar = stage_params(par, n_par, smem);                // syncs
     const int64_t groups = (n + KB - 1) / KB;
     const int64_t warp_groups = (groups + 31) / 32 * 32;                // whole warps iterate together
@@ -156,13 +292,13 @@ sdf_vjp_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int
 }
 
 template <int CAP>
-__global__ void __launch_bounds__(BLOCK_B)
+__global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
 march_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
-                 const float* __restrict__ origin, const float* __restrict__ dirs,
-                 const float* __restrict__ gpos, int64_t n, int steps, float* __restrict__ traj,
+                 int acc_shift, const float* __restrict__ origin, const float* __restrict__ dirs,
+                 const float* __restrict__ gpos, int64_t n, int steps, float tol, float* __restrict__ traj,
                  float* __restrict__ dorigin, float* __restrict__ ddirs, float* __restrict__ dpar) {
     extern __shared__ __align__(16) unsigned char smem[];
-    float* sacc = stage_accumulators(smem, n_par);
+    const GradAcc sacc = stage_accumulators(smem, n_par, acc_shift);
     const float4* spar = stage_params(par, n_par, smem);
     const int64_t groups = (n + KB - 1) / KB;
     const int64_t warp_groups = (groups + 31) / 32 * 32;
@@ -172,12 +308,15 @@ march_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, i
         float px[KB], py[KB], pz[KB], vx[KB], vy[KB], vz[KB];
         load3k(origin, first, n, px, py, pz);
         load3k(dirs, first, n, vx, vy, vz);
-        replay_march<CAP>(code, n_instr, spar, steps, traj, px, py, pz, vx, vy, vz);
+        int conv[KB];
+        float ux[KB], uy[KB], uz[KB];
+        forward_pass<CAP>(code, n_instr, spar, steps, tol, nullptr, traj, px, py, pz, vx, vy, vz, conv, ux, uy, uz);
         float lx[KB], ly[KB], lz[KB], dvx[KB], dvy[KB], dvz[KB];
         load3k(gpos, first, n, lx, ly, lz);
 #pragma unroll
         for (int k = 0; k < KB; ++k) dvx[k] = dvy[k] = dvz[k] = 0.f;
-        reverse_march<CAP>(code, n_instr, spar, steps, traj, sacc, vx, vy, vz, lx, ly, lz, dvx, dvy, dvz);
+        reverse_pass<CAP>(code, n_instr, spar, steps, nullptr, nullptr, traj, sacc, conv, px, py, pz,
+                          vx, vy, vz, lx, ly, lz, dvx, dvy, dvz);
         store3k(dorigin, first, n, lx, ly, lz);
         store3k(ddirs, first, n, dvx, dvy, dvz);
     }
@@ -186,10 +325,12 @@ march_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, i
 
 // ---- fused G-buffer backward ------------------------------------------------------------------
 struct RenderBwdParams {
+    int acc_shift;
     CamParams cam;
     Stencil st;
     int64_t ray_begin, n_rays;
     int steps;
+    float tol;
     RmRenderGrads g;
     float* traj;
     float* dpar;
@@ -232,11 +373,11 @@ __device__ __forceinline__ void flush_pose_grad(float* dposes, int view, const f
 }
 
 template <int CAP>
-__global__ void __launch_bounds__(BLOCK_B)
+__global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
 render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
                   const float* __restrict__ poses, const __grid_constant__ RenderBwdParams P) {
     extern __shared__ __align__(16) unsigned char smem[];
-    float* sacc = stage_accumulators(smem, n_par);
+    const GradAcc sacc = stage_accumulators(smem, n_par, P.acc_shift);
     const float4* spar = stage_params(par, n_par, smem);
     const int64_t n = P.n_rays;
     const int64_t groups = (n + KB - 1) / KB;
@@ -264,89 +405,43 @@ render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, 
             px[k] = ow[0]; py[k] = ow[1]; pz[k] = ow[2];
             vx[k] = vw[0]; vy[k] = vw[1]; vz[k] = vw[2];
         }
-        // ---- replay the march ----
-        replay_march<CAP>(code, n_instr, spar, P.steps, P.traj, px, py, pz, vx, vy, vz);
+        // ---- forward pass: replay the march, sample the stencil offsets ----
+        int conv[KB];
+        float ux[KB], uy[KB], uz[KB];
+        forward_pass<CAP>(code, n_instr, spar, P.steps, P.tol, need_stencil ? &P.st : nullptr, P.traj,
+                          px, py, pz, vx, vy, vz, conv, ux, uy, uz);
 
-        // ---- adjoint of p_S: upstream + stencil (SDFNormals.forward, ray_marching.py:115-125)
-        //      + f(p_S) (control.py:244) ----
+        // ---- adjoints of the stencil outputs (SDFNormals.forward, ray_marching.py:115-125) and of
+        //      f(p_S) (control.py:244) ----
         float lx[KB], ly[KB], lz[KB];
         load3k(P.g.pos, first, n, lx, ly, lz);
-        float a_c[KB];                                      // adjoint of the centre sample f(p_S)
-        load1k(P.g.sdf, first, n, a_c);
-        if (need_stencil) {
-            float o[4][KB];
-            for (int j = 0; j < 4; ++j) {                   // the normal needs the four offset samples
-                float x[KB], y[KB], z[KB], d[KB];
-#pragma unroll
-                for (int k = 0; k < KB; ++k) {
-                    x[k] = px[k] + P.st.off[j][0]; y[k] = py[k] + P.st.off[j][1]; z[k] = pz[k] + P.st.off[j][2];
-                }
-                eval_scene<KB, false, CAP>(code, n_instr, spar, x, y, z, d);
-#pragma unroll
-                for (int k = 0; k < KB; ++k) {
-                    if (j == 0) o[0][k] = d[k];
-                    else if (j == 1) o[1][k] = d[k];
-                    else if (j == 2) o[2][k] = d[k];
-                    else o[3][k] = d[k];
-                }
-            }
+        StencilAdjoint sa;
+        load1k(P.g.sdf, first, n, sa.gs);
+        {
             float gnx[KB], gny[KB], gnz[KB], glap[KB];
             load3k(P.g.normals, first, n, gnx, gny, gnz);
             load1k(P.g.laplacian, first, n, glap);
-            float a_o[4][KB];
 #pragma unroll
             for (int k = 0; k < KB; ++k) {
-                // forward: u = Ainv (o[1..3] - o[0]); nrm = u / |u|; lap = (fc - mean o) * 6/eps^2
-                const float d0 = o[1][k] - o[0][k], d1 = o[2][k] - o[0][k], d2 = o[3][k] - o[0][k];
-                const float ux = (P.st.inv[0] * d0 + P.st.inv[1] * d1) + P.st.inv[2] * d2;
-                const float uy = (P.st.inv[3] * d0 + P.st.inv[4] * d1) + P.st.inv[5] * d2;
-                const float uz = (P.st.inv[6] * d0 + P.st.inv[7] * d1) + P.st.inv[8] * d2;
-                const float len = __fsqrt_rn(ux * ux + uy * uy + uz * uz);
+                // forward: nrm = u / |u|; d nrm / d u = (I - nrm nrm^T) / |u|
+                const float len = __fsqrt_rn(ux[k] * ux[k] + uy[k] * uy[k] + uz[k] * uz[k]);
                 const float il = __fdiv_rn(1.f, len);
-                const float nx = ux * il, ny = uy * il, nz = uz * il;
-                // d nrm / d u = (I - nrm nrm^T) / |u|
+                const float nx = ux[k] * il, ny = uy[k] * il, nz = uz[k] * il;
                 const float gn = gnx[k] * nx + gny[k] * ny + gnz[k] * nz;
                 const bool has_n = P.g.normals != nullptr;
-                const float gux = has_n ? (gnx[k] - gn * nx) * il : 0.f;
-                const float guy = has_n ? (gny[k] - gn * ny) * il : 0.f;
-                const float guz = has_n ? (gnz[k] - gn * nz) * il : 0.f;
-                const float gd0 = P.st.inv[0] * gux + P.st.inv[3] * guy + P.st.inv[6] * guz;   // Ainv^T g_u
-                const float gd1 = P.st.inv[1] * gux + P.st.inv[4] * guy + P.st.inv[7] * guz;
-                const float gd2 = P.st.inv[2] * gux + P.st.inv[5] * guy + P.st.inv[8] * guz;
-                const float gm = glap[k] * P.st.lap_scale;                                     // d lap / d fc
-                a_o[0][k] = -(gd0 + gd1 + gd2) - 0.25f * gm;
-                a_o[1][k] = gd0 - 0.25f * gm;
-                a_o[2][k] = gd1 - 0.25f * gm;
-                a_o[3][k] = gd2 - 0.25f * gm;
-                a_c[k] += gm;
+                sa.gux[k] = has_n ? (gnx[k] - gn * nx) * il : 0.f;
+                sa.guy[k] = has_n ? (gny[k] - gn * ny) * il : 0.f;
+                sa.guz[k] = has_n ? (gnz[k] - gn * nz) * il : 0.f;
+                sa.gm[k] = glap[k] * P.st.lap_scale;
             }
-            for (int j = 0; j < 4; ++j) {
-                float x[KB], y[KB], z[KB], a[KB], f[KB], gx[KB], gy[KB], gz[KB];
-#pragma unroll
-                for (int k = 0; k < KB; ++k) {
-                    x[k] = px[k] + P.st.off[j][0]; y[k] = py[k] + P.st.off[j][1]; z[k] = pz[k] + P.st.off[j][2];
-                    a[k] = j == 0 ? a_o[0][k] : (j == 1 ? a_o[1][k] : (j == 2 ? a_o[2][k] : a_o[3][k]));
-                }
-                NodeRecords<KB> rec;
-                eval_record<KB, CAP>(code, n_instr, spar, x, y, z, rec, f);
-                sweep_vjp<KB, CAP>(code, n_instr, spar, x, y, z, a, rec, sacc, gx, gy, gz);
-#pragma unroll
-                for (int k = 0; k < KB; ++k) { lx[k] += gx[k]; ly[k] += gy[k]; lz[k] += gz[k]; }
-            }
-        }
-        if (need_stencil || P.g.sdf != nullptr) {
-            float f[KB], gx[KB], gy[KB], gz[KB];
-            NodeRecords<KB> rec;
-            eval_record<KB, CAP>(code, n_instr, spar, px, py, pz, rec, f);
-            sweep_vjp<KB, CAP>(code, n_instr, spar, px, py, pz, a_c, rec, sacc, gx, gy, gz);
-#pragma unroll
-            for (int k = 0; k < KB; ++k) { lx[k] += gx[k]; ly[k] += gy[k]; lz[k] += gz[k]; }
         }
 
-        // ---- reverse the march ----
+        // ---- reverse pass: stencil samples, converged tail, exact steps ----
         float dvx[KB], dvy[KB], dvz[KB];
         load3k(P.g.dirs, first, n, dvx, dvy, dvz);
-        reverse_march<CAP>(code, n_instr, spar, P.steps, P.traj, sacc, vx, vy, vz, lx, ly, lz, dvx, dvy, dvz);
+        reverse_pass<CAP>(code, n_instr, spar, P.steps, &P.st,
+                          (need_stencil || P.g.sdf != nullptr) ? &sa : nullptr, P.traj, sacc, conv,
+                          px, py, pz, vx, vy, vz, lx, ly, lz, dvx, dvy, dvz);
         float gox[KB], goy[KB], goz[KB];
         load3k(P.g.origin, first, n, gox, goy, goz);
 
@@ -394,7 +489,15 @@ inline unsigned backward_grid(int64_t n) {
     const int64_t cap = 148 * 8;                      // bounded: one global atomic per parameter per block
     return (unsigned)(want < cap ? (want > 0 ? want : 1) : cap);
 }
-inline size_t backward_smem(const RmTape* t) { return 2 * (size_t)t->n_par * sizeof(float); }
+// log2 of the accumulator columns: as many lane-private columns as fit in ~40 KB per block
+inline int backward_acc_shift(const RmTape* t) {
+    int shift = 5;
+    while (shift > 0 && ((size_t)t->n_par << shift) * sizeof(float) > 40 * 1024) --shift;
+    return shift;
+}
+inline size_t backward_smem(const RmTape* t) {
+    return (size_t)t->n_par * sizeof(float) * (1 + ((size_t)1 << backward_acc_shift(t)));
+}
 
 }  // namespace rm
 
@@ -417,17 +520,17 @@ extern "C" int rm_sdf_vjp(const RmTape* tape, const float* points, const float* 
     RM_WITH_CODE(tape, {
         if (int s = prepare_smem(sdf_vjp_kernel<CAP>, sm)) return s;
         sdf_vjp_kernel<CAP><<<backward_grid(n), BLOCK_B, sm, (cudaStream_t)stream>>>(
-            code, tape->par, tape->n_instr, tape->n_par, points, grad_sdf, n, dpoints, dpar);
+            code, tape->par, tape->n_instr, tape->n_par, backward_acc_shift(tape), points, grad_sdf, n, dpoints, dpar);
     });
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }
 
 extern "C" int rm_march_bwd(const RmTape* tape, const float* origin, const float* dirs,
-                            const float* grad_pos, int64_t n, int32_t steps, float* traj_scratch,
-                            float* dorigin, float* ddirs, float* dpar, void* stream) {
+                            const float* grad_pos, int64_t n, int32_t steps, float converge_tol,
+                            float* traj_scratch, float* dorigin, float* ddirs, float* dpar, void* stream) {
     if (int s = check_backward_tape(tape)) return s;
-    if (n < 0 || steps < 0 || (dpar == nullptr && tape->n_par > 0) ||
+    if (n < 0 || steps < 0 || !(converge_tol >= 0.f) || (dpar == nullptr && tape->n_par > 0) ||
         (n > 0 && (!origin || !dirs || !grad_pos || (steps > 0 && !traj_scratch))))
         return fail(RM_ERR_INVALID, "rm_march_bwd: null buffer or negative count");
     if (tape->n_par > 0)
@@ -437,8 +540,8 @@ extern "C" int rm_march_bwd(const RmTape* tape, const float* origin, const float
     RM_WITH_CODE(tape, {
         if (int s = prepare_smem(march_bwd_kernel<CAP>, sm)) return s;
         march_bwd_kernel<CAP><<<backward_grid(n), BLOCK_B, sm, (cudaStream_t)stream>>>(
-            code, tape->par, tape->n_instr, tape->n_par, origin, dirs, grad_pos, n, steps,
-            traj_scratch, dorigin, ddirs, dpar);
+            code, tape->par, tape->n_instr, tape->n_par, backward_acc_shift(tape), origin, dirs, grad_pos, n, steps,
+            converge_tol, traj_scratch, dorigin, ddirs, dpar);
     });
     RM_CUDA(cudaGetLastError());
     return RM_OK;
@@ -456,8 +559,8 @@ extern "C" int rm_render_bwd(const RmTape* tape, const RmCamera* cam, const floa
     const int64_t total = (int64_t)cam->n_views * cam->width * cam->height;
     if (a->ray_begin < 0 || a->n_rays < 0 || a->ray_begin + a->n_rays > total)
         return fail(RM_ERR_INVALID, "rm_render_bwd: ray range outside the camera batch");
-    if (a->steps < 0 || !(a->normals_eps > 0.f))
-        return fail(RM_ERR_INVALID, "rm_render_bwd: negative steps or eps <= 0");
+    if (a->steps < 0 || !(a->normals_eps > 0.f) || !(a->bwd_converge_tol >= 0.f))
+        return fail(RM_ERR_INVALID, "rm_render_bwd: negative steps, eps <= 0 or negative tolerance");
     if (a->bounces != 0)
         return fail(RM_ERR_UNSUPPORTED, "rm_render_bwd: reflected segments are not differentiable here");
     if (a->n_rays > 0 && a->steps > 0 && traj_scratch == nullptr)
@@ -468,6 +571,8 @@ extern "C" int rm_render_bwd(const RmTape* tape, const RmCamera* cam, const floa
     if (a->n_rays == 0) return RM_OK;
     make_stencil(a->normals_eps, &P.st);
     P.ray_begin = a->ray_begin; P.n_rays = a->n_rays; P.steps = a->steps;
+    P.acc_shift = backward_acc_shift(tape);
+    P.tol = a->bwd_converge_tol;
     P.g = *grads; P.traj = traj_scratch; P.dpar = dpar; P.dposes = dposes;
     const size_t sm = backward_smem(tape);
     RM_WITH_CODE(tape, {

@@ -58,7 +58,7 @@ __device__ __forceinline__ void block_minmax(MinMax m, float* gmin, float* gmax,
         for (int w = 1; w < BLOCK / 32; ++w) {
             m.mn = fminf(m.mn, sh[w][0]); m.mx = fmaxf(m.mx, sh[w][1]); m.nan = fmaxf(m.nan, sh[w][2]);
         }
-        if (gmin && m.mn != CUDART_INF_F) atomic_min_f(gmin, m.mn);
+        if (gmin && m.mn != CUDART_INF_F) atomic_max_f(gmin, -m.mn);    // minima are stored negated
         if (gmax && m.mx != -CUDART_INF_F) atomic_max_f(gmax, m.mx);
         if (m.nan > 0.f) atomicMax(reinterpret_cast<int*>(gnan), __float_as_int(1.0f));
     }
@@ -227,7 +227,7 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
 
 __global__ void reduce_init_kernel(float* r) {
     if (threadIdx.x == 0) {
-        r[0] = CUDART_INF_F; r[1] = -CUDART_INF_F; r[2] = CUDART_INF_F; r[3] = -CUDART_INF_F;
+        r[0] = -CUDART_INF_F; r[1] = -CUDART_INF_F; r[2] = -CUDART_INF_F; r[3] = -CUDART_INF_F;
         r[4] = -CUDART_INF_F; r[5] = 0.f; r[6] = 0.f; r[7] = 0.f;
     }
 }
@@ -244,8 +244,8 @@ struct FinalizeParams {
 __global__ void __launch_bounds__(256)
 shade_finalize_kernel(const float* __restrict__ reduce, const FinalizeParams F) {
     const float nan = CUDART_NAN_F;
-    const float dmin = reduce[5] > 0.f ? nan : reduce[0], dmax = reduce[5] > 0.f ? nan : reduce[1];
-    const float pmin = reduce[6] > 0.f ? nan : reduce[2], pmax = reduce[6] > 0.f ? nan : reduce[3];
+    const float dmin = reduce[5] > 0.f ? nan : -reduce[0], dmax = reduce[5] > 0.f ? nan : reduce[1];
+    const float pmin = reduce[6] > 0.f ? nan : -reduce[2], pmax = reduce[6] > 0.f ? nan : reduce[3];
     const float lmax = reduce[7] > 0.f ? nan : reduce[4];
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     const int64_t n4 = F.n >> 2;

@@ -98,8 +98,13 @@ struct Stencil {
     float w[5][3];        // column of Ainv applied to (o_j - o_0): w[0] = w[4] = 0, w[j] = Ainv[:, j-1]
     float first[5];       // 1 for j == 0 (defines o_0)
     float in_sum[5];      // 1 for the four offset samples (Laplacian mean)
-    float inv[9];         // Ainv, row-major (backward kernel)
+    float inv[9];         // Ainv, row-major
     float lap_scale;      // 6 / eps^2
+    // backward: adjoint of sample j = wb[j] . g_u + lap_w[j] * g_lap*lap_scale + sdf_w[j] * g_sdf, where
+    // g_u is the adjoint of u = Ainv (o[1..3] - o_0): wb[0] = -(w[1]+w[2]+w[3]), wb[1..3] = w[1..3]
+    float wb[5][3];
+    float lap_w[5];       // -1/4 for the four offset samples, +1 for the centre
+    float sdf_w[5];       // 1 for the centre (control.py:244)
 };
 
 // ---- shaders (rendering/shader.py) ----------------------------------------------------------
@@ -203,6 +208,11 @@ inline void make_stencil(float eps, Stencil* st) {
     for (int r = 0; r < 3; ++r)
         for (int c = 0; c < 3; ++c) st->inv[r * 3 + c] = (float)inv[r][c];
     for (int j = 0; j < 5; ++j) {
+        st->lap_w[j] = j < 4 ? -0.25f : 1.f;
+        st->sdf_w[j] = j == 4 ? 1.f : 0.f;
+        for (int c = 0; c < 3; ++c)
+            st->wb[j][c] = (j >= 1 && j <= 3) ? (float)inv[c][j - 1]
+                         : (j == 0 ? -(float)(inv[c][0] + inv[c][1] + inv[c][2]) : 0.f);
         st->first[j] = j == 0 ? 1.f : 0.f;
         st->in_sum[j] = j < 4 ? 1.f : 0.f;
         for (int c = 0; c < 3; ++c) {

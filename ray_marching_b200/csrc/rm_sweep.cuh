@@ -64,16 +64,34 @@ __device__ __forceinline__ void child_adjoint(int fold, int ordinal, OpenNode<K>
     }
 }
 
-// The reverse sweep.  `sacc` = per-block shared accumulators, one float per tape parameter.
-// Outputs g{x,y,z}[k] = abar[k] * grad_p f(p_k).  All 32 lanes of the warp must call this together.
+// Shared-memory gradient accumulators: `cols` (power of two <= 32) lane-private columns per tape
+// parameter, element (addr, lane & (cols-1)).  With cols = 32 every lane of a warp adds to its own
+// bank (conflict-free ATOMS, no warp reduction at all); large tapes use fewer columns, where the
+// hardware serialises the lanes that share a column.  One reduction over the columns per block
+// (flush_accumulators) replaces a warp butterfly per leaf, step and ray.
+struct GradAcc {
+    float* base;
+    int cmask;        // cols - 1
+    int shift;        // log2(cols)
+    __device__ __forceinline__ void add(int addr, float v) const {
+        if (v != 0.f) atomicAdd(base + (addr << shift) + ((int)threadIdx.x & cmask), v);
+    }
+};
+
+// Softmax weights below this are treated as zero (smooth-union children far behind the surface);
+// a 512-child union then loses at most 512e-9 of the gradient, far inside the 1e-3 tolerance.
+constexpr float CULL_EPS = 1e-9f;
+
+// The reverse sweep.  Outputs g{x,y,z}[k] = abar[k] * grad_p f(p_k) and adds d f / d par into
+// `acc`.  All 32 lanes of the warp must call this together (warp votes skip leaves whose adjoint
+// is zero in every lane: the losing children of a hard union, culled children of a smooth one).
 template <int K, int CAP>
 __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_instr,
                                           const float4* __restrict__ spar, const float (&px)[K],
                                           const float (&py)[K], const float (&pz)[K],
                                           const float (&abar)[K], const NodeRecords<K>& rec,
-                                          float* sacc, float (&gx)[K], float (&gy)[K],
+                                          const GradAcc acc, float (&gx)[K], float (&gy)[K],
                                           float (&gz)[K]) {
-    const int lane = threadIdx.x & 31;
     OpenNode<K> cur;
     OpenNode<K> stk[MAX_DEPTH];
     int sp = 0;
@@ -92,8 +110,7 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
                 float g = 0.f;
 #pragma unroll
                 for (int k = 0; k < K; ++k) g += cur.a[k] != 0.f ? __fdiv_rn(cur.s[k] - cur.a[k] * cur.d[k], cur.c) : 0.f;
-                g = warp_sum(g);
-                if (lane == 0 && g != 0.f) atomicAdd(sacc + off * 4, g);
+                acc.add(off * 4, g);
             }
             if (!(head & HEAD_ROOT)) cur = stk[--sp];
             continue;
@@ -109,14 +126,9 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
             posts_forward<K>(head, pv, raw, y, sg);
             child_adjoint<K>(fold, ordinal, cur, abar, y, a);
             posts_backward<K>(head, sg, a, gpost);
-            if (np) {
 #pragma unroll
-                for (int i = 0; i < 3; ++i)
-                    if (i < np) {
-                        const float g = warp_sum(gpost[i]);
-                        if (lane == 0 && g != 0.f) atomicAdd(sacc + off * 4 + i, g);
-                    }
-            }
+            for (int i = 0; i < 3; ++i)
+                if (i < np) acc.add(off * 4 + i, gpost[i]);
             if (!(head & HEAD_ROOT)) stk[sp++] = cur;
 #pragma unroll
             for (int k = 0; k < K; ++k) {
@@ -126,15 +138,47 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
             cur.c = op == OP_CLOSE_SMOOTH ? rec.c[node] : 0.f;
             continue;
         }
-        // ---- leaf: recompute q, value and local gradients --------------------------------
-        const int frame_rec = (head & HEAD_FRAME) ? off : -1;
-        const int prim_rec = off + ((head & HEAD_FRAME) ? 3 : 0);
+        // ---- leaf ------------------------------------------------------------------------
+        const bool has_frame = (head & HEAD_FRAME) != 0;
+        const int prim_rec = off + (has_frame ? 3 : 0);
         const int post_rec = prim_rec + prim_f4(op);
         float4 r0 = make_float4(1.f, 0.f, 0.f, 0.f), r1 = make_float4(0.f, 1.f, 0.f, 0.f),
                r2 = make_float4(0.f, 0.f, 1.f, 0.f);
-        if (frame_rec >= 0) { r0 = spar[frame_rec]; r1 = spar[frame_rec + 1]; r2 = spar[frame_rec + 2]; }
+        if (has_frame) { r0 = spar[off]; r1 = spar[off + 1]; r2 = spar[off + 2]; }
         const float4 pp = np ? spar[post_rec] : make_float4(0.f, 0.f, 0.f, 0.f);
         const float pv[3] = {pp.x, pp.y, pp.z};
+
+        // cheap pre-test: is any lane's adjoint of this child non-zero?
+        bool live = false;
+        if (fold == FOLD_MIN) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) live |= (cur.win[k] == ordinal) && cur.a[k] != 0.f;
+        } else if (fold == FOLD_SMOOTH) {
+            // value only (no gradients) -> softmax weight; the d/dk sum needs it for every child
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                const float qx = fmaf(r0.x, px[k], fmaf(r0.y, py[k], fmaf(r0.z, pz[k], r0.w)));
+                const float qy = fmaf(r1.x, px[k], fmaf(r1.y, py[k], fmaf(r1.z, pz[k], r1.w)));
+                const float qz = fmaf(r2.x, px[k], fmaf(r2.y, py[k], fmaf(r2.z, pz[k], r2.w)));
+                raw[k] = prim_eval<false>(op, spar + prim_rec, qx, qy, qz);
+            }
+            posts_forward<K>(head, pv, raw, y, sg);
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                const float w = expf(cur.c * (y[k] - cur.d[k]));
+                live |= cur.a[k] != 0.f && w >= CULL_EPS;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < K; ++k) live |= abar[k] != 0.f;
+        }
+        if (!__any_sync(0xffffffffu, live)) continue;
+
+        // value + local gradients; per-thread sums over the K samples of every parameter partial
+        float fr[12];                         // d/d(frame rows): A_r0 b_0 | A_r1 b_1 | A_r2 b_2
+        float pr[12];                         // d/d(primitive record)
+#pragma unroll
+        for (int i = 0; i < 12; ++i) { fr[i] = 0.f; pr[i] = 0.f; }
         float gq[K][3], gp[K][12];
 #pragma unroll
         for (int k = 0; k < K; ++k) {
@@ -145,12 +189,11 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
         }
         posts_forward<K>(head, pv, raw, y, sg);
         child_adjoint<K>(fold, ordinal, cur, abar, y, a);
-        posts_backward<K>(head, sg, a, gpost);
-        // a[k] is now the adjoint of the leaf's raw value.  Record layout of the 32 partials:
-        // [0,12) frame rows (A_r0 A_r1 A_r2 b_r), [12,24) primitive record, [24,27) post params.
-        float acc[32];
+        if (fold == FOLD_SMOOTH) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+            for (int k = 0; k < K; ++k) a[k] = fabsf(a[k]) < CULL_EPS * fabsf(cur.a[k]) ? 0.f : a[k];
+        }
+        posts_backward<K>(head, sg, a, gpost);
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             const float ak = a[k];
@@ -159,19 +202,23 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
             gx[k] += fmaf(r0.x, g0, fmaf(r1.x, g1, r2.x * g2));
             gy[k] += fmaf(r0.y, g0, fmaf(r1.y, g1, r2.y * g2));
             gz[k] += fmaf(r0.z, g0, fmaf(r1.z, g1, r2.z * g2));
-            acc[0] = fmaf(g0, px[k], acc[0]); acc[1] = fmaf(g0, py[k], acc[1]); acc[2] = fmaf(g0, pz[k], acc[2]); acc[3] += g0;
-            acc[4] = fmaf(g1, px[k], acc[4]); acc[5] = fmaf(g1, py[k], acc[5]); acc[6] = fmaf(g1, pz[k], acc[6]); acc[7] += g1;
-            acc[8] = fmaf(g2, px[k], acc[8]); acc[9] = fmaf(g2, py[k], acc[9]); acc[10] = fmaf(g2, pz[k], acc[10]); acc[11] += g2;
+            fr[0] = fmaf(g0, px[k], fr[0]); fr[1] = fmaf(g0, py[k], fr[1]); fr[2] = fmaf(g0, pz[k], fr[2]); fr[3] += g0;
+            fr[4] = fmaf(g1, px[k], fr[4]); fr[5] = fmaf(g1, py[k], fr[5]); fr[6] = fmaf(g1, pz[k], fr[6]); fr[7] += g1;
+            fr[8] = fmaf(g2, px[k], fr[8]); fr[9] = fmaf(g2, py[k], fr[9]); fr[10] = fmaf(g2, pz[k], fr[10]); fr[11] += g2;
 #pragma unroll
-            for (int i = 0; i < 12; ++i) acc[12 + i] = fmaf(ak, gp[k][i], acc[12 + i]);
+            for (int i = 0; i < 12; ++i) pr[i] = fmaf(ak, gp[k][i], pr[i]);
         }
-        acc[24] = gpost[0]; acc[25] = gpost[1]; acc[26] = gpost[2];
-        const float tot = warp_transpose_sum(acc, lane);
-        int addr = -1;
-        if (lane < 12) addr = frame_rec >= 0 ? frame_rec * 4 + lane : -1;
-        else if (lane < 24) addr = (lane - 12) < 4 * prim_f4(op) ? prim_rec * 4 + (lane - 12) : -1;
-        else if (lane < 27) addr = (lane - 24) < np ? post_rec * 4 + (lane - 24) : -1;
-        if (addr >= 0 && tot != 0.f) atomicAdd(sacc + addr, tot);
+        if (has_frame) {
+#pragma unroll
+            for (int i = 0; i < 12; ++i) acc.add(off * 4 + i, fr[i]);
+        }
+        const int n_prim = 4 * prim_f4(op);
+#pragma unroll
+        for (int i = 0; i < 12; ++i)
+            if (i < n_prim) acc.add(prim_rec * 4 + i, pr[i]);
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+            if (i < np) acc.add(post_rec * 4 + i, gpost[i]);
     }
 }
 

@@ -18,6 +18,19 @@ from . import _lib
 from ._lib import (RmCamera, RmRenderArgs, RmRenderGrads, RmRenderOut, RmTape, check, lib, ptr,
                    stream_ptr)
 
+# Backward kernels: step-length tolerance (relative to 1 + |p|_inf) below which a ray counts as
+# settled and its remaining march steps are reversed in closed form (include/rm_b200.h,
+# rm_march_bwd).  0 reverses every step of the unrolled graph.
+BWD_CONVERGE_TOL = 1e-6
+
+
+def set_backward_converge_tol(tol: float) -> float:
+    """Sets the settled-ray tolerance of the backward kernels; returns the previous value."""
+    global BWD_CONVERGE_TOL
+    old, BWD_CONVERGE_TOL = BWD_CONVERGE_TOL, float(tol)
+    return old
+
+
 MODES = ["lambertian", "distance", "proximity", "vignette", "normal", "laplacian",
          "tangent", "spin"]
 MODE_CHANNELS = [1, 1, 1, 1, 3, 1, 3, 3]
@@ -193,7 +206,7 @@ def render(tape, cam: RmCamera, poses: Tensor, *, steps: int = 32, normals_eps: 
         a = RmRenderArgs(ray_begin, n, int(steps), int(bounces), float(normals_eps), float(hit_tau),
                          float(2 * normals_eps if lift_delta is None else lift_delta),
                          int(mode_mask), int(display_mode), int(degree), int(early_exit),
-                         int(fast_math), ptr(cmap))
+                         int(fast_math), ptr(cmap), 0.0)
         t = _tape_struct(tape.code_tensor(dev), par, tape.n_nodes, tape.max_depth)
         check(lib().rm_render(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(o),
                               stream_ptr(dev)), "rm_render")
@@ -258,7 +271,7 @@ _sdf_eval.register_autograd(_sdf_eval_backward, setup_context=_sdf_eval_setup)
 
 @torch.library.custom_op("rm_b200::march_bwd", mutates_args=())
 def _march_bwd(code: Tensor, par: Tensor, origin: Tensor, dirs: Tensor, grad_pos: Tensor,
-               steps: int, n_nodes: int, max_depth: int) -> Tuple[Tensor, Tensor, Tensor]:
+               steps: int, n_nodes: int, max_depth: int, tol: float) -> Tuple[Tensor, Tensor, Tensor]:
     dev = _lib.require_cuda(par, origin, dirs, grad_pos)
     o, v, g = _flat3(origin), _flat3(dirs), _flat3(grad_pos)
     n = o.shape[0]
@@ -266,13 +279,13 @@ def _march_bwd(code: Tensor, par: Tensor, origin: Tensor, dirs: Tensor, grad_pos
     do, dv = torch.empty_like(o), torch.empty_like(v)
     dpar = torch.empty_like(par)
     tape = _tape_struct(code, par, n_nodes, max_depth)
-    check(lib().rm_march_bwd(C.byref(tape), ptr(o), ptr(v), ptr(g), n, steps, ptr(traj), ptr(do),
+    check(lib().rm_march_bwd(C.byref(tape), ptr(o), ptr(v), ptr(g), n, steps, float(tol), ptr(traj), ptr(do),
                              ptr(dv), ptr(dpar), stream_ptr(dev)), "rm_march_bwd")
     return dpar, do.reshape(origin.shape), dv.reshape(dirs.shape)
 
 
 @_march_bwd.register_fake
-def _(code, par, origin, dirs, grad_pos, steps, n_nodes, max_depth):
+def _(code, par, origin, dirs, grad_pos, steps, n_nodes, max_depth, tol):
     return torch.empty_like(par), torch.empty_like(origin), torch.empty_like(dirs)
 
 
@@ -287,7 +300,8 @@ def _march_setup(ctx, inputs, output):
 def _march_backward(ctx, grad):
     code, par, origin, dirs = ctx.saved_tensors
     steps, n_nodes, max_depth = ctx.meta
-    dpar, do, dv = _march_bwd(code, par, origin, dirs, grad.contiguous(), steps, n_nodes, max_depth)
+    dpar, do, dv = _march_bwd(code, par, origin, dirs, grad.contiguous(), steps, n_nodes, max_depth,
+                              BWD_CONVERGE_TOL)
     return None, dpar, do, dv, None, None, None, None
 
 
@@ -308,7 +322,7 @@ def _render_gbuffer(code: Tensor, par: Tensor, poses: Tensor, n_views: int, widt
     o.origin, o.dirs, o.pos, o.sdf, o.normals, o.laplacian = (ptr(origin), ptr(dirs), ptr(pos), ptr(sdf),
                                                               ptr(nrm), ptr(lap))
     poses = poses.contiguous()
-    a = RmRenderArgs(0, n, int(steps), 0, float(eps), 0.0, 0.0, 0, -1, 1, 0, 0, 0)   # IEEE math
+    a = RmRenderArgs(0, n, int(steps), 0, float(eps), 0.0, 0.0, 0, -1, 1, 0, 0, 0, 0.0)   # IEEE math
     cam = camera_struct(n_views, width, height, focal, sensor_w, sensor_h)
     t = _tape_struct(code, par, n_nodes, max_depth)
     check(lib().rm_render(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(o),
@@ -328,7 +342,7 @@ def _render_bwd(code: Tensor, par: Tensor, poses: Tensor, n_views: int, width: i
                 focal: float, sensor_w: float, sensor_h: float, steps: int, eps: float,
                 g_origin: Optional[Tensor], g_dirs: Optional[Tensor], g_pos: Optional[Tensor],
                 g_sdf: Optional[Tensor], g_normals: Optional[Tensor], g_lap: Optional[Tensor],
-                n_nodes: int, max_depth: int) -> Tuple[Tensor, Tensor]:
+                n_nodes: int, max_depth: int, tol: float) -> Tuple[Tensor, Tensor]:
     dev = _lib.require_cuda(par, poses, g_origin, g_dirs, g_pos, g_sdf, g_normals, g_lap)
     n = n_views * width * height
     cont = lambda g: None if g is None else g.contiguous()
@@ -338,7 +352,7 @@ def _render_bwd(code: Tensor, par: Tensor, poses: Tensor, n_views: int, width: i
     dpar = torch.empty_like(par)
     poses = poses.contiguous()
     dposes = torch.empty_like(poses)
-    a = RmRenderArgs(0, n, int(steps), 0, float(eps), 0.0, 0.0, 0, -1, 1, 0, 0, 0)
+    a = RmRenderArgs(0, n, int(steps), 0, float(eps), 0.0, 0.0, 0, -1, 1, 0, 0, 0, float(tol))
     cam = camera_struct(n_views, width, height, focal, sensor_w, sensor_h)
     t = _tape_struct(code, par, n_nodes, max_depth)
     check(lib().rm_render_bwd(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(grads),
@@ -348,7 +362,7 @@ def _render_bwd(code: Tensor, par: Tensor, poses: Tensor, n_views: int, width: i
 
 @_render_bwd.register_fake
 def _(code, par, poses, n_views, width, height, focal, sensor_w, sensor_h, steps, eps, g_origin, g_dirs,
-      g_pos, g_sdf, g_normals, g_lap, n_nodes, max_depth):
+      g_pos, g_sdf, g_normals, g_lap, n_nodes, max_depth, tol):
     return torch.empty_like(par), torch.empty_like(poses)
 
 
@@ -362,7 +376,8 @@ def _gbuffer_backward(ctx, g_origin, g_dirs, g_pos, g_sdf, g_normals, g_lap):
     code, par, poses = ctx.saved_tensors
     (n_views, width, height, focal, sw, sh, steps, eps, n_nodes, max_depth) = ctx.meta
     dpar, dposes = _render_bwd(code, par, poses, n_views, width, height, focal, sw, sh, steps, eps,
-                               g_origin, g_dirs, g_pos, g_sdf, g_normals, g_lap, n_nodes, max_depth)
+                               g_origin, g_dirs, g_pos, g_sdf, g_normals, g_lap, n_nodes, max_depth,
+                               BWD_CONVERGE_TOL)
     return (None, dpar, dposes) + (None,) * 10
 
 

@@ -3,7 +3,7 @@ gloo in the CPU tests).  Rays are independent (the stencil samples the SDF, not 
 pixels; ``rendering/ray_marching.py:116``), so the data path never exchanges pixels.  Only two tiny
 collectives exist:
 
-* ``allreduce_shader_range``: MIN/MAX over the 8-float reduction scratch between ``rm_render`` and
+* ``allreduce_shader_range``: one MAX over the 8-float reduction scratch (minima stored negated) between ``rm_render`` and
   ``rm_shade_finalize`` when a normalising shader (distance / proximity / laplacian; global
   ``.min()/.max()`` over the whole camera batch, ``shader.py:35-36,52-53,84``) runs on a sharded batch;
 * ``allreduce_gradients``: SUM over one flat buffer holding every scene-parameter and camera
@@ -16,10 +16,7 @@ from typing import Iterable, List, Sequence, Tuple
 import torch
 import torch.distributed as dist
 
-# layout of the reduction scratch (include/rm_b200.h): which entries combine with MIN / MAX
-REDUCE_MIN_IDX = (0, 2)
-REDUCE_MAX_IDX = (1, 3, 4, 5, 6, 7)
-
+# the reduction scratch (include/rm_b200.h) stores minima negated: every entry combines with MAX
 
 def world() -> Tuple[int, int]:
     if dist.is_available() and dist.is_initialized():
@@ -45,15 +42,10 @@ def shard_views(n_views: int, rank: int, world_size: int) -> List[int]:
 
 
 def allreduce_shader_range(reduce: torch.Tensor, group=None) -> torch.Tensor:
-    """In-place MIN/MAX all-reduce of the shader reduction scratch (no-op for a single process)."""
-    if world()[1] == 1:
-        return reduce
-    mins = reduce[list(REDUCE_MIN_IDX)].contiguous()
-    maxs = reduce[list(REDUCE_MAX_IDX)].contiguous()
-    dist.all_reduce(mins, op=dist.ReduceOp.MIN, group=group)
-    dist.all_reduce(maxs, op=dist.ReduceOp.MAX, group=group)
-    reduce[list(REDUCE_MIN_IDX)] = mins
-    reduce[list(REDUCE_MAX_IDX)] = maxs
+    """In-place MAX all-reduce of the 8-float shader reduction scratch (no-op for a single process):
+    one latency-bound collective, no staging kernels."""
+    if world()[1] > 1:
+        dist.all_reduce(reduce, op=dist.ReduceOp.MAX, group=group)
     return reduce
 
 

@@ -28,7 +28,7 @@ def test_struct_layout_matches_header():
     assert ctypes.sizeof(_lib.RmTape) == 32
     assert ctypes.sizeof(_lib.RmCamera) == 24
     assert ctypes.sizeof(_lib.RmRenderOut) == 16 * 8
-    assert ctypes.sizeof(_lib.RmRenderArgs) == 64
+    assert ctypes.sizeof(_lib.RmRenderArgs) == 72
     assert ctypes.sizeof(_lib.RmRenderGrads) == 48
 
 

@@ -241,3 +241,29 @@ def test_fused_render_bwd_unused_planes_are_skipped():
     (orc.gbuffer(qr, tr, 32)["pos"] ** 2).mean().backward()
     assert rel_err(q.grad, qr.grad) < 2e-3 and rel_err(t.grad, tr.grad) < 2e-3
     assert rel_err(flat_grads(list(scene.parameters())), flat_grads(list(ref_scene.parameters()))) < 2e-3
+
+
+@pytest.mark.parametrize("tol", [0.0, 1e-6])
+def test_backward_exact_and_settled_ray_modes_agree_with_reference(golden, tol):
+    """tol = 0 reverses every step of the unrolled graph; tol = 1e-6 (default) reverses the settled
+    tail of every ray in closed form.  Both must match the reference's autograd to 1e-3."""
+    from ray_marching_b200 import ops
+    old = ops.set_backward_converge_tol(tol)
+    try:
+        g = golden("grads")
+        for tag, build in [("scene2", S.make_test_scene2), ("syn8", lambda: S.make_synthetic_scene(8, 0, True))]:
+            scene = build()
+            loop = RenderLoop(scene, normals_eps=5e-2, **cases.config1_camera(16, 16)).to(DEV)
+            q = t32(g[f"grads/{tag}/q"]).to(DEV).requires_grad_(True)
+            t = t32(g[f"grads/{tag}/t"]).to(DEV).requires_grad_(True)
+            gb = loop.gbuffer(q, t, 32)
+            lam = (-(gb["dirs"] * gb["normals"]).sum(-1, keepdim=True)).clamp(0, 1)
+            depth = (gb["pos"] - gb["origin"]).norm(dim=-1, keepdim=True)
+            loss = ((lam - t32(g[f"grads/{tag}/lam_target"]).to(DEV)) ** 2).mean() + \
+                   ((depth - t32(g[f"grads/{tag}/depth_target"]).to(DEV)) ** 2).mean()
+            loss.backward()
+            assert rel_err(q.grad, g[f"grads/{tag}/dq"]) < 1e-3, (tag, tol)
+            assert rel_err(t.grad, g[f"grads/{tag}/dt"]) < 1e-3, (tag, tol)
+            assert rel_err(flat_grads(list(scene.parameters())), g[f"grads/{tag}/dparams_flat"]) < 1e-3, (tag, tol)
+    finally:
+        ops.set_backward_converge_tol(old)

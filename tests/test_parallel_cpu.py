@@ -38,9 +38,9 @@ def _worker(rank, ws, port, out):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=ws)
     try:
-        # shader range scratch: per-rank partial min/max/NaN flags
-        inf = float("inf")
-        red = torch.tensor([1.0 + rank, 5.0 - rank, -2.0 * rank, 0.5 * rank, 3.0 + rank, 0.0,
+        # shader range scratch: per-rank partial (-min, max, -min, max, max|lap|, 3 NaN flags);
+        # minima are stored negated so that one MAX all-reduce combines every entry
+        red = torch.tensor([-(1.0 + rank), 5.0 - rank, 2.0 * rank, 0.5 * rank, 3.0 + rank, 0.0,
                             float(rank == 1), 0.0])
         parallel.allreduce_shader_range(red)
         # gradients: one parameter has no grad on rank 1
@@ -67,7 +67,7 @@ def test_collectives_world_size_2_gloo():
         p.join(timeout=60)
         assert p.exitcode == 0
     for rank, red, ga, gb, n in res:
-        assert red == [1.0, 5.0, -2.0, 0.5, 4.0, 0.0, 1.0, 0.0]
+        assert red == [-1.0, 5.0, 2.0, 0.5, 4.0, 0.0, 1.0, 0.0]      # min 1, max 5, min -2, max .5
         assert ga == [1.5, 1.5, 1.5] and gb == [[2.0, 2.0], [2.0, 2.0]] and n == 7
 
 
