@@ -29,7 +29,10 @@ namespace rm {
 #define RM_MINB_BWD 3
 #endif
 
-constexpr int KB = 2;            // samples per thread in the backward kernels
+#ifndef RM_KB
+#define RM_KB 2
+#endif
+constexpr int KB = RM_KB;        // samples per thread in the backward kernels (2 or 4)
 constexpr int BLOCK_B = 128;
 
 __device__ __forceinline__ void load3k(const float* base, int64_t first, int64_t n, float (&x)[KB],
@@ -69,13 +72,28 @@ __device__ __forceinline__ float* traj_slot(float* traj, int s) {
 }
 __device__ __forceinline__ void traj_store(float* traj, int s, const float (&x)[KB], const float (&y)[KB],
                                            const float (&z)[KB]) {
-    float2* p = reinterpret_cast<float2*>(traj_slot(traj, s));
-    p[0] = make_float2(x[0], y[0]); p[1] = make_float2(z[0], x[1]); p[2] = make_float2(y[1], z[1]);
+    if constexpr (KB == 2) {
+        float2* p = reinterpret_cast<float2*>(traj_slot(traj, s));
+        p[0] = make_float2(x[0], y[0]); p[1] = make_float2(z[0], x[KB - 1]); p[2] = make_float2(y[KB - 1], z[KB - 1]);
+    } else {
+        static_assert(KB == 2 || KB == 4, "KB must be 2 or 4");
+        float4* p = reinterpret_cast<float4*>(traj_slot(traj, s));
+        p[0] = make_float4(x[0], y[0], z[0], x[1]);
+        p[1] = make_float4(y[1], z[1], x[KB - 2], y[KB - 2]);
+        p[2] = make_float4(z[KB - 2], x[KB - 1], y[KB - 1], z[KB - 1]);
+    }
 }
 __device__ __forceinline__ void traj_load(float* traj, int s, float (&x)[KB], float (&y)[KB], float (&z)[KB]) {
-    const float2* p = reinterpret_cast<const float2*>(traj_slot(traj, s));
-    const float2 a = p[0], b = p[1], c = p[2];
-    x[0] = a.x; y[0] = a.y; z[0] = b.x; x[1] = b.y; y[1] = c.x; z[1] = c.y;
+    if constexpr (KB == 2) {
+        const float2* p = reinterpret_cast<const float2*>(traj_slot(traj, s));
+        const float2 a = p[0], b = p[1], c = p[2];
+        x[0] = a.x; y[0] = a.y; z[0] = b.x; x[KB - 1] = b.y; y[KB - 1] = c.x; z[KB - 1] = c.y;
+    } else {
+        const float4* p = reinterpret_cast<const float4*>(traj_slot(traj, s));
+        const float4 a = p[0], b = p[1], c = p[2];
+        x[0] = a.x; y[0] = a.y; z[0] = a.z; x[1] = a.w; y[1] = b.x; z[1] = b.y;
+        x[KB - 2] = b.z; y[KB - 2] = b.w; z[KB - 2] = c.x; x[KB - 1] = c.y; y[KB - 1] = c.z; z[KB - 1] = c.w;
+    }
 }
 
 // Shared memory: [tape par (n_par floats) | accumulators (n_par x cols floats)], see GradAcc.
@@ -183,16 +201,9 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
     const bool tail = __any_sync(0xffffffffu, any_tail);
     for (int o = 16; o > 0; o >>= 1) first_exact = max(first_exact, __shfl_xor_sync(0xffffffffu, first_exact, o));
 
-    float qx[KB], qy[KB], qz[KB];          // stationary points (tail tasks)
-    float g1x[KB], g1y[KB], g1z[KB], a0[KB], rest[KB], tsum[KB];
+    float g1x[KB], g1y[KB], g1z[KB], a0[KB], rest[KB], tsum[KB];   // carried from task 5 to task 6
 #pragma unroll
-    for (int k = 0; k < KB; ++k) {
-        const int sc = conv[k] < steps ? conv[k] : 0;
-        const float* slot = traj_slot(traj, sc) + 3 * k;
-        const bool has = tail && steps > 0;
-        qx[k] = has ? slot[0] : 0.f; qy[k] = has ? slot[1] : 0.f; qz[k] = has ? slot[2] : 0.f;
-        g1x[k] = g1y[k] = g1z[k] = a0[k] = rest[k] = tsum[k] = 0.f;
-    }
+    for (int k = 0; k < KB; ++k) g1x[k] = g1y[k] = g1z[k] = a0[k] = rest[k] = tsum[k] = 0.f;
     int task = sa != nullptr ? 0 : 5;
     if (task == 5 && !tail) task = 7;
     const int n_tasks = 7 + first_exact;
@@ -211,7 +222,9 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
         } else if (task < 7) {
 #pragma unroll
             for (int k = 0; k < KB; ++k) {
-                x[k] = qx[k]; y[k] = qy[k]; z[k] = qz[k];
+                // stationary point q = p_conv, read from this lane's own slot (unused when conv == steps)
+                const float* slot = traj_slot(traj, conv[k] < steps ? conv[k] : 0) + 3 * k;
+                x[k] = slot[0]; y[k] = slot[1]; z[k] = slot[2];
                 if (task == 5) a0[k] = conv[k] < steps ? lx[k] * vx[k] + ly[k] * vy[k] + lz[k] * vz[k] : 0.f;
                 a[k] = task == 5 ? a0[k] : rest[k];
             }
@@ -394,14 +407,13 @@ render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, 
          g += (int64_t)gridDim.x * BLOCK_B) {
         const int64_t first = g * KB;
         // ---- rays from the pixel index (PinholeCamera.forward) ----
-        float ob[KB][3], vb[KB][3];
         float px[KB], py[KB], pz[KB], vx[KB], vy[KB], vz[KB];
         Pose pose;
         int cur_view = -1;
 #pragma unroll
         for (int k = 0; k < KB; ++k) {
-            float ow[3], vw[3];
-            world_ray(P.cam, poses, P.ray_begin + first + k, pose, cur_view, ob[k], vb[k], ow, vw);
+            float ob[3], vb[3], ow[3], vw[3];
+            world_ray(P.cam, poses, P.ray_begin + first + k, pose, cur_view, ob, vb, ow, vw);
             px[k] = ow[0]; py[k] = ow[1]; pz[k] = ow[2];
             vx[k] = vw[0]; vy[k] = vw[1]; vz[k] = vw[2];
         }
@@ -462,12 +474,15 @@ render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, 
                 acc_view = view;
             }
             if (valid) {
-                const Pose ps = load_pose(poses, view);
+                // camera-frame ray regenerated from the pixel index (not kept live across the passes)
+                float ob[3], vb[3], ow[3], vw[3];
+                world_ray(P.cam, poses, r, pose, cur_view, ob, vb, ow, vw);
+                const Pose& ps = pose;
                 const float lo[3] = {lx[k] + gox[k], ly[k] + goy[k], lz[k] + goz[k]};
                 const float lv[3] = {dvx[k], dvy[k], dvz[k]};
                 float dq[4] = {0.f, 0.f, 0.f, 0.f};
-                rotation_vjp(ps.q, ob[k], lo, dq);
-                rotation_vjp(ps.q, vb[k], lv, dq);
+                rotation_vjp(ps.q, ob, lo, dq);
+                rotation_vjp(ps.q, vb, lv, dq);
                 cam_acc[0] += dq[0]; cam_acc[1] += dq[1]; cam_acc[2] += dq[2]; cam_acc[3] += dq[3];
                 cam_acc[4] += lo[0]; cam_acc[5] += lo[1]; cam_acc[6] += lo[2];
             }

@@ -174,30 +174,40 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
         }
         if (!__any_sync(0xffffffffu, live)) continue;
 
-        // value + local gradients; per-thread sums over the K samples of every parameter partial
+        // value + local gradients, one sample at a time (keeps the 15 local partials of a sample
+        // short-lived); per-thread sums over the K samples of every parameter partial
         float fr[12];                         // d/d(frame rows): A_r0 b_0 | A_r1 b_1 | A_r2 b_2
         float pr[12];                         // d/d(primitive record)
 #pragma unroll
         for (int i = 0; i < 12; ++i) { fr[i] = 0.f; pr[i] = 0.f; }
-        float gq[K][3], gp[K][12];
 #pragma unroll
         for (int k = 0; k < K; ++k) {
             const float qx = fmaf(r0.x, px[k], fmaf(r0.y, py[k], fmaf(r0.z, pz[k], r0.w)));
             const float qy = fmaf(r1.x, px[k], fmaf(r1.y, py[k], fmaf(r1.z, pz[k], r1.w)));
             const float qz = fmaf(r2.x, px[k], fmaf(r2.y, py[k], fmaf(r2.z, pz[k], r2.w)));
-            raw[k] = prim_grad(op, spar + prim_rec, qx, qy, qz, gq[k], gp[k]);
-        }
-        posts_forward<K>(head, pv, raw, y, sg);
-        child_adjoint<K>(fold, ordinal, cur, abar, y, a);
-        if (fold == FOLD_SMOOTH) {
+            float gq[3], gp[12];
+            const float rawk = prim_grad(op, spar + prim_rec, qx, qy, qz, gq, gp);
+            // post-ops forward (stage signs), adjoint of the child's value, post-ops backward
+            float yk = rawk, sgk[3] = {1.f, 1.f, 1.f};
 #pragma unroll
-            for (int k = 0; k < K; ++k) a[k] = fabsf(a[k]) < CULL_EPS * fabsf(cur.a[k]) ? 0.f : a[k];
-        }
-        posts_backward<K>(head, sg, a, gpost);
+            for (int i = 0; i < 3; ++i)
+                if (i < np) {
+                    const bool onion = head_post(head, i) == POST_ONION;
+                    sgk[i] = onion ? sgn0(yk) : 1.f;
+                    yk = (onion ? fabsf(yk) : yk) - pv[i];
+                }
+            float ak;
+            if (fold == FOLD_NONE) ak = abar[k];
+            else if (fold == FOLD_MIN) ak = (cur.win[k] == ordinal) ? cur.a[k] : 0.f;
+            else {
+                const float w = expf(cur.c * (yk - cur.d[k]));
+                ak = (cur.a[k] != 0.f && w >= CULL_EPS) ? cur.a[k] * w : 0.f;
+                cur.s[k] = fmaf(ak, yk, cur.s[k]);
+            }
 #pragma unroll
-        for (int k = 0; k < K; ++k) {
-            const float ak = a[k];
-            const float g0 = ak * gq[k][0], g1 = ak * gq[k][1], g2 = ak * gq[k][2];
+            for (int i = 2; i >= 0; --i)
+                if (i < np) { gpost[i] -= ak; ak *= sgk[i]; }
+            const float g0 = ak * gq[0], g1 = ak * gq[1], g2 = ak * gq[2];
             // world-space gradient: A^T (a gq)
             gx[k] += fmaf(r0.x, g0, fmaf(r1.x, g1, r2.x * g2));
             gy[k] += fmaf(r0.y, g0, fmaf(r1.y, g1, r2.y * g2));
@@ -206,7 +216,7 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
             fr[4] = fmaf(g1, px[k], fr[4]); fr[5] = fmaf(g1, py[k], fr[5]); fr[6] = fmaf(g1, pz[k], fr[6]); fr[7] += g1;
             fr[8] = fmaf(g2, px[k], fr[8]); fr[9] = fmaf(g2, py[k], fr[9]); fr[10] = fmaf(g2, pz[k], fr[10]); fr[11] += g2;
 #pragma unroll
-            for (int i = 0; i < 12; ++i) pr[i] = fmaf(ak, gp[k][i], pr[i]);
+            for (int i = 0; i < 12; ++i) pr[i] = fmaf(ak, gp[i], pr[i]);
         }
         if (has_frame) {
 #pragma unroll

@@ -21,7 +21,7 @@ from ._lib import (RmCamera, RmRenderArgs, RmRenderGrads, RmRenderOut, RmTape, c
 # Backward kernels: step-length tolerance (relative to 1 + |p|_inf) below which a ray counts as
 # settled and its remaining march steps are reversed in closed form (include/rm_b200.h,
 # rm_march_bwd).  0 reverses every step of the unrolled graph.
-BWD_CONVERGE_TOL = 1e-6
+BWD_CONVERGE_TOL = 1e-7
 
 
 def set_backward_converge_tol(tol: float) -> float:
