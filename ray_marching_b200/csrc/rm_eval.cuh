@@ -27,6 +27,9 @@ __device__ __forceinline__ float prim_eval(int op, const float4* P, float x, flo
 // an online log-sum-exp of x_i = c * f_i (c = -k, or -k*log2(e) in FAST mode): a0 = running
 // max, a1 = sum of exp(x_i - a0).  Equals the reference's max-shifted logsumexp
 // (transformations.py:69-70) up to rounding.
+//
+// Decode per instruction: one 16-byte constant load (prefetched one instruction ahead), one add
+// for the record address, a switch on the dispatch id, a switch on the tail selector.
 template <int K, bool FAST, int CAP>
 __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_instr,
                                            const float4* __restrict__ spar, const float (&px)[K],
@@ -37,111 +40,125 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
     float c = 0.f;                                   // scale of the innermost open smooth union
     float stk[MAX_DEPTH * (2 * K + 1)];              // spilled accumulators of enclosing unions
     int sp = 0;
+    const char* sbytes = reinterpret_cast<const char*>(spar);
 #pragma unroll
     for (int k = 0; k < K; ++k) { a0[k] = 0.f; a1[k] = 0.f; d[k] = 0.f; }
 
-    int2 nxt = C.ins[0];
+    int4 nxt = C.ins[0];
     for (int pc = 0; pc < n_instr; ++pc) {
-        const int2 ins = nxt;
-        nxt = C.ins[pc + 1 < n_instr ? pc + 1 : pc];   // prefetch: hides the constant-load latency
-        const int head = ins.x;
-        const float4* P = spar + word_par(ins.y);
-        const int op = head_op(head);
-        if (op < OP_OPEN_MIN) {
-            if (head & HEAD_FRAME) {                 // q = A p + b  (composed affine chain)
-                const float4 r0 = P[0], r1 = P[1], r2 = P[2];
-                P += 3;
-                // the switch sits outside the K loop: one uniform jump per instruction
+        const int4 ins = nxt;
+        nxt = C.ins[pc + 1];                          // prefetch (pad entry after the last instruction)
+        const float4* P = reinterpret_cast<const float4*>(sbytes + ins.z);
+
 #define RM_LEAF_FRAME(EXPR)                                                                     \
-    _Pragma("unroll") for (int k = 0; k < K; ++k) {                                             \
-        const float x = fmaf(r0.x, px[k], fmaf(r0.y, py[k], fmaf(r0.z, pz[k], r0.w)));          \
-        const float y = fmaf(r1.x, px[k], fmaf(r1.y, py[k], fmaf(r1.z, pz[k], r1.w)));          \
-        const float z = fmaf(r2.x, px[k], fmaf(r2.y, py[k], fmaf(r2.z, pz[k], r2.w)));          \
-        d[k] = EXPR;                                                                            \
-    }
-                switch (op) {
-                    case OP_SPHERE: { const float4 p0 = P[0]; RM_LEAF_FRAME(prim_sphere<FAST>(p0, x, y, z)) } break;
-                    case OP_BOX: { const float4 p0 = P[0]; RM_LEAF_FRAME(prim_box<FAST>(p0, x, y, z)) } break;
-                    case OP_TORUS: { const float4 p0 = P[0]; RM_LEAF_FRAME(prim_torus<FAST>(p0, x, y, z)) } break;
-                    case OP_LINE: { const float4 p0 = P[0], p1 = P[1], p2 = P[2]; RM_LEAF_FRAME(prim_line<FAST>(p0, p1, p2, x, y, z)) } break;
-                    case OP_DISK: { const float4 p0 = P[0]; RM_LEAF_FRAME(prim_disk<FAST>(p0, x, y, z)) } break;
-                    default: { RM_LEAF_FRAME(x) } break;
-                }
-#undef RM_LEAF_FRAME
-            } else {
+    {                                                                                           \
+        const float4 r0 = P[0], r1 = P[1], r2 = P[2];                                           \
+        const float4 p0 = P[3];                                                                 \
+        (void)p0;                                                                               \
+        _Pragma("unroll") for (int k = 0; k < K; ++k) {                                         \
+            const float x = fmaf(r0.x, px[k], fmaf(r0.y, py[k], fmaf(r0.z, pz[k], r0.w)));      \
+            const float y = fmaf(r1.x, px[k], fmaf(r1.y, py[k], fmaf(r1.z, pz[k], r1.w)));      \
+            const float z = fmaf(r2.x, px[k], fmaf(r2.y, py[k], fmaf(r2.z, pz[k], r2.w)));      \
+            (void)y; (void)z;                                                                   \
+            d[k] = EXPR;                                                                        \
+        }                                                                                       \
+    }                                                                                           \
+    break;
 #define RM_LEAF_WORLD(EXPR)                                                                     \
-    _Pragma("unroll") for (int k = 0; k < K; ++k) {                                             \
-        const float x = px[k], y = py[k], z = pz[k];                                            \
-        (void)y; (void)z;                                                                       \
-        d[k] = EXPR;                                                                            \
-    }
-                switch (op) {
-                    case OP_SPHERE: { const float4 p0 = P[0]; RM_LEAF_WORLD(prim_sphere<FAST>(p0, x, y, z)) } break;
-                    case OP_BOX: { const float4 p0 = P[0]; RM_LEAF_WORLD(prim_box<FAST>(p0, x, y, z)) } break;
-                    case OP_TORUS: { const float4 p0 = P[0]; RM_LEAF_WORLD(prim_torus<FAST>(p0, x, y, z)) } break;
-                    case OP_LINE: { const float4 p0 = P[0], p1 = P[1], p2 = P[2]; RM_LEAF_WORLD(prim_line<FAST>(p0, p1, p2, x, y, z)) } break;
-                    case OP_DISK: { const float4 p0 = P[0]; RM_LEAF_WORLD(prim_disk<FAST>(p0, x, y, z)) } break;
-                    default: { RM_LEAF_WORLD(x) } break;
+    {                                                                                           \
+        const float4 p0 = P[0];                                                                 \
+        (void)p0;                                                                               \
+        _Pragma("unroll") for (int k = 0; k < K; ++k) {                                         \
+            const float x = px[k], y = py[k], z = pz[k];                                        \
+            (void)y; (void)z;                                                                   \
+            d[k] = EXPR;                                                                        \
+        }                                                                                       \
+    }                                                                                           \
+    break;
+        switch (ins_disp(ins.w)) {
+            case OP_SPHERE: RM_LEAF_WORLD(prim_sphere<FAST>(p0, x, y, z))
+            case OP_BOX: RM_LEAF_WORLD(prim_box<FAST>(p0, x, y, z))
+            case OP_TORUS: RM_LEAF_WORLD(prim_torus<FAST>(p0, x, y, z))
+            case OP_LINE: RM_LEAF_WORLD(prim_line<FAST>(p0, P[1], P[2], x, y, z))
+            case OP_DISK: RM_LEAF_WORLD(prim_disk<FAST>(p0, x, y, z))
+            case OP_PLANE: RM_LEAF_WORLD(x)                               // primitives.py:40-41
+            case OP_SPHERE | DISP_FRAME: RM_LEAF_FRAME(prim_sphere<FAST>(p0, x, y, z))
+            case OP_BOX | DISP_FRAME: RM_LEAF_FRAME(prim_box<FAST>(p0, x, y, z))
+            case OP_TORUS | DISP_FRAME: RM_LEAF_FRAME(prim_torus<FAST>(p0, x, y, z))
+            case OP_LINE | DISP_FRAME: RM_LEAF_FRAME(prim_line<FAST>(p0, P[4], P[5], x, y, z))
+            case OP_DISK | DISP_FRAME: RM_LEAF_FRAME(prim_disk<FAST>(p0, x, y, z))
+            case OP_PLANE | DISP_FRAME: RM_LEAF_FRAME(x)
+            case DISP_OPEN_MIN:
+            case DISP_OPEN_SMOOTH: {
+                if (!(ins.x & HEAD_ROOT)) {
+                    float* s = stk + sp * (2 * K + 1);
+#pragma unroll
+                    for (int k = 0; k < K; ++k) { s[2 * k] = a0[k]; s[2 * k + 1] = a1[k]; }
+                    s[2 * K] = c;
+                    ++sp;
                 }
-#undef RM_LEAF_WORLD
+                if (ins_disp(ins.w) == DISP_OPEN_MIN) {
+#pragma unroll
+                    for (int k = 0; k < K; ++k) a0[k] = CUDART_INF_F;
+                } else {
+                    c = M::exp_scale(P[0].x);
+#pragma unroll
+                    for (int k = 0; k < K; ++k) { a0[k] = -CUDART_INF_F; a1[k] = 0.f; }
+                }
+                continue;
             }
-            P += prim_f4(op);
-        } else if (op <= OP_OPEN_SMOOTH) {
-            if (!(head & HEAD_ROOT)) {
-                float* s = stk + sp * (2 * K + 1);
+            default: {                                // CLOSE: finish this union, restore parent
+                if (ins_disp(ins.w) == DISP_CLOSE_MIN) {
 #pragma unroll
-                for (int k = 0; k < K; ++k) { s[2 * k] = a0[k]; s[2 * k + 1] = a1[k]; }
-                s[2 * K] = c;
-                ++sp;
-            }
-            if (op == OP_OPEN_MIN) {
+                    for (int k = 0; k < K; ++k) d[k] = a0[k];
+                } else {
 #pragma unroll
-                for (int k = 0; k < K; ++k) a0[k] = CUDART_INF_F;
-            } else {
-                c = M::exp_scale(P[0].x);
+                    for (int k = 0; k < K; ++k) d[k] = M::div(a0[k] + M::log(a1[k]), c);
+                }
+                if (!(ins.x & HEAD_ROOT)) {
+                    --sp;
+                    const float* s = stk + sp * (2 * K + 1);
 #pragma unroll
-                for (int k = 0; k < K; ++k) { a0[k] = -CUDART_INF_F; a1[k] = 0.f; }
-            }
-            continue;
-        } else {                                      // CLOSE: finish this union, restore parent
-            if (op == OP_CLOSE_MIN) {
-#pragma unroll
-                for (int k = 0; k < K; ++k) d[k] = a0[k];
-            } else {
-#pragma unroll
-                for (int k = 0; k < K; ++k) d[k] = M::div(a0[k] + M::log(a1[k]), c);
-            }
-            if (!(head & HEAD_ROOT)) {
-                --sp;
-                const float* s = stk + sp * (2 * K + 1);
-#pragma unroll
-                for (int k = 0; k < K; ++k) { a0[k] = s[2 * k]; a1[k] = s[2 * k + 1]; }
-                c = s[2 * K];
+                    for (int k = 0; k < K; ++k) { a0[k] = s[2 * k]; a1[k] = s[2 * k + 1]; }
+                    c = s[2 * K];
+                }
+                break;
             }
         }
-        // unary value ops attached to this instruction (rounding / onion)
-        const int np = head_npost(head);
-        if (np) {
-            const float4 pp = P[0];
-            const float pv[3] = {pp.x, pp.y, pp.z};
+#undef RM_LEAF_FRAME
+#undef RM_LEAF_WORLD
+
+        // tail = fold * 4 + post case: unary value ops (rounding / onion), then the parent's fold
+        const int tail = ins_tail(ins.w);
+        if (tail == 0) continue;                      // the root's CLOSE
+        const int post = tail & 3;
+        if (post != TAIL_POST_NONE) {
+            const float4 pp = *reinterpret_cast<const float4*>(sbytes + ins_post_off(ins.w));
+            if (post == TAIL_POST_ONION) {
 #pragma unroll
-            for (int i = 0; i < 3; ++i) {
-                if (i < np) {
-                    if (head_post(head, i) == POST_ONION) {
+                for (int k = 0; k < K; ++k) d[k] = fabsf(d[k]) - pp.x;
+            } else if (post == TAIL_POST_ROUND) {
 #pragma unroll
-                        for (int k = 0; k < K; ++k) d[k] = fabsf(d[k]) - pv[i];
-                    } else {
+                for (int k = 0; k < K; ++k) d[k] = d[k] - pp.x;
+            } else {
+                const float pv[3] = {pp.x, pp.y, pp.z};
+                const int np = head_npost(ins.x);
 #pragma unroll
-                        for (int k = 0; k < K; ++k) d[k] = d[k] - pv[i];
+                for (int i = 0; i < 3; ++i) {
+                    if (i < np) {
+                        const bool onion = head_post(ins.x, i) == POST_ONION;
+#pragma unroll
+                        for (int k = 0; k < K; ++k) d[k] = (onion ? fabsf(d[k]) : d[k]) - pv[i];
                     }
                 }
             }
         }
-        const int fold = head_fold(head);
-        if (fold == FOLD_MIN) {
+        if (tail < 2 * 4) {
+            if (tail >= 4) {                          // FOLD_MIN
 #pragma unroll
-            for (int k = 0; k < K; ++k) a0[k] = min_nan(a0[k], d[k]);
-        } else if (fold == FOLD_SMOOTH) {
+                for (int k = 0; k < K; ++k) a0[k] = min_nan(a0[k], d[k]);
+            }
+        } else {                                      // FOLD_SMOOTH
 #pragma unroll
             for (int k = 0; k < K; ++k) {
                 const float x = c * d[k];

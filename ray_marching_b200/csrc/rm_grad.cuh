@@ -140,7 +140,7 @@ __device__ __forceinline__ void eval_record(const TapeCode<CAP>& C, const int n_
 #pragma unroll
     for (int k = 0; k < K; ++k) { a0[k] = a1[k] = d[k] = 0.f; }
     for (int pc = 0; pc < n_instr; ++pc) {
-        const int2 ins = C.ins[pc];
+        const int4 ins = C.ins[pc];
         const int head = ins.x, op = head_op(head);
         const int node = word_node(ins.y);
         const float4* P = spar + word_par(ins.y);

@@ -53,12 +53,12 @@ inline size_t tape_smem_bytes(const RmTape* t) { return (size_t)t->n_par * 4; }
         if ((tape)->n_instr <= rm::CODE_CAP_SMALL) {                                     \
             constexpr int CAP = rm::CODE_CAP_SMALL;                                      \
             rm::TapeCode<CAP> code;                                                      \
-            memcpy(code.ins, (tape)->code_host, (size_t)(tape)->n_instr * sizeof(int2)); \
+            rm::expand_code((tape)->code_host, (tape)->n_instr, code.ins);              \
             __VA_ARGS__                                                                  \
         } else {                                                                         \
             constexpr int CAP = rm::CODE_CAP_LARGE;                                      \
             rm::TapeCode<CAP> code;                                                      \
-            memcpy(code.ins, (tape)->code_host, (size_t)(tape)->n_instr * sizeof(int2)); \
+            rm::expand_code((tape)->code_host, (tape)->n_instr, code.ins);              \
             __VA_ARGS__                                                                  \
         }                                                                                \
     } while (0)

@@ -100,7 +100,7 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
     cur.c = 0.f;
 
     for (int pc = n_instr - 1; pc >= 0; --pc) {
-        const int2 ins = C.ins[pc];
+        const int4 ins = C.ins[pc];
         const int head = ins.x, op = head_op(head);
         const int fold = head_fold(head), np = head_npost(head);
         const int off = word_par(ins.y), node = word_node(ins.y), ordinal = head_ordinal(head);

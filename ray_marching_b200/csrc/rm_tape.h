@@ -39,12 +39,48 @@ __host__ __device__ __forceinline__ int prim_f4(int op) {
 }
 
 // Code block passed BY VALUE as a __grid_constant__ kernel parameter.  Two capacities keep the
-// launch-parameter copy small for the registry scenes (768 B) while covering 512-primitive tapes.
+// launch-parameter copy small for the registry scenes (1.5 KB) while covering 512-primitive tapes.
+// Each instruction is expanded on the host (expand_code) to 16 bytes:
+//   x, y : word0, word1 as above (the backward kernels decode these)
+//   z    : byte offset of the instruction's first parameter record in the staged block
+//   w    : post-op record byte offset [0:20] | tail selector [20:24] | dispatch id [24:32]
+// so that the forward interpreter needs one add for the record address, one switch on the
+// dispatch id (leaf kind x has-frame, or union op) and one switch on the tail selector
+// (fold kind x {no post-op, one rounding, one onion, generic chain}).
 constexpr int CODE_CAP_SMALL = 96;
 constexpr int CODE_CAP_LARGE = 1024;
 template <int CAP>
 struct TapeCode {
-    int2 ins[CAP];
+    int4 ins[CAP + 1];     // + one pad entry: the interpreter prefetches ins[pc + 1] unconditionally
 };
+
+enum : int { DISP_FRAME = 8, DISP_OPEN_MIN = 16, DISP_OPEN_SMOOTH = 17, DISP_CLOSE_MIN = 18, DISP_CLOSE_SMOOTH = 19 };
+enum : int { TAIL_POST_NONE = 0, TAIL_POST_ROUND = 1, TAIL_POST_ONION = 2, TAIL_POST_CHAIN = 3 };  // tail = fold * 4 + post case
+
+__host__ __device__ __forceinline__ int ins_disp(int w) { return (int)((unsigned)w >> 24); }
+__host__ __device__ __forceinline__ int ins_tail(int w) { return (w >> 20) & 15; }
+__host__ __device__ __forceinline__ int ins_post_off(int w) { return w & 0xFFFFF; }
+
+// Host: [n][2] words -> expanded instructions.
+inline void expand_code(const int32_t* words, int n, int4* out) {
+    for (int i = 0; i < n; ++i) {
+        const int head = words[2 * i], w1 = words[2 * i + 1];
+        const int op = head_op(head), np = head_npost(head), fold = head_fold(head);
+        const int off = word_par(w1);
+        int disp, post_f4 = off;
+        if (op < OP_OPEN_MIN) {
+            disp = op | ((head & HEAD_FRAME) ? DISP_FRAME : 0);
+            post_f4 = off + ((head & HEAD_FRAME) ? 3 : 0) + prim_f4(op);
+        } else {
+            disp = DISP_OPEN_MIN + (op - OP_OPEN_MIN);
+        }
+        int post_case = TAIL_POST_NONE;
+        if (np == 1) post_case = head_post(head, 0) == POST_ONION ? TAIL_POST_ONION : TAIL_POST_ROUND;
+        else if (np > 1) post_case = TAIL_POST_CHAIN;
+        const int tail = (op == OP_OPEN_MIN || op == OP_OPEN_SMOOTH) ? 0 : fold * 4 + post_case;
+        out[i] = make_int4(head, w1, off * 16, ((np ? post_f4 * 16 : 0) & 0xFFFFF) | (tail << 20) | (disp << 24));
+    }
+    out[n] = make_int4(0, 0, 0, 0);
+}
 
 }  // namespace rm
