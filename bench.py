@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Benchmark of the sphere-tracing hot path (contract: see the task statement / DESIGN.md §Measurement).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c1|c2|c3|c4|c5] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload c1|c2|c3|c4|c4b|c5] [--impl reference]
 
 A *step* is one pass of the hot path over one batch of synthetic input: one rendered frame (one
 view per GPU; weak scaling), or, for c4, one forward+backward of the inverse-rendering loss.
@@ -60,6 +60,10 @@ def workload(name: str):
         return dict(name=name, scene=S.make_test_scene2,
                     desc="inverse rendering fwd+bwd, make_test_scene2 1024x1024, lambertian+depth MSE",
                     width=1024, height=1024, modes=(0,), bounces=0, cam_t=(0.0, 0.1, 1.0), backward=True)
+    if name == "c4b":
+        return dict(name=name, scene=lambda: S.make_synthetic_scene(64, 0, True),
+                    desc="inverse rendering fwd+bwd, synthetic-64 in shell (650 params) 1024x1024, lambertian+depth MSE",
+                    width=1024, height=1024, modes=(0,), bounces=0, cam_t=(0.0, 0.0, -4.0), backward=True)
     if name == "c5":
         return dict(name=name, scene=lambda: S.make_synthetic_scene(512, 0, True),
                     desc="synthetic-512 smooth union in shell, 3840x2160 per view, lambertian",
@@ -182,6 +186,7 @@ def run_gpu(args):
     loop = RenderLoop(scene, num_cameras=1, px_width=W, px_height=H, focal_length=PX * H,
                       sensor_width=PX * W, sensor_height=PX * H, normals_eps=EPS).to(dev)
     loop.early_exit = bool(args.early_exit)
+    loop.cull = bool(args.cull)
     tape = tape_of(loop.scene)
     rays = W * H                                   # per GPU and step: one view per rank (weak scaling)
     fpr = flops_per_ray(tape, wl)
@@ -256,13 +261,35 @@ def run_gpu(args):
             e0.record()
             ops.render(tape, loop.camera.struct(), poses_k, steps=STEPS, normals_eps=EPS,
                        mode_mask=mask_k, bounces=wl["bounces"], early_exit=loop.early_exit,
-                       fast_math=loop.fast_math, cmap=loop.shader.cyclic_cmap, finalize=False,
+                       fast_math=2 if (loop.fast_math and loop.cull) else int(loop.fast_math),
+                       cmap=loop.shader.cyclic_cmap, finalize=False,
                        reduce=res_holder["res"].reduce if needs_reduce else None,
                        out=res_holder["res"])
             e1.record()
             e1.synchronize()
             ks.append(e0.elapsed_time(e1))
         kern_ms = sum(ks) / len(ks)
+
+    # the same frame with bounding-sphere culling of smooth-union children:
+    # executed work < algorithmic work, results equal to 1e-5 relative depth (tests)
+    cull_info = None
+    if not wl["backward"] and tape._cull_union is not None and not loop.cull:
+        loop.cull = True
+        for _ in range(3):
+            gpu_step()
+        torch.cuda.synchronize()
+        ce0, ce1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n_c = max(3, min(args.steps, 10))
+        ce0.record()
+        for _ in range(n_c):
+            gpu_step()
+        ce1.record()
+        ce1.synchronize()
+        cull_ms = ce0.elapsed_time(ce1) / n_c
+        loop.cull = False
+        cull_info = {"ms_per_step": cull_ms, "value": rays / (cull_ms * 1e-3) / 1e6, "unit": "Mrays/s",
+                     "note": "per-GPU, bounding-sphere culling of smooth-union children inside march "
+                             "steps; executed < algorithmic work, so no roofline fraction is quoted"}
 
     # end-to-end: pinned host pose in, images out to pinned host memory, every step
     e2e = measure_e2e(frame, wl, q, t, dev, args, barrier) if not wl["backward"] else \
@@ -292,7 +319,7 @@ def run_gpu(args):
             "config": {"workload": f"{wl['name']}: {wl['desc']}", "rays_per_gpu_per_step": rays,
                        "marching_steps": STEPS, "views": world, "sharding": "one view per GPU",
                        "l2": "flushed between timed iterations (192 MB memset, untimed)",
-                       "early_exit": bool(args.early_exit), "tape": tape.describe(),
+                       "early_exit": bool(args.early_exit), "cull": bool(args.cull), "tape": tape.describe(),
                        "msteps_per_s": value * STEPS * (wl["bounces"] + 1),
                        "wall_s_timed_region": wall},
             "e2e": {"value": rays * world / (e2e_ms / args.steps * 1e-3) / 1e6, "unit": "Mrays/s",
@@ -300,6 +327,8 @@ def run_gpu(args):
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks,
         }
+        if cull_info is not None:
+            line["culling"] = cull_info
         if kern_ms is not None:
             ach = fpr * rays / (kern_max * 1e-3) / 1e12
             line["roofline"] = {
@@ -494,6 +523,8 @@ def cpu_sample_size(wl):
         return wl["width"], wl["height"], "full frame"
     if wl["name"] == "c4":
         return 512, 512, "512x512 sub-sample of the 1024x1024 frame (same intrinsics per pixel), fwd+bwd"
+    if wl["name"] == "c4b":
+        return 96, 96, "96x96 sub-sample of the 1024x1024 frame (same intrinsics per pixel), fwd+bwd"
     if wl["name"] == "c3":
         return 192, 108, "192x108 sub-sample of the 4K frame, all 3 march segments"
     return 64, 36, "64x36 sub-sample of one 4K view"
@@ -555,10 +586,13 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c4", "c5"])
+    ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c4", "c4b", "c5"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--early-exit", type=int, default=0,
                     help="1: bit-identical fixed-point exit of the march loop (executed < algorithmic work)")
+    ap.add_argument("--cull", type=int, default=0,
+                    help="1: make bounding-sphere culling the measured configuration (default: reported "
+                         "beside the fully evaluated headline for the smooth-union workloads)")
     ap.add_argument("--cpu-budget", type=float, default=20.0)
     args = ap.parse_args()
     if args.impl == "reference":

@@ -36,7 +36,8 @@ typedef struct RmTape {
     const int32_t* code_host; /* HOST [n_instr][2] instruction words (static per scene structure):
                                  word0 = op[0:4] frame[4] fold[5:7] root[7] npost[8:10] posts[10:16]
                                  ordinal[16:32]; word1 = parameter offset in float4 units [0:16],
-                                 union node id [16:32].  Copied into the launch parameters.        */
+                                 union node id [16:31], culling flag [31] (csrc/rm_tape.h).
+                                 Copied into the launch parameters.                               */
     const float*   par;       /* DEVICE [n_par] parameter records, 16-byte aligned (live values)  */
     int32_t n_instr;          /* <= 1024 */
     int32_t n_par;            /* multiple of 4 */
@@ -102,7 +103,9 @@ typedef struct RmRenderArgs {
     int32_t display_mode;   /* mode index shaded into rgba, or -1 */
     int32_t degree;         /* colour-wheel multiplicity of modes 6,7 */
     int32_t early_exit;     /* 1: stop marching a ray once p stops changing (bit-identical) */
-    int32_t fast_math;      /* 1: approximate sqrt/exp inside march steps (stencil stays IEEE) */
+    int32_t fast_math;      /* 1: approximate sqrt/exp inside march steps (stencil stays IEEE);
+                               2: additionally skip smooth-union children whose bounding sphere proves
+                               their softmax term < 2^-30 of the largest one (march steps only)      */
     const float* cmap;      /* [4096][3] cyclic colour LUT for modes 6,7 (may be NULL otherwise) */
     float   bwd_converge_tol; /* rm_render_bwd only: see rm_march_bwd (0 = reverse every step) */
 } RmRenderArgs;

@@ -45,6 +45,7 @@ class RenderLoop(nn.Module):
         self.shader = Shader()
         self.early_exit = False          # bit-identical fixed-point exit of the march loop
         self.fast_math = True            # approximate sqrt/exp inside march steps only
+        self.cull = False                # bounding-sphere culling of smooth-union children (march steps)
 
     # ---- fused, no autograd -------------------------------------------------------------
     def render_planes(self, orientations: Tensor, translations: Tensor, *, modes: Sequence[int] = (),
@@ -63,7 +64,8 @@ class RenderLoop(nn.Module):
                           normals_eps=self.normals.normals_eps, mode_mask=mask, gbuffer=gbuffer,
                           display_mode=display_mode, degree=degree, bounces=bounces,
                           hit_tau=hit_tau, lift_delta=lift_delta, early_exit=self.early_exit,
-                          fast_math=self.fast_math, cmap=self.shader.cyclic_cmap,
+                          fast_math=2 if (self.fast_math and self.cull) else int(self.fast_math),
+                          cmap=self.shader.cyclic_cmap,
                           ray_begin=ray_begin, n_rays=n_rays, finalize=finalize, out=out)
 
     def display_frame(self, orientations: Tensor, translations: Tensor, mode: int = 0,

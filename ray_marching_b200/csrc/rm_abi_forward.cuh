@@ -45,13 +45,17 @@ extern "C" int rm_march(const RmTape* tape, const float* origin, const float* di
     if (n == 0) return RM_OK;
     const size_t sm = tape_smem_bytes(tape);
     RM_WITH_CODE(tape, {
-        if (fast_math) {
-            if (int s = prepare_smem(march_kernel<true, CAP>, sm)) return s;
-            march_kernel<true, CAP><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
+        if (fast_math >= 2) {
+            if (int s = prepare_smem(march_kernel<true, CAP, true>, sm)) return s;
+            march_kernel<true, CAP, true><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
+                code, tape->par, tape->n_instr, tape->n_par, origin, dirs, n, steps, pos_out);
+        } else if (fast_math) {
+            if (int s = prepare_smem(march_kernel<true, CAP, false>, sm)) return s;
+            march_kernel<true, CAP, false><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, origin, dirs, n, steps, pos_out);
         } else {
-            if (int s = prepare_smem(march_kernel<false, CAP>, sm)) return s;
-            march_kernel<false, CAP><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
+            if (int s = prepare_smem(march_kernel<false, CAP, false>, sm)) return s;
+            march_kernel<false, CAP, false><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, origin, dirs, n, steps, pos_out);
         }
     });
@@ -115,13 +119,17 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
     P.cmap = a->cmap; P.out = *out;
     const size_t sm = tape_smem_bytes(tape);
     RM_WITH_CODE(tape, {
-        if (a->fast_math) {
-            if (int s = prepare_smem(render_kernel<true, CAP>, sm)) return s;
-            render_kernel<true, CAP><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+        if (a->fast_math >= 2) {
+            if (int s = prepare_smem(render_kernel<true, CAP, true>, sm)) return s;
+            render_kernel<true, CAP, true><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+                code, tape->par, tape->n_instr, tape->n_par, poses, P);
+        } else if (a->fast_math) {
+            if (int s = prepare_smem(render_kernel<true, CAP, false>, sm)) return s;
+            render_kernel<true, CAP, false><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
         } else {
-            if (int s = prepare_smem(render_kernel<false, CAP>, sm)) return s;
-            render_kernel<false, CAP><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+            if (int s = prepare_smem(render_kernel<false, CAP, false>, sm)) return s;
+            render_kernel<false, CAP, false><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
         }
     });

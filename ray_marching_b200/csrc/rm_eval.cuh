@@ -30,12 +30,29 @@ __device__ __forceinline__ float prim_eval(int op, const float4* P, float x, flo
 //
 // Decode per instruction: one 16-byte constant load (prefetched one instruction ahead), one add
 // for the record address, a switch on the dispatch id, a switch on the tail selector.
-template <int K, bool FAST, int CAP>
+//
+// CULL (march steps only): the children of one designated smooth union carry a
+// bounding sphere (world centre c, radius R with f_i(p) >= s_min (|p - c| - R) outside it).  A child
+// is skipped when, for every ray of the warp, its term is below 2^-30 of a LOWER bound of the
+// union's largest term: thr = max(running max, c_k (h + L m) - log2 n), where h is the union's value
+// at the previous march position, m the distance moved since and L the Lipschitz bound of the scene
+// (max term >= logsumexp - log n, and f_U(p') <= f_U(p) + L |p' - p|).  `hint` carries h in and
+// the union's value at this point out; `move` is m (+inf disables the seed).
+constexpr float CULL_LOG2 = -30.0f;
+
+template <int K, bool FAST, int CAP, bool CULL = false>
 __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_instr,
                                            const float4* __restrict__ spar, const float (&px)[K],
                                            const float (&py)[K], const float (&pz)[K],
-                                           float (&out)[K]) {
+                                           float (&out)[K], float* hint = nullptr,
+                                           const float* move = nullptr) {
     using M = Math<FAST>;
+    float seed[CULL ? K : 1];                        // lower bound of the culled union's largest term
+    float cs = 0.f;                                  // c * s_min of the culled union (<= 0)
+    if (CULL) {
+#pragma unroll
+        for (int k = 0; k < (CULL ? K : 1); ++k) seed[k] = -CUDART_INF_F;
+    }
     float a0[K], a1[K], d[K];
     float c = 0.f;                                   // scale of the innermost open smooth union
     float stk[MAX_DEPTH * (2 * K + 1)];              // spilled accumulators of enclosing unions
@@ -49,6 +66,21 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
         const int4 ins = nxt;
         nxt = C.ins[pc + 1];                          // prefetch (pad entry after the last instruction)
         const float4* P = reinterpret_cast<const float4*>(sbytes + ins.z);
+        const int disp_raw = ins_disp(ins.w);
+        const int disp = disp_raw & ~DISP_CULL;
+        if (CULL) {
+            if ((disp_raw & DISP_CULL) && disp < DISP_OPEN_MIN) {
+                const float4 cr = P[-1];             // bounding sphere of this leaf
+                bool skip = true;
+#pragma unroll
+                for (int k = 0; k < K; ++k) {
+                    const float dx = px[k] - cr.x, dy = py[k] - cr.y, dz = pz[k] - cr.z;
+                    const float t = M::sqrt(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) - cr.w;
+                    skip = skip && t > 0.f && (cs * t - fmaxf(a0[k], seed[k]) < CULL_LOG2);
+                }
+                if (__all_sync(0xffffffffu, skip)) continue;
+            }
+        }
 
 #define RM_LEAF_FRAME(EXPR)                                                                     \
     {                                                                                           \
@@ -75,7 +107,7 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
         }                                                                                       \
     }                                                                                           \
     break;
-        switch (ins_disp(ins.w)) {
+        switch (disp) {
             case OP_SPHERE: RM_LEAF_WORLD(prim_sphere<FAST>(p0, x, y, z))
             case OP_BOX: RM_LEAF_WORLD(prim_box<FAST>(p0, x, y, z))
             case OP_TORUS: RM_LEAF_WORLD(prim_torus<FAST>(p0, x, y, z))
@@ -97,23 +129,35 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
                     s[2 * K] = c;
                     ++sp;
                 }
-                if (ins_disp(ins.w) == DISP_OPEN_MIN) {
+                if (disp == DISP_OPEN_MIN) {
 #pragma unroll
                     for (int k = 0; k < K; ++k) a0[k] = CUDART_INF_F;
                 } else {
-                    c = M::exp_scale(P[0].x);
+                    const float4 u = P[0];           // (-k, s_min, L_max, log2 n)
+                    c = M::exp_scale(u.x);
 #pragma unroll
                     for (int k = 0; k < K; ++k) { a0[k] = -CUDART_INF_F; a1[k] = 0.f; }
+                    if (CULL && (disp_raw & DISP_CULL) && u.w > 0.f) {
+                        cs = c * u.y;
+#pragma unroll
+                        for (int k = 0; k < (CULL ? K : 1); ++k)
+                            seed[k] = fmaf(c, fmaf(u.z, move[k], hint[k]), -u.w);
+                    }
                 }
                 continue;
             }
             default: {                                // CLOSE: finish this union, restore parent
-                if (ins_disp(ins.w) == DISP_CLOSE_MIN) {
+                if (disp == DISP_CLOSE_MIN) {
 #pragma unroll
                     for (int k = 0; k < K; ++k) d[k] = a0[k];
                 } else {
 #pragma unroll
                     for (int k = 0; k < K; ++k) d[k] = M::div(a0[k] + M::log(a1[k]), c);
+                    if (CULL && (disp_raw & DISP_CULL)) {
+#pragma unroll
+                        for (int k = 0; k < (CULL ? K : 1); ++k) hint[k] = d[k];
+                        cs = 0.f;
+                    }
                 }
                 if (!(ins.x & HEAD_ROOT)) {
                     --sp;

@@ -150,15 +150,20 @@ camera_kernel(CamParams cam, const float* __restrict__ poses, int64_t ray_begin,
 }
 
 // ---- the march loop (ray_marching.py:78-84): p <- f(p) v + p --------------------------------
-template <bool FAST, int CAP>
+// CULL: see eval_scene.  The union value of the previous step and the step length bound the union
+// value at the new position (|v| = 1, so the ray moved |f(p)|).
+template <bool FAST, int CAP, bool CULL>
 __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                            int steps, bool early_exit,
                                            float (&px)[K], float (&py)[K], float (&pz)[K],
                                            const float (&vx)[K], const float (&vy)[K],
                                            const float (&vz)[K]) {
     float d[K];
+    float hint[CULL ? K : 1], move[CULL ? K : 1];
+#pragma unroll
+    for (int k = 0; k < (CULL ? K : 1); ++k) { hint[k] = CUDART_INF_F; move[k] = 0.f; }
     for (int s = 0; s < steps; ++s) {                 // one interpreter instance (instruction cache)
-        eval_scene<K, FAST, CAP>(code, n_instr, spar, px, py, pz, d);
+        eval_scene<K, FAST, CAP, CULL>(code, n_instr, spar, px, py, pz, d, hint, move);
         bool moved = false;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
@@ -167,6 +172,7 @@ __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_inst
             const float nz = fmaf(d[k], vz[k], pz[k]);
             if (early_exit) moved |= (nx != px[k]) | (ny != py[k]) | (nz != pz[k]);
             px[k] = nx; py[k] = ny; pz[k] = nz;
+            if (CULL) move[CULL ? k : 0] = fabsf(d[k]) * 1.0001f;   // |v| = 1 up to rounding
         }
         // A ray whose position did not change is at a fixed point of the update: all further
         // steps reproduce it bit for bit, so leaving the loop (when the whole warp is there) does
@@ -175,7 +181,7 @@ __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_inst
     }
 }
 
-template <bool FAST, int CAP>
+template <bool FAST, int CAP, bool CULL>
 __global__ void __launch_bounds__(BLOCK)
 march_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
              const float* __restrict__ origin, const float* __restrict__ dirs, int64_t n, int steps,
@@ -187,7 +193,7 @@ march_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n
     float px[K], py[K], pz[K], vx[K], vy[K], vz[K];
     load3(origin, first, n, px, py, pz);
     load3(dirs, first, n, vx, vy, vz);
-    march_rays<FAST, CAP>(code, n_instr, spar, steps, false, px, py, pz, vx, vy, vz);
+    march_rays<FAST, CAP, CULL>(code, n_instr, spar, steps, false, px, py, pz, vx, vy, vz);
     store3(out, first, n, px, py, pz);
 }
 

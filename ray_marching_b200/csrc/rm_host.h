@@ -36,6 +36,8 @@ inline int check_tape(const RmTape* t) {
         else if (op == OP_CLOSE_MIN || op == OP_CLOSE_SMOOTH) --depth;
         else return fail(RM_ERR_INVALID, "tape instruction %d has unknown opcode %d", i, op);
         if (depth < 0 || depth > MAX_DEPTH) return fail(RM_ERR_INVALID, "tape unions are unbalanced at instruction %d", i);
+        if (word_cull(w1) && op >= OP_SPHERE && op <= OP_TORUS && off < 1)
+            return fail(RM_ERR_INVALID, "tape instruction %d: bounding-sphere record missing", i);
         if (need > 0 && off + need > n_f4)
             return fail(RM_ERR_INVALID, "tape instruction %d reads parameters beyond the block", i);
         if ((op == OP_OPEN_MIN || op == OP_OPEN_SMOOTH || op == OP_CLOSE_MIN || op == OP_CLOSE_SMOOTH) &&

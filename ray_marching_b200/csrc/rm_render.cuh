@@ -64,7 +64,7 @@ __device__ __forceinline__ void block_minmax(MinMax m, float* gmin, float* gmax,
     }
 }
 
-template <bool FAST, int CAP>
+template <bool FAST, int CAP, bool CULL>
 __global__ void __launch_bounds__(BLOCK, RM_MINB)
 render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
               const float* __restrict__ poses, const __grid_constant__ RenderParams P) {
@@ -93,7 +93,7 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
         for (int k = 0; k < K; ++k) { px[k] = ox[k]; py[k] = oy[k]; pz[k] = oz[k]; }
 
         for (int b = 0;; ++b) {
-            march_rays<FAST, CAP>(code, n_instr, spar, P.steps, P.early_exit != 0, px, py, pz, vx, vy, vz);
+            march_rays<FAST, CAP, CULL>(code, n_instr, spar, P.steps, P.early_exit != 0, px, py, pz, vx, vy, vz);
             stencil_eval<CAP>(code, n_instr, spar, P.st, need_stencil, px, py, pz, f, nx, ny, nz, lap);
             if (b >= P.bounces) break;
             // reflected-ray branch (reflect = control.py:179-194)

@@ -2,7 +2,7 @@
 //
 // An instruction is two 32-bit words:
 //   word0: op[0:4] frame[4] fold[5:7] root[7] npost[8:10] post kinds[10:16] ordinal[16:32]
-//   word1: parameter offset in float4 units [0:16], union node id [16:32]
+//   word1: parameter offset in float4 units [0:16], union node id [16:31], culling flag [31]
 // The code block travels in the kernel-parameter space (constant bank): with a warp-uniform
 // program counter every decode step (load, field extraction, compare, branch) is issued on the
 // uniform datapath (LDCU / USHF / UISETP / BRA.U) and costs no vector registers, no BSSY/BSYNC
@@ -31,7 +31,10 @@ __host__ __device__ __forceinline__ int head_npost(int h) { return (h >> 8) & 3;
 __host__ __device__ __forceinline__ int head_post(int h, int i) { return (h >> (10 + 2 * i)) & 3; }
 __host__ __device__ __forceinline__ int head_ordinal(int h) { return (int)((unsigned)h >> 16); }
 __host__ __device__ __forceinline__ int word_par(int w) { return w & 0xFFFF; }
-__host__ __device__ __forceinline__ int word_node(int w) { return (int)((unsigned)w >> 16); }
+__host__ __device__ __forceinline__ int word_node(int w) { return (w >> 16) & 0x7FFF; }
+// word1 bit 31: leaf -> a bounding-sphere record (world centre, radius / s_min) sits right before its
+// first record; OPEN/CLOSE_SMOOTH -> this is the union whose children carry those records
+__host__ __device__ __forceinline__ bool word_cull(int w) { return w < 0; }
 
 // float4 records occupied by the primitive parameters of a leaf op
 __host__ __device__ __forceinline__ int prim_f4(int op) {
@@ -54,6 +57,7 @@ struct TapeCode {
     int4 ins[CAP + 1];     // + one pad entry: the interpreter prefetches ins[pc + 1] unconditionally
 };
 
+enum : int { DISP_CULL = 32 };   // dispatch flag: bounding-sphere culling applies (see word_cull)
 enum : int { DISP_FRAME = 8, DISP_OPEN_MIN = 16, DISP_OPEN_SMOOTH = 17, DISP_CLOSE_MIN = 18, DISP_CLOSE_SMOOTH = 19 };
 enum : int { TAIL_POST_NONE = 0, TAIL_POST_ROUND = 1, TAIL_POST_ONION = 2, TAIL_POST_CHAIN = 3 };  // tail = fold * 4 + post case
 
@@ -78,6 +82,7 @@ inline void expand_code(const int32_t* words, int n, int4* out) {
         if (np == 1) post_case = head_post(head, 0) == POST_ONION ? TAIL_POST_ONION : TAIL_POST_ROUND;
         else if (np > 1) post_case = TAIL_POST_CHAIN;
         const int tail = (op == OP_OPEN_MIN || op == OP_OPEN_SMOOTH) ? 0 : fold * 4 + post_case;
+        if (word_cull(w1) && op != OP_OPEN_MIN && op != OP_CLOSE_MIN) disp |= DISP_CULL;
         out[i] = make_int4(head, w1, off * 16, ((np ? post_f4 * 16 : 0) & 0xFFFFF) | (tail << 20) | (disp << 24));
     }
     out[n] = make_int4(0, 0, 0, 0);

@@ -162,11 +162,13 @@ class RenderResult:
 def render(tape, cam: RmCamera, poses: Tensor, *, steps: int = 32, normals_eps: float = 5e-2,
            mode_mask: int = 0, gbuffer: bool = False, display_mode: int = -1, degree: int = 1,
            bounces: int = 0, hit_tau: float = 1e-3, lift_delta: Optional[float] = None,
-           early_exit: bool = False, fast_math: bool = True, cmap: Optional[Tensor] = None,
+           early_exit: bool = False, fast_math: int = 1, cmap: Optional[Tensor] = None,
            ray_begin: int = 0, n_rays: Optional[int] = None, finalize: bool = True,
            reduce: Optional[Tensor] = None, out: Optional[RenderResult] = None) -> RenderResult:
     """One launch of the fused camera->march->stencil->shade kernel (no autograd).
 
+    ``fast_math``: 0 IEEE everywhere, 1 approximate sqrt/exp inside march steps, 2 additionally
+    bounding-sphere culling of smooth-union children inside march steps.
     ``finalize=False`` leaves modes 1/2/5 un-normalised (so a sharded job can all-reduce
     ``result.reduce`` first and then call :func:`shade_finalize`)."""
     dev = _lib.require_cuda(poses)

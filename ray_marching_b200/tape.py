@@ -55,6 +55,8 @@ MAX_DEPTH = 8           # union nesting depth supported by the interpreter's spi
 MAX_INSTR = 1024        # largest kernel-parameter code block (csrc/rm_tape.h)
 MAX_ORDINAL = 0xFFFF    # children per union
 MAX_PAR_F4 = 0xFFFF     # parameter records addressable by an instruction (float4 units)
+WORD1_CULL = 1 << 31    # leaf: a bounding-sphere record precedes its first record; OPEN/CLOSE: the culled union
+CULL_MIN_CHILDREN = 8   # smooth unions smaller than this are not worth bounding-sphere tests
 
 _PRIM_OP = {"SDFSphere": OP_SPHERE, "SDFBox": OP_BOX, "SDFPlane": OP_PLANE,
             "SDFLine": OP_LINE, "SDFDisk": OP_DISK, "SDFTorus": OP_TORUS}
@@ -73,13 +75,13 @@ def encode_head(op, frame=False, fold=0, posts=()):
 
 
 def decode(word0: int, word1: int):
-    """(op, has_frame, fold, root, post kinds, ordinal, par offset in float4, node id)."""
+    """(op, has_frame, fold, root, post kinds, ordinal, par offset in float4, node id, cull flag)."""
     word0 &= 0xFFFFFFFF
     word1 &= 0xFFFFFFFF
     npost = (word0 >> 8) & 3
     posts = [(word0 >> (10 + 2 * i)) & 3 for i in range(npost)]
     return (word0 & 15, bool(word0 & HEAD_FRAME), (word0 >> 5) & 3, bool(word0 & HEAD_ROOT), posts,
-            word0 >> 16, word1 & 0xFFFF, word1 >> 16)
+            word0 >> 16, word1 & 0xFFFF, (word1 >> 16) & 0x7FFF, bool(word1 & WORD1_CULL))
 
 
 class _Src:
@@ -121,6 +123,14 @@ class Tape:
         self.flops_per_eval = 0
         self.leaf_kinds: List[int] = []
 
+        # forward culling: the largest smooth union gets bounding spheres for its
+        # leaf children, so the march can skip children whose softmax term is provably negligible
+        smooth = [m for m in root.modules() if type(m).__name__ == "SDFSmoothUnion"]
+        big = max(smooth, key=lambda m: len(m.sdfs), default=None)
+        self._cull_union = big if big is not None and len(big.sdfs) >= CULL_MIN_CHILDREN else None
+        self._cull_leaves: List[dict] = []
+        self._in_cull = False
+
         self._ord = [0]                     # next child ordinal of every open union (root: dummy)
         self._emit(root, frame=-1, fold=FOLD_NONE, posts=[], depth=0)
 
@@ -136,7 +146,7 @@ class Tape:
         for head, off4, ordinal, node in self._code:
             if ordinal > MAX_ORDINAL:
                 raise NotImplementedError(f"a union with more than {MAX_ORDINAL} children")
-            words.append([head | (ordinal << 16), off4 | (node << 16)])
+            words.append([head | (ordinal << 16), off4 | ((node & 0x7FFF) << 16) | (node & WORD1_CULL)])
         # uint32 bit patterns stored as int32 (two's complement), contiguous (n_instr, 2)
         self.code = np.ascontiguousarray(np.asarray(words, dtype=np.uint32).reshape(-1, 2)
                                          .view(np.int32))
@@ -209,20 +219,26 @@ class Tape:
             self.max_depth = max(self.max_depth, depth + 1)
             ordinal = self._next_ordinal()
             root = HEAD_ROOT if depth == 0 else 0      # nothing to save / restore around the root union
+            culled = node is self._cull_union
+            flag = WORD1_CULL if culled else 0
             if smooth:
-                off4 = self._f4([("neg_theta", self._slot(node.blend_k))])
-                self._code.append([encode_head(OP_OPEN_SMOOTH) | root, off4, 0, node_id])
+                # (-k, s_min, L_max, log2 n): the last three are 0 unless this is the culled union
+                off4 = self._f4([("neg_theta", self._slot(node.blend_k))] +
+                                ([("cullu", 0), ("cullu", 1), ("cullu", 2)] if culled else []))
+                self._code.append([encode_head(OP_OPEN_SMOOTH) | root, off4, 0, node_id | flag])
             else:
                 self._code.append([encode_head(OP_OPEN_MIN) | root, 0, 0, node_id])
             child_fold = FOLD_SMOOTH if smooth else FOLD_MIN
             self._ord.append(0)
             for child in node.sdfs:
+                self._in_cull = culled                  # only DIRECT children carry a bounding sphere
                 self._emit(child, frame, child_fold, [], depth + 1)
+            self._in_cull = False
             self._ord.pop()
             kinds, entries = self._post_record(posts)
             off4 = self._f4(entries) if kinds else 0
             op = OP_CLOSE_SMOOTH if smooth else OP_CLOSE_MIN
-            self._code.append([encode_head(op, False, fold, kinds) | root, off4, ordinal, node_id])
+            self._code.append([encode_head(op, False, fold, kinds) | root, off4, ordinal, node_id | flag])
             return
         if kind not in _PRIM_OP:
             raise NotImplementedError(f"cannot lower scene node of type {kind}")
@@ -230,6 +246,28 @@ class Tape:
         self.flops_per_eval += _PRIM_FLOPS[op]
         self.n_leaves += 1
         self.leaf_kinds.append(op)
+        cull = self._in_cull and op != OP_PLANE          # a half-space has no bounding sphere
+        self._in_cull = False
+        if cull:
+            ci = len(self._cull_leaves)
+            self._f4([("cull", ci * 4 + i) for i in range(4)])    # world centre, radius / s_min
+            pz = self.n_theta                                      # index of the padding zero
+            info = dict(frame=frame, add=[pz] * 4, box=[pz] * 3, ls=[pz] * 3, le=[pz] * 3)
+            adds = [self._slot(p) for _, p in posts]
+            if op in (OP_SPHERE, OP_DISK):
+                adds.append(self._slot(node.radius))
+            elif op == OP_TORUS:
+                adds += [self._slot(node.radius1), self._slot(node.radius2)]
+            elif op == OP_BOX:
+                info["box"] = [self._slot(node.halfsides) + i for i in range(3)]
+            elif op == OP_LINE:
+                adds.append(self._slot(node.radius))
+                info["ls"] = [self._slot(node.start) + i for i in range(3)]
+                info["le"] = [self._slot(node.end) + i for i in range(3)]
+            if len(adds) > 4:
+                raise NotImplementedError("too many radius terms for a bounding sphere")
+            info["add"] = adds + [pz] * (4 - len(adds))
+            self._cull_leaves.append(info)
         first = len(self._src) // 4
         if frame >= 0:
             for r in range(3):
@@ -251,14 +289,25 @@ class Tape:
         kinds, entries = self._post_record(posts)
         if kinds:
             self._f4(entries)
-        self._code.append([encode_head(op, frame >= 0, fold, kinds), first, self._next_ordinal(), 0])
+        self._code.append([encode_head(op, frame >= 0, fold, kinds), first, self._next_ordinal(),
+                           WORD1_CULL if cull else 0])
 
     # ------------------------------------------------------------------ lowering recipe
     def _finalise_recipe(self):
         nA, nL, P = len(self._affines), len(self._lines), self.n_theta
+        nC = len(self._cull_leaves)
         base = {"zero": 0, "theta": 1, "neg_theta": 1 + P, "AB": 1 + 2 * P,
                 "ABn": 1 + 2 * P + 3 * nL, "A": 1 + 2 * P + 6 * nL,
-                "b": 1 + 2 * P + 6 * nL + 9 * nA}
+                "b": 1 + 2 * P + 6 * nL + 9 * nA, "cull": 1 + 2 * P + 6 * nL + 12 * nA,
+                "cullu": 1 + 2 * P + 6 * nL + 12 * nA + 4 * nC}
+        i64 = lambda rows: torch.tensor(rows, dtype=torch.int64).reshape(len(rows), -1)
+        self._cull_idx = None
+        if nC:
+            self._cull_idx = dict(
+                frame=torch.tensor([c["frame"] for c in self._cull_leaves], dtype=torch.int64),
+                add=i64([c["add"] for c in self._cull_leaves]), box=i64([c["box"] for c in self._cull_leaves]),
+                ls=i64([c["ls"] for c in self._cull_leaves]), le=i64([c["le"] for c in self._cull_leaves]))
+        self._cull_n = len(self._cull_union.sdfs) if self._cull_union is not None else 0
         self._perm = torch.tensor([base[piece] + idx for piece, idx in self._src],
                                   dtype=torch.int64)
         ar3, ar4 = np.arange(3), np.arange(4)
@@ -288,6 +337,7 @@ class Tape:
                 perm=mv(self._perm), q_idx=mv(self._q_idx), t_idx=mv(self._t_idx),
                 ls_idx=mv(self._ls_idx), le_idx=mv(self._le_idx),
                 levels=[(mv(a), mv(b)) for a, b in self._levels],
+                cull=None if self._cull_idx is None else {k: mv(v) for k, v in self._cull_idx.items()},
             )
         return self._dev_cache[key]
 
@@ -325,7 +375,42 @@ class Tape:
                 b = b.index_put((idx,), (Ai @ b[parent][..., None])[..., 0] + b[idx])
                 A = A.index_put((idx,), Ai @ Ap)
             pieces += [A.reshape(-1), b.reshape(-1)]
+        if self._cull_union is not None:
+            pieces += self._cull_pieces(theta, d, A if len(self._affines) else None,
+                                        b if len(self._affines) else None)
         return torch.cat(pieces)[d["perm"]]
+
+    def _cull_pieces(self, theta, d, A, b):
+        """Bounding spheres of the culled union's leaf children (not differentiated): world centre and
+        radius / s_min per leaf, and (s_min, L_max, log2 n) for the union record, where every frame
+        satisfies s_min |dx| <= |A dx| <= L_max |dx|.  Left at zero (= culling off) while autograd
+        records: the differentiable forward runs in IEEE mode, which never culls."""
+        nC = len(self._cull_leaves)
+        if theta.requires_grad and torch.is_grad_enabled():
+            return [theta.new_zeros(4 * nC), theta.new_zeros(3)]
+        with torch.no_grad():
+            c = d["cull"]
+            tp = torch.cat([theta.detach(), theta.new_zeros(1)])
+            radius = tp[c["add"]].sum(-1) + tp[c["box"]].norm(dim=-1)
+            s, e = tp[c["ls"]], tp[c["le"]]
+            radius = radius + 0.5 * (e - s).norm(dim=-1)
+            centre = 0.5 * (s + e)                                   # local centre (capsule midpoint)
+            smin = theta.new_ones(nC)
+            lmax = theta.new_ones(())
+            if A is not None:
+                sv = torch.linalg.svdvals(A.detach().double()).to(theta.dtype)    # (nA, 3) descending
+                lmax = torch.clamp(sv[:, 0].max(), min=1.0)
+                has = c["frame"] >= 0
+                f = c["frame"].clamp(min=0)
+                Ainv = torch.linalg.inv(A.detach().double()).to(theta.dtype)
+                world = (Ainv[f] @ (centre - b.detach()[f])[..., None])[..., 0]
+                centre = torch.where(has[:, None], world, centre)
+                smin = torch.where(has, sv[f, 2], smin)
+            smin_all = torch.clamp(smin.min(), max=1.0) if nC else theta.new_ones(())
+            rec = torch.cat([centre, (radius / smin)[:, None]], dim=-1).reshape(-1)
+            import math
+            union = torch.stack([smin_all, lmax, theta.new_tensor(math.log2(max(self._cull_n, 1)))])
+            return [rec, union]
 
     def lowered_params(self, device=None) -> torch.Tensor:
         """Current ``par`` on the parameters' device (``device`` only matters for a scene

@@ -22,7 +22,7 @@ def run(tape, par, pts):
     stack, acc = [], None
     d = None
     for w0, w1 in code.tolist():
-        op, has_frame, fold, _root, posts, _ordinal, off, _node = T.decode(w0, w1)
+        op, has_frame, fold, _root, posts, _ordinal, off, _node, _cull = T.decode(w0, w1)
         P = off
         if op < T.OP_OPEN_MIN:
             qx, qy, qz = x, y, z

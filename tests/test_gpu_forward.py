@@ -257,3 +257,30 @@ def test_config1_full_size_properties():
     d = res.images[1]
     assert d.min().item() == 0.0 and abs(d.max().item() - 1.0) < 1e-6
     assert torch.isnan(res.images[2]).all()
+
+
+@pytest.mark.parametrize("n_prims", [64, 512])
+def test_culling_matches_full_evaluation(n_prims):
+    """Bounding-sphere culling of smooth-union children (march steps only): hit
+    positions equal the fully evaluated march to 1e-5 relative depth and the oracle to 1e-4."""
+    scene = S.make_synthetic_scene(n_prims, 0, True)
+    intr = cases.config1_camera(96, 54)
+    loop = RenderLoop(scene, normals_eps=5e-2, **intr).to(DEV)
+    q = torch.tensor([[1.0, 0.0, 0.0, 0.0]], device=DEV)
+    t = torch.tensor([[0.0, 0.0, -4.0]], device=DEV)
+    full = loop.render_planes(q, t, gbuffer=True, modes=(0,))
+    loop.cull = True
+    cul = loop.render_planes(q, t, gbuffer=True, modes=(0,))
+    depth = lambda r: (r.pos - r.origin).norm(dim=-1)
+    rel = ((depth(cul) - depth(full)).abs() / depth(full)).max().item()
+    assert rel < 1e-5, rel
+    assert (cul.images[0] - full.images[0]).abs().max().item() < 1e-3
+    if n_prims == 64:
+        ref_scene = S.make_synthetic_scene(n_prims, 0, True)
+        orc = O.RenderLoopOracle(ref_scene, normals_eps=5e-2, **intr)
+        with torch.no_grad():
+            gb = orc.gbuffer(q.cpu(), t.cpu(), 32)
+        dref = (gb["pos"] - gb["px"]).norm(dim=-1).reshape(-1)
+        settled = gb["dists"].reshape(-1).abs() < 1e-4       # grazing rays are still moving at step 32
+        assert settled.float().mean().item() > 0.9
+        assert ((depth(cul).cpu() - dref).abs() / dref)[settled].max().item() < 1e-4
