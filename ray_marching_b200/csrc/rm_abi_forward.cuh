@@ -44,7 +44,7 @@ extern "C" int rm_march(const RmTape* tape, const float* origin, const float* di
         return fail(RM_ERR_INVALID, "rm_march: null buffer or negative count");
     if (n == 0) return RM_OK;
     const size_t sm = tape_smem_bytes(tape);
-    RM_WITH_CODE(tape, {
+    RM_WITH_CODE_EX(tape, fast_math >= 2, {
         if (fast_math >= 2) {
             if (int s = prepare_smem(march_kernel<true, CAP, true>, sm)) return s;
             march_kernel<true, CAP, true><<<grid_for(n), BLOCK, sm, (cudaStream_t)stream>>>(
@@ -118,7 +118,7 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
     P.display_mode = a->display_mode; P.degree = a->degree; P.early_exit = a->early_exit;
     P.cmap = a->cmap; P.out = *out;
     const size_t sm = tape_smem_bytes(tape);
-    RM_WITH_CODE(tape, {
+    RM_WITH_CODE_EX(tape, a->fast_math >= 2, {
         if (a->fast_math >= 2) {
             if (int s = prepare_smem(render_kernel<true, CAP, true>, sm)) return s;
             render_kernel<true, CAP, true><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(

@@ -40,13 +40,28 @@ __device__ __forceinline__ float prim_eval(int op, const float4* P, float x, flo
 // the union's value at this point out; `move` is m (+inf disables the seed).
 constexpr float CULL_LOG2 = -30.0f;
 
-template <int K, bool FAST, int CAP, bool CULL = false>
+// RECORD (backward kernels): per union node, its raw value (before post-ops) and -- hard unions --
+// the winning child ordinal (first index on ties, as torch.min(dim)), kept in local memory and
+// touched only at union boundaries; the reverse sweep (rm_sweep.cuh) consumes them.
+constexpr int MAX_NODES = 16;      // union nodes supported by the backward records
+template <int K>
+struct NodeRecords {
+    float d[MAX_NODES][K];     // raw value of the union (before its post-ops)
+    int win[MAX_NODES][K];     // winning child ordinal (hard unions)
+    float c[MAX_NODES];        // -k of smooth unions
+};
+
+// CULLMODE: 0 = the code carries no culling flags; 1 = flags present (a culling launch) but this
+// instance evaluates every child (IEEE stencil samples); 2 = cull.
+template <int K, bool FAST, int CAP, int CULLMODE = 0, bool RECORD = false>
 __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_instr,
                                            const float4* __restrict__ spar, const float (&px)[K],
                                            const float (&py)[K], const float (&pz)[K],
                                            float (&out)[K], float* hint = nullptr,
-                                           const float* move = nullptr) {
+                                           const float* move = nullptr,
+                                           NodeRecords<K>* rec = nullptr) {
     using M = Math<FAST>;
+    constexpr bool CULL = CULLMODE == 2;
     float seed[CULL ? K : 1];                        // lower bound of the culled union's largest term
     float cs = 0.f;                                  // c * s_min of the culled union (<= 0)
     if (CULL) {
@@ -67,7 +82,7 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
         nxt = C.ins[pc + 1];                          // prefetch (pad entry after the last instruction)
         const float4* P = reinterpret_cast<const float4*>(sbytes + ins.z);
         const int disp_raw = ins_disp(ins.w);
-        const int disp = disp_raw & ~DISP_CULL;
+        const int disp = CULLMODE ? (disp_raw & ~DISP_CULL) : disp_raw;  // flags are only set for culling launches
         if (CULL) {
             if ((disp_raw & DISP_CULL) && disp < DISP_OPEN_MIN) {
                 const float4 cr = P[-1];             // bounding sphere of this leaf
@@ -131,10 +146,11 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
                 }
                 if (disp == DISP_OPEN_MIN) {
 #pragma unroll
-                    for (int k = 0; k < K; ++k) a0[k] = CUDART_INF_F;
+                    for (int k = 0; k < K; ++k) { a0[k] = CUDART_INF_F; if (RECORD) a1[k] = __int_as_float(0); }
                 } else {
                     const float4 u = P[0];           // (-k, s_min, L_max, log2 n)
                     c = M::exp_scale(u.x);
+                    if (RECORD) rec->c[word_node(ins.y)] = c;
 #pragma unroll
                     for (int k = 0; k < K; ++k) { a0[k] = -CUDART_INF_F; a1[k] = 0.f; }
                     if (CULL && (disp_raw & DISP_CULL) && u.w > 0.f) {
@@ -149,7 +165,10 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
             default: {                                // CLOSE: finish this union, restore parent
                 if (disp == DISP_CLOSE_MIN) {
 #pragma unroll
-                    for (int k = 0; k < K; ++k) d[k] = a0[k];
+                    for (int k = 0; k < K; ++k) {
+                        d[k] = a0[k];
+                        if (RECORD) rec->win[word_node(ins.y)][k] = __float_as_int(a1[k]);
+                    }
                 } else {
 #pragma unroll
                     for (int k = 0; k < K; ++k) d[k] = M::div(a0[k] + M::log(a1[k]), c);
@@ -158,6 +177,10 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
                         for (int k = 0; k < (CULL ? K : 1); ++k) hint[k] = d[k];
                         cs = 0.f;
                     }
+                }
+                if (RECORD) {
+#pragma unroll
+                    for (int k = 0; k < K; ++k) rec->d[word_node(ins.y)][k] = d[k];
                 }
                 if (!(ins.x & HEAD_ROOT)) {
                     --sp;
@@ -199,8 +222,15 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
         }
         if (tail < 2 * 4) {
             if (tail >= 4) {                          // FOLD_MIN
+                if (RECORD) {
+                    const int ordinal = head_ordinal(ins.x);
 #pragma unroll
-                for (int k = 0; k < K; ++k) a0[k] = min_nan(a0[k], d[k]);
+                    for (int k = 0; k < K; ++k)
+                        if (d[k] < a0[k]) { a0[k] = d[k]; a1[k] = __int_as_float(ordinal); }   // strict: first wins ties
+                } else {
+#pragma unroll
+                    for (int k = 0; k < K; ++k) a0[k] = min_nan(a0[k], d[k]);
+                }
             }
         } else {                                      // FOLD_SMOOTH
 #pragma unroll

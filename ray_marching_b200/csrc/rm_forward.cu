@@ -2,8 +2,8 @@
 //
 // Thread mapping: every thread owns K consecutive rays (pixels), so a warp covers 32*K
 // consecutive pixels of a row: coherent rays, 128-bit stores for 1-channel planes and three
-// 128-bit stores per 4 rays for 3-channel planes.  K = 4 rays x 128 threads with the register
-// budget capped at 64 (8 resident blocks = 32 warps per SM) measured best on B200: the path is
+// 128-bit stores per 4 rays for 3-channel planes.  K = 4 rays x 256 threads with the register
+// budget capped at 64 (4 resident blocks = 32 warps per SM) measured best on B200: the path is
 // bound by the latency of the decode -> parameter load -> MUFU chains, which resident warps hide
 // (profiles/r01: K=4/154 regs 0.65 ms, K=8/229 regs 0.60 ms, K=2/64 regs 0.59 ms, K=4/64 regs
 // 0.45 ms on config 2).  The tape's instruction words arrive in the
@@ -23,10 +23,10 @@
 #define RM_K 4
 #endif
 #ifndef RM_BLOCK
-#define RM_BLOCK 128
+#define RM_BLOCK 256
 #endif
 #ifndef RM_MINB
-#define RM_MINB 8
+#define RM_MINB 4
 #endif
 
 namespace rm {
@@ -163,7 +163,7 @@ __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_inst
 #pragma unroll
     for (int k = 0; k < (CULL ? K : 1); ++k) { hint[k] = CUDART_INF_F; move[k] = 0.f; }
     for (int s = 0; s < steps; ++s) {                 // one interpreter instance (instruction cache)
-        eval_scene<K, FAST, CAP, CULL>(code, n_instr, spar, px, py, pz, d, hint, move);
+        eval_scene<K, FAST, CAP, CULL ? 2 : 0>(code, n_instr, spar, px, py, pz, d, hint, move);
         bool moved = false;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
@@ -201,7 +201,7 @@ march_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n
 // One call site of the interpreter; the samples are folded into the normal / Laplacian on the fly
 // (o_0, the running sum, and Ainv (o_j - o_0) accumulated column by column, in the reference's
 // summation order) so that no per-sample storage and no sample-dependent branch is needed.
-template <int CAP>
+template <int CAP, bool CULLFLAGS = false>
 __device__ __forceinline__ void stencil_eval(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                              const Stencil& st, bool need_offsets,
                                              const float (&px)[K], const float (&py)[K],
@@ -216,7 +216,7 @@ __device__ __forceinline__ void stencil_eval(const TapeCode<CAP>& code, int n_in
         const float dx = st.off[j][0], dy = st.off[j][1], dz = st.off[j][2];
 #pragma unroll
         for (int k = 0; k < K; ++k) { x[k] = px[k] + dx; y[k] = py[k] + dy; z[k] = pz[k] + dz; }
-        eval_scene<K, false, CAP>(code, n_instr, spar, x, y, z, d);
+        eval_scene<K, false, CAP, CULLFLAGS ? 1 : 0>(code, n_instr, spar, x, y, z, d);
         const float wx = st.w[j][0], wy = st.w[j][1], wz = st.w[j][2];
         const float first = st.first[j], in_sum = st.in_sum[j];
 #pragma unroll

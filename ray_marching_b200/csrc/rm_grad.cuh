@@ -18,8 +18,6 @@
 
 namespace rm {
 
-constexpr int MAX_NODES = 16;      // union nodes supported by the backward records
-
 __device__ __forceinline__ float sgn0(float x) { return x > 0.f ? 1.f : (x < 0.f ? -1.f : 0.f); }
 __device__ __forceinline__ float inv_or_zero(float n) { return n > 0.f ? __fdiv_rn(1.f, n) : 0.f; }
 
@@ -118,107 +116,14 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
-// Per-thread records of pass 1 (local memory; touched only at union boundaries).
-template <int K>
-struct NodeRecords {
-    float d[MAX_NODES][K];     // raw value of the union (before its post-ops)
-    int win[MAX_NODES][K];     // winning child ordinal (hard unions)
-    float c[MAX_NODES];        // -k of smooth unions
-};
-
-// Pass 1: forward evaluation (IEEE math) that fills the node records.  Returns f(p_k).
+// Pass 1 of the scene VJP: forward evaluation (IEEE math) that fills the node records -- the
+// interpreter of rm_eval.cuh in RECORD mode.  Returns f(p_k).
 template <int K, int CAP>
 __device__ __forceinline__ void eval_record(const TapeCode<CAP>& C, const int n_instr,
                                             const float4* __restrict__ spar, const float (&px)[K],
                                             const float (&py)[K], const float (&pz)[K],
                                             NodeRecords<K>& rec, float (&out)[K]) {
-    using M = Math<false>;
-    float a0[K], a1[K], d[K];
-    float c = 0.f;
-    float stk[MAX_DEPTH * (2 * K + 1)];
-    int sp = 0;
-#pragma unroll
-    for (int k = 0; k < K; ++k) { a0[k] = a1[k] = d[k] = 0.f; }
-    for (int pc = 0; pc < n_instr; ++pc) {
-        const int4 ins = C.ins[pc];
-        const int head = ins.x, op = head_op(head);
-        const int node = word_node(ins.y);
-        const float4* P = spar + word_par(ins.y);
-        if (op < OP_OPEN_MIN) {
-            float4 r0 = make_float4(1.f, 0.f, 0.f, 0.f), r1 = make_float4(0.f, 1.f, 0.f, 0.f),
-                   r2 = make_float4(0.f, 0.f, 1.f, 0.f);
-            if (head & HEAD_FRAME) { r0 = P[0]; r1 = P[1]; r2 = P[2]; P += 3; }
-#pragma unroll
-            for (int k = 0; k < K; ++k) {
-                const float x = fmaf(r0.x, px[k], fmaf(r0.y, py[k], fmaf(r0.z, pz[k], r0.w)));
-                const float y = fmaf(r1.x, px[k], fmaf(r1.y, py[k], fmaf(r1.z, pz[k], r1.w)));
-                const float z = fmaf(r2.x, px[k], fmaf(r2.y, py[k], fmaf(r2.z, pz[k], r2.w)));
-                d[k] = prim_eval<false>(op, P, x, y, z);
-            }
-            P += prim_f4(op);
-        } else if (op <= OP_OPEN_SMOOTH) {
-            if (!(head & HEAD_ROOT)) {
-                float* s = stk + sp * (2 * K + 1);
-#pragma unroll
-                for (int k = 0; k < K; ++k) { s[2 * k] = a0[k]; s[2 * k + 1] = a1[k]; }
-                s[2 * K] = c;
-                ++sp;
-            }
-            if (op == OP_OPEN_MIN) {
-#pragma unroll
-                for (int k = 0; k < K; ++k) { a0[k] = CUDART_INF_F; a1[k] = __int_as_float(0); }
-            } else {
-                c = P[0].x;
-                rec.c[node] = c;
-#pragma unroll
-                for (int k = 0; k < K; ++k) { a0[k] = -CUDART_INF_F; a1[k] = 0.f; }
-            }
-            continue;
-        } else {
-#pragma unroll
-            for (int k = 0; k < K; ++k) {
-                if (op == OP_CLOSE_MIN) { d[k] = a0[k]; rec.win[node][k] = __float_as_int(a1[k]); }
-                else d[k] = M::div(a0[k] + M::log(a1[k]), c);
-                rec.d[node][k] = d[k];
-            }
-            if (!(head & HEAD_ROOT)) {
-                --sp;
-                const float* s = stk + sp * (2 * K + 1);
-#pragma unroll
-                for (int k = 0; k < K; ++k) { a0[k] = s[2 * k]; a1[k] = s[2 * k + 1]; }
-                c = s[2 * K];
-            }
-        }
-        const int np = head_npost(head);
-        if (np) {
-            const float4 pp = P[0];
-            const float pv[3] = {pp.x, pp.y, pp.z};
-#pragma unroll
-            for (int i = 0; i < 3; ++i)
-                if (i < np) {
-                    const bool onion = head_post(head, i) == POST_ONION;
-#pragma unroll
-                    for (int k = 0; k < K; ++k) d[k] = (onion ? fabsf(d[k]) : d[k]) - pv[i];
-                }
-        }
-        const int fold = head_fold(head);
-        if (fold == FOLD_MIN) {
-            const int ordinal = head_ordinal(head);
-#pragma unroll
-            for (int k = 0; k < K; ++k)
-                if (d[k] < a0[k]) { a0[k] = d[k]; a1[k] = __int_as_float(ordinal); }   // strict: first wins ties
-        } else if (fold == FOLD_SMOOTH) {
-#pragma unroll
-            for (int k = 0; k < K; ++k) {
-                const float x = c * d[k];
-                const float e = M::exp(-fabsf(x - a0[k]));
-                a1[k] = (x > a0[k]) ? fmaf(a1[k], e, 1.f) : a1[k] + e;
-                a0[k] = fmaxf(a0[k], x);
-            }
-        }
-    }
-#pragma unroll
-    for (int k = 0; k < K; ++k) out[k] = d[k];
+    eval_scene<K, false, CAP, 0, true>(C, n_instr, spar, px, py, pz, out, nullptr, nullptr, &rec);
 }
 
 }  // namespace rm

@@ -50,17 +50,18 @@ inline int check_tape(const RmTape* t) {
 inline size_t tape_smem_bytes(const RmTape* t) { return (size_t)t->n_par * 4; }
 
 // Runs BODY with `CAP` (constexpr) and `code` (TapeCode<CAP>, filled from the host block) in scope.
-#define RM_WITH_CODE(tape, ...)                                                          \
+#define RM_WITH_CODE(tape, ...) RM_WITH_CODE_EX(tape, false, __VA_ARGS__)
+#define RM_WITH_CODE_EX(tape, with_cull, ...)                                            \
     do {                                                                                 \
         if ((tape)->n_instr <= rm::CODE_CAP_SMALL) {                                     \
             constexpr int CAP = rm::CODE_CAP_SMALL;                                      \
             rm::TapeCode<CAP> code;                                                      \
-            rm::expand_code((tape)->code_host, (tape)->n_instr, code.ins);              \
+            rm::expand_code((tape)->code_host, (tape)->n_instr, code.ins, with_cull);   \
             __VA_ARGS__                                                                  \
         } else {                                                                         \
             constexpr int CAP = rm::CODE_CAP_LARGE;                                      \
             rm::TapeCode<CAP> code;                                                      \
-            rm::expand_code((tape)->code_host, (tape)->n_instr, code.ins);              \
+            rm::expand_code((tape)->code_host, (tape)->n_instr, code.ins, with_cull);   \
             __VA_ARGS__                                                                  \
         }                                                                                \
     } while (0)

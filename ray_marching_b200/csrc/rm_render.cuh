@@ -94,7 +94,7 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
 
         for (int b = 0;; ++b) {
             march_rays<FAST, CAP, CULL>(code, n_instr, spar, P.steps, P.early_exit != 0, px, py, pz, vx, vy, vz);
-            stencil_eval<CAP>(code, n_instr, spar, P.st, need_stencil, px, py, pz, f, nx, ny, nz, lap);
+            stencil_eval<CAP, CULL>(code, n_instr, spar, P.st, need_stencil, px, py, pz, f, nx, ny, nz, lap);
             if (b >= P.bounces) break;
             // reflected-ray branch (reflect = control.py:179-194)
 #pragma unroll

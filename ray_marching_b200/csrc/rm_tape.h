@@ -66,7 +66,8 @@ __host__ __device__ __forceinline__ int ins_tail(int w) { return (w >> 20) & 15;
 __host__ __device__ __forceinline__ int ins_post_off(int w) { return w & 0xFFFFF; }
 
 // Host: [n][2] words -> expanded instructions.
-inline void expand_code(const int32_t* words, int n, int4* out) {
+// `with_cull`: set the DISP_CULL dispatch flags (only the culling kernels look at them).
+inline void expand_code(const int32_t* words, int n, int4* out, bool with_cull = false) {
     for (int i = 0; i < n; ++i) {
         const int head = words[2 * i], w1 = words[2 * i + 1];
         const int op = head_op(head), np = head_npost(head), fold = head_fold(head);
@@ -82,7 +83,7 @@ inline void expand_code(const int32_t* words, int n, int4* out) {
         if (np == 1) post_case = head_post(head, 0) == POST_ONION ? TAIL_POST_ONION : TAIL_POST_ROUND;
         else if (np > 1) post_case = TAIL_POST_CHAIN;
         const int tail = (op == OP_OPEN_MIN || op == OP_OPEN_SMOOTH) ? 0 : fold * 4 + post_case;
-        if (word_cull(w1) && op != OP_OPEN_MIN && op != OP_CLOSE_MIN) disp |= DISP_CULL;
+        if (with_cull && word_cull(w1) && op != OP_OPEN_MIN && op != OP_CLOSE_MIN) disp |= DISP_CULL;
         out[i] = make_int4(head, w1, off * 16, ((np ? post_f4 * 16 : 0) & 0xFFFFF) | (tail << 20) | (disp << 24));
     }
     out[n] = make_int4(0, 0, 0, 0);
