@@ -193,6 +193,11 @@ int rm_render_bwd(const RmTape* tape, const RmCamera* cam, const float* poses,
  * iters*128 independent FFMA (256 flop).  Not part of the render path. */
 int rm_probe_ffma(int32_t blocks, int32_t iters, float* sink, void* stream);
 
+/* Test hook for the kernels' branch-free correctly rounded arithmetic (csrc/rm_math.cuh): for n
+ * operand pairs writes out[6][n] = { sqrt_inline(a), sqrt.rn(a), div_inline(a,b), div.rn(a,b),
+ * rcp_or_zero(b), (0 < b < inf ? 1/b : 0) }.  Not part of the render path. */
+int rm_probe_math(const float* a, const float* b, int64_t n, float* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -26,13 +26,21 @@
 namespace rm {
 
 #ifndef RM_MINB_BWD
-#define RM_MINB_BWD 3
+#define RM_MINB_BWD 4
+#endif
+
+#ifndef RM_ACC_BYTES
+#define RM_ACC_BYTES (48 * 1024)   // shared-memory budget of the gradient accumulator columns per block
+#endif
+
+#ifndef RM_BWD_EARLY_BREAK
+#define RM_BWD_EARLY_BREAK 1
 #endif
 
 #ifndef RM_KB
-#define RM_KB 2
+#define RM_KB 1
 #endif
-constexpr int KB = RM_KB;        // samples per thread in the backward kernels (2 or 4)
+constexpr int KB = RM_KB;        // samples per thread in the backward kernels (1, 2 or 4)
 constexpr int BLOCK_B = 128;
 
 __device__ __forceinline__ void load3k(const float* base, int64_t first, int64_t n, float (&x)[KB],
@@ -72,11 +80,14 @@ __device__ __forceinline__ float* traj_slot(float* traj, int s) {
 }
 __device__ __forceinline__ void traj_store(float* traj, int s, const float (&x)[KB], const float (&y)[KB],
                                            const float (&z)[KB]) {
-    if constexpr (KB == 2) {
+    if constexpr (KB == 1) {
+        float* p = traj_slot(traj, s);
+        p[0] = x[0]; p[1] = y[0]; p[2] = z[0];
+    } else if constexpr (KB == 2) {
         float2* p = reinterpret_cast<float2*>(traj_slot(traj, s));
         p[0] = make_float2(x[0], y[0]); p[1] = make_float2(z[0], x[KB - 1]); p[2] = make_float2(y[KB - 1], z[KB - 1]);
     } else {
-        static_assert(KB == 2 || KB == 4, "KB must be 2 or 4");
+        static_assert(KB == 1 || KB == 2 || KB == 4, "KB must be 1, 2 or 4");
         float4* p = reinterpret_cast<float4*>(traj_slot(traj, s));
         p[0] = make_float4(x[0], y[0], z[0], x[1]);
         p[1] = make_float4(y[1], z[1], x[KB - 2], y[KB - 2]);
@@ -84,7 +95,10 @@ __device__ __forceinline__ void traj_store(float* traj, int s, const float (&x)[
     }
 }
 __device__ __forceinline__ void traj_load(float* traj, int s, float (&x)[KB], float (&y)[KB], float (&z)[KB]) {
-    if constexpr (KB == 2) {
+    if constexpr (KB == 1) {
+        const float* p = traj_slot(traj, s);
+        x[0] = p[0]; y[0] = p[1]; z[0] = p[2];
+    } else if constexpr (KB == 2) {
         const float2* p = reinterpret_cast<const float2*>(traj_slot(traj, s));
         const float2 a = p[0], b = p[1], c = p[2];
         x[0] = a.x; y[0] = a.y; z[0] = b.x; x[KB - 1] = b.y; y[KB - 1] = c.x; z[KB - 1] = c.y;
@@ -141,9 +155,9 @@ __device__ __forceinline__ void forward_pass(const TapeCode<CAP>& code, int n_in
                                              const float (&vx)[KB], const float (&vy)[KB],
                                              const float (&vz)[KB], int (&conv)[KB],
                                              float (&ux)[KB], float (&uy)[KB], float (&uz)[KB]) {
-    float o0[KB];
+    float o0[KB], prev[KB];                                    // prev: last step length while settled
 #pragma unroll
-    for (int k = 0; k < KB; ++k) { conv[k] = 0; ux[k] = uy[k] = uz[k] = o0[k] = 0.f; }
+    for (int k = 0; k < KB; ++k) { conv[k] = 0; ux[k] = uy[k] = uz[k] = o0[k] = 0.f; prev[k] = -1.f; }
     const int n_tasks = steps + (st != nullptr ? 4 : 0);
     for (int task = 0; task < n_tasks; ++task) {
         const bool marching = task < steps;
@@ -156,12 +170,24 @@ __device__ __forceinline__ void forward_pass(const TapeCode<CAP>& code, int n_in
         for (int k = 0; k < KB; ++k) { x[k] = px[k] + dx; y[k] = py[k] + dy; z[k] = pz[k] + dz; }
         eval_scene<KB, false, CAP>(code, n_instr, spar, x, y, z, d);
         if (marching) {
+            bool at_rest = true;
 #pragma unroll
             for (int k = 0; k < KB; ++k) {
                 const float scale = 1.f + fmaxf(fabsf(px[k]), fmaxf(fabsf(py[k]), fabsf(pz[k])));
-                if (!(fabsf(d[k]) <= tol * scale)) conv[k] = task + 1;       // also catches NaN
+                const float ad = fabsf(d[k]);
+                const bool within = ad <= tol * scale;                       // false for NaN
+                if (!within) conv[k] = task + 1;
+                // settled for two steps in a row without growing: a contracting fixed point
+                at_rest = at_rest && within && prev[k] >= ad;
+                prev[k] = within ? ad : -1.f;
                 px[k] = fmaf(d[k], vx[k], px[k]); py[k] = fmaf(d[k], vy[k], py[k]); pz[k] = fmaf(d[k], vz[k], pz[k]);
             }
+            // every ray of the warp at rest: the remaining steps stay within the tolerance (they are
+            // part of the converged tail by definition), so the replay jumps to the stencil.  With
+            // tol = 0 this triggers only when f == 0 exactly twice, where skipping is exact.
+#if RM_BWD_EARLY_BREAK
+            if (__all_sync(0xffffffffu, at_rest)) task = steps - 1;
+#endif
         } else {
             const float wx = st->w[j][0], wy = st->w[j][1], wz = st->w[j][2], first = st->first[j];
 #pragma unroll
@@ -199,7 +225,9 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
 #pragma unroll
     for (int k = 0; k < KB; ++k) { any_tail |= conv[k] < steps; first_exact = max(first_exact, conv[k]); }
     const bool tail = __any_sync(0xffffffffu, any_tail);
-    for (int o = 16; o > 0; o >>= 1) first_exact = max(first_exact, __shfl_xor_sync(0xffffffffu, first_exact, o));
+    // warp max through REDUX: the result lives in a uniform register, which keeps the task loop
+    // (and the interpreters' decode inside it) on the uniform datapath
+    first_exact = __reduce_max_sync(0xffffffffu, first_exact);
 
     float g1x[KB], g1y[KB], g1z[KB], a0[KB], rest[KB], tsum[KB];   // carried from task 5 to task 6
 #pragma unroll
@@ -234,7 +262,7 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
             for (int k = 0; k < KB; ++k)
                 a[k] = s < conv[k] ? lx[k] * vx[k] + ly[k] * vy[k] + lz[k] * vz[k] : 0.f;
         }
-        NodeRecords<KB> rec;
+        NodeRecords<KB, CAP> rec;
         eval_record<KB, CAP>(code, n_instr, spar, x, y, z, rec, f);
         sweep_vjp<KB, CAP>(code, n_instr, spar, x, y, z, a, rec, sacc, gx, gy, gz);
         if (task < 5) {
@@ -246,7 +274,7 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
             for (int k = 0; k < KB; ++k) {
                 const int n = steps - conv[k];
                 // c from the sweep: (a0 grad f).v / a0
-                const float gv = a0[k] != 0.f ? __fdiv_rn(gx[k] * vx[k] + gy[k] * vy[k] + gz[k] * vz[k], a0[k]) : 0.f;
+                const float gv = a0[k] != 0.f ? div_rn_inline(gx[k] * vx[k] + gy[k] * vy[k] + gz[k] * vz[k], a0[k]) : 0.f;
                 const float c = 1.f + gv;
                 float cn = 1.f, sn = 0.f, tn = 0.f;            // c^j, S_j, T_j = sum_{i<j} S_i
                 for (int j = 0; j < n; ++j) { tn += sn; sn += cn; cn *= c; }
@@ -283,20 +311,18 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
 template <int CAP>
 __global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
 sdf_vjp_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
-               int acc_shift, const float* __restrict__ pts, const float* __restrict__ gout, int64_t n,
+               int acc_shift, int iters, const float* __restrict__ pts, const float* __restrict__ gout, int64_t n,
                float* __restrict__ dpts, float* __restrict__ dpar) {
     extern __shared__ __align__(16) unsigned char smem[];
     const GradAcc sacc = stage_accumulators(smem, n_par, acc_shift);
     const float4* spar = stage_params(par, n_par, smem);                // syncs
-    const int64_t groups = (n + KB - 1) / KB;
-    const int64_t warp_groups = (groups + 31) / 32 * 32;                // whole warps iterate together
-    for (int64_t g = (int64_t)blockIdx.x * BLOCK_B + threadIdx.x; g < warp_groups;
-         g += (int64_t)gridDim.x * BLOCK_B) {
+    for (int it = 0; it < iters; ++it) {                    // block-uniform trip count (see backward_grid)
+        const int64_t g = ((int64_t)it * gridDim.x + blockIdx.x) * BLOCK_B + threadIdx.x;
         const int64_t first = g * KB;
         float x[KB], y[KB], z[KB], a[KB], f[KB], gx[KB], gy[KB], gz[KB];
         load3k(pts, first, n, x, y, z);
         load1k(gout, first, n, a);
-        NodeRecords<KB> rec;
+        NodeRecords<KB, CAP> rec;
         eval_record<KB, CAP>(code, n_instr, spar, x, y, z, rec, f);
         sweep_vjp<KB, CAP>(code, n_instr, spar, x, y, z, a, rec, sacc, gx, gy, gz);
         store3k(dpts, first, n, gx, gy, gz);
@@ -307,16 +333,14 @@ sdf_vjp_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int
 template <int CAP>
 __global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
 march_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
-                 int acc_shift, const float* __restrict__ origin, const float* __restrict__ dirs,
+                 int acc_shift, int iters, const float* __restrict__ origin, const float* __restrict__ dirs,
                  const float* __restrict__ gpos, int64_t n, int steps, float tol, float* __restrict__ traj,
                  float* __restrict__ dorigin, float* __restrict__ ddirs, float* __restrict__ dpar) {
     extern __shared__ __align__(16) unsigned char smem[];
     const GradAcc sacc = stage_accumulators(smem, n_par, acc_shift);
     const float4* spar = stage_params(par, n_par, smem);
-    const int64_t groups = (n + KB - 1) / KB;
-    const int64_t warp_groups = (groups + 31) / 32 * 32;
-    for (int64_t g = (int64_t)blockIdx.x * BLOCK_B + threadIdx.x; g < warp_groups;
-         g += (int64_t)gridDim.x * BLOCK_B) {
+    for (int it = 0; it < iters; ++it) {                    // block-uniform trip count (see backward_grid)
+        const int64_t g = ((int64_t)it * gridDim.x + blockIdx.x) * BLOCK_B + threadIdx.x;
         const int64_t first = g * KB;
         float px[KB], py[KB], pz[KB], vx[KB], vy[KB], vz[KB];
         load3k(origin, first, n, px, py, pz);
@@ -339,6 +363,7 @@ march_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, i
 // ---- fused G-buffer backward ------------------------------------------------------------------
 struct RenderBwdParams {
     int acc_shift;
+    int iters;
     CamParams cam;
     Stencil st;
     int64_t ray_begin, n_rays;
@@ -393,8 +418,6 @@ render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, 
     const GradAcc sacc = stage_accumulators(smem, n_par, P.acc_shift);
     const float4* spar = stage_params(par, n_par, smem);
     const int64_t n = P.n_rays;
-    const int64_t groups = (n + KB - 1) / KB;
-    const int64_t warp_groups = (groups + 31) / 32 * 32;
     const bool need_stencil = P.g.normals != nullptr || P.g.laplacian != nullptr;
     const int64_t per_view = (int64_t)P.cam.width * P.cam.height;
 
@@ -403,8 +426,9 @@ render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, 
     for (int i = 0; i < 7; ++i) cam_acc[i] = 0.f;
     int acc_view = -1;
 
-    for (int64_t g = (int64_t)blockIdx.x * BLOCK_B + threadIdx.x; g < warp_groups;
-         g += (int64_t)gridDim.x * BLOCK_B) {
+    const int iters = P.iters;
+    for (int it = 0; it < iters; ++it) {                    // block-uniform trip count (see backward_grid)
+        const int64_t g = ((int64_t)it * gridDim.x + blockIdx.x) * BLOCK_B + threadIdx.x;
         const int64_t first = g * KB;
         // ---- rays from the pixel index (PinholeCamera.forward) ----
         float px[KB], py[KB], pz[KB], vx[KB], vy[KB], vz[KB];
@@ -436,8 +460,8 @@ render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, 
 #pragma unroll
             for (int k = 0; k < KB; ++k) {
                 // forward: nrm = u / |u|; d nrm / d u = (I - nrm nrm^T) / |u|
-                const float len = __fsqrt_rn(ux[k] * ux[k] + uy[k] * uy[k] + uz[k] * uz[k]);
-                const float il = __fdiv_rn(1.f, len);
+                const float len = sqrt_rn_inline(ux[k] * ux[k] + uy[k] * uy[k] + uz[k] * uz[k]);
+                const float il = div_rn_inline(1.f, len);
                 const float nx = ux[k] * il, ny = uy[k] * il, nz = uz[k] * il;
                 const float gn = gnx[k] * nx + gny[k] * ny + gnz[k] * nz;
                 const bool has_n = P.g.normals != nullptr;
@@ -499,15 +523,24 @@ inline int check_backward_tape(const RmTape* t) {
                     MAX_NODES, t->n_nodes);
     return RM_OK;
 }
+// The kernels loop `iters` times over a grid of `blocks`; both are chosen so that every block runs
+// the same (block-uniform) number of iterations and only the last block has idle slots.  Bounded
+// grid: one global atomic per parameter per block, and the trajectory scratch is sized by it.
+inline int backward_iters(int64_t n) {
+    const int64_t want = (n + (int64_t)BLOCK_B * KB - 1) / ((int64_t)BLOCK_B * KB);
+    const int64_t cap = 148 * 8;
+    return (int)((want + cap - 1) / cap > 0 ? (want + cap - 1) / cap : 1);
+}
 inline unsigned backward_grid(int64_t n) {
     const int64_t want = (n + (int64_t)BLOCK_B * KB - 1) / ((int64_t)BLOCK_B * KB);
-    const int64_t cap = 148 * 8;                      // bounded: one global atomic per parameter per block
-    return (unsigned)(want < cap ? (want > 0 ? want : 1) : cap);
+    const int64_t it = backward_iters(n);
+    const int64_t blocks = (want + it - 1) / it;
+    return (unsigned)(blocks > 0 ? blocks : 1);
 }
 // log2 of the accumulator columns: as many lane-private columns as fit in ~40 KB per block
 inline int backward_acc_shift(const RmTape* t) {
     int shift = 5;
-    while (shift > 0 && ((size_t)t->n_par << shift) * sizeof(float) > 40 * 1024) --shift;
+    while (shift > 0 && ((size_t)t->n_par << shift) * sizeof(float) > RM_ACC_BYTES) --shift;
     return shift;
 }
 inline size_t backward_smem(const RmTape* t) {
@@ -535,7 +568,8 @@ extern "C" int rm_sdf_vjp(const RmTape* tape, const float* points, const float* 
     RM_WITH_CODE(tape, {
         if (int s = prepare_smem(sdf_vjp_kernel<CAP>, sm)) return s;
         sdf_vjp_kernel<CAP><<<backward_grid(n), BLOCK_B, sm, (cudaStream_t)stream>>>(
-            code, tape->par, tape->n_instr, tape->n_par, backward_acc_shift(tape), points, grad_sdf, n, dpoints, dpar);
+            code, tape->par, tape->n_instr, tape->n_par, backward_acc_shift(tape), backward_iters(n), points, grad_sdf, n,
+            dpoints, dpar);
     });
     RM_CUDA(cudaGetLastError());
     return RM_OK;
@@ -555,7 +589,8 @@ extern "C" int rm_march_bwd(const RmTape* tape, const float* origin, const float
     RM_WITH_CODE(tape, {
         if (int s = prepare_smem(march_bwd_kernel<CAP>, sm)) return s;
         march_bwd_kernel<CAP><<<backward_grid(n), BLOCK_B, sm, (cudaStream_t)stream>>>(
-            code, tape->par, tape->n_instr, tape->n_par, backward_acc_shift(tape), origin, dirs, grad_pos, n, steps,
+            code, tape->par, tape->n_instr, tape->n_par, backward_acc_shift(tape), backward_iters(n), origin, dirs, grad_pos,
+            n, steps,
             converge_tol, traj_scratch, dorigin, ddirs, dpar);
     });
     RM_CUDA(cudaGetLastError());
@@ -587,6 +622,7 @@ extern "C" int rm_render_bwd(const RmTape* tape, const RmCamera* cam, const floa
     make_stencil(a->normals_eps, &P.st);
     P.ray_begin = a->ray_begin; P.n_rays = a->n_rays; P.steps = a->steps;
     P.acc_shift = backward_acc_shift(tape);
+    P.iters = backward_iters(a->n_rays);
     P.tol = a->bwd_converge_tol;
     P.g = *grads; P.traj = traj_scratch; P.dpar = dpar; P.dposes = dposes;
     const size_t sm = backward_smem(tape);

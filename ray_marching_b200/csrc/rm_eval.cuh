@@ -44,11 +44,12 @@ constexpr float CULL_LOG2 = -30.0f;
 // the winning child ordinal (first index on ties, as torch.min(dim)), kept in local memory and
 // touched only at union boundaries; the reverse sweep (rm_sweep.cuh) consumes them.
 constexpr int MAX_NODES = 16;      // union nodes supported by the backward records
-template <int K>
+template <int K, int CAP>
 struct NodeRecords {
     float d[MAX_NODES][K];     // raw value of the union (before its post-ops)
     int win[MAX_NODES][K];     // winning child ordinal (hard unions)
     float c[MAX_NODES];        // -k of smooth unions
+    float y[CAP][K];           // per instruction: value a child of a smooth union fed into the blend
 };
 
 // CULLMODE: 0 = the code carries no culling flags; 1 = flags present (a culling launch) but this
@@ -59,7 +60,7 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
                                            const float (&py)[K], const float (&pz)[K],
                                            float (&out)[K], float* hint = nullptr,
                                            const float* move = nullptr,
-                                           NodeRecords<K>* rec = nullptr) {
+                                           NodeRecords<K, CAP>* rec = nullptr) {
     using M = Math<FAST>;
     constexpr bool CULL = CULLMODE == 2;
     float seed[CULL ? K : 1];                        // lower bound of the culled union's largest term
@@ -235,6 +236,7 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
         } else {                                      // FOLD_SMOOTH
 #pragma unroll
             for (int k = 0; k < K; ++k) {
+                if (RECORD) rec->y[pc][k] = d[k];
                 const float x = c * d[k];
                 const float e = M::exp(-fabsf(x - a0[k]));
                 a1[k] = (x > a0[k]) ? fmaf(a1[k], e, 1.f) : a1[k] + e;

@@ -233,10 +233,10 @@ __device__ __forceinline__ void stencil_eval(const TapeCode<CAP>& code, int n_in
 #pragma unroll
     for (int k = 0; k < K; ++k) {
         // n = normalize(Ainv d, eps=0): 0/0 = NaN for missed rays, as F.normalize gives (:119)
-        const float len = __fsqrt_rn(nx[k] * nx[k] + ny[k] * ny[k] + nz[k] * nz[k]);
-        nx[k] = __fdiv_rn(nx[k], len);
-        ny[k] = __fdiv_rn(ny[k], len);
-        nz[k] = __fdiv_rn(nz[k], len);
+        const float len = sqrt_rn_inline(nx[k] * nx[k] + ny[k] * ny[k] + nz[k] * nz[k]);
+        nx[k] = div_rn_inline(nx[k], len);
+        ny[k] = div_rn_inline(ny[k], len);
+        nz[k] = div_rn_inline(nz[k], len);
         lap[k] = (f[k] - sum[k] * 0.25f) * st.lap_scale;    // (:120-124)
     }
 }

@@ -19,7 +19,7 @@
 namespace rm {
 
 __device__ __forceinline__ float sgn0(float x) { return x > 0.f ? 1.f : (x < 0.f ? -1.f : 0.f); }
-__device__ __forceinline__ float inv_or_zero(float n) { return n > 0.f ? __fdiv_rn(1.f, n) : 0.f; }
+__device__ __forceinline__ float inv_or_zero(float n) { return rcp_or_zero(n); }
 
 // Value, gradient w.r.t. the local point (gq) and w.r.t. the primitive's parameter record (gp, in
 // the record layout written by tape.py: up to 3 float4).  IEEE math throughout.
@@ -28,7 +28,7 @@ __device__ __forceinline__ float prim_grad(int op, const float4* P, float x, flo
 #pragma unroll
     for (int i = 0; i < 12; ++i) gp[i] = 0.f;
     if (op == OP_SPHERE) {                                   // primitives.py:11-17
-        const float n = __fsqrt_rn(fmaf(x, x, fmaf(y, y, z * z)));
+        const float n = sqrt_rn_inline(fmaf(x, x, fmaf(y, y, z * z)));
         const float inv = inv_or_zero(n);
         gq[0] = x * inv; gq[1] = y * inv; gq[2] = z * inv;
         gp[0] = -1.f;
@@ -40,7 +40,7 @@ __device__ __forceinline__ float prim_grad(int op, const float4* P, float x, flo
         const int arg = (ax >= ay && ax >= az) ? 0 : (ay >= az ? 1 : 2);   // first index on ties
         const float mx = arg == 0 ? ax : (arg == 1 ? ay : az);
         const float ox = ax > 0.f ? ax : 0.f, oy = ay > 0.f ? ay : 0.f, oz = az > 0.f ? az : 0.f;
-        const float n = __fsqrt_rn(fmaf(ox, ox, fmaf(oy, oy, oz * oz)));
+        const float n = sqrt_rn_inline(fmaf(ox, ox, fmaf(oy, oy, oz * oz)));
         const float inv = inv_or_zero(n);
         const float in = mx < 0.f ? 1.f : 0.f;
         const float gax = ox * inv + (arg == 0 ? in : 0.f);
@@ -57,7 +57,7 @@ __device__ __forceinline__ float prim_grad(int op, const float4* P, float x, flo
         const bool inside = hr >= 0.f && hr <= 1.f;          // clamp passes gradient on [0,1]
         const float h = clamp_nan(hr, 0.f, 1.f);
         const float wx = fmaf(h, ab.x, -apx), wy = fmaf(h, ab.y, -apy), wz = fmaf(h, ab.z, -apz);
-        const float n = __fsqrt_rn(fmaf(wx, wx, fmaf(wy, wy, wz * wz)));
+        const float n = sqrt_rn_inline(fmaf(wx, wx, fmaf(wy, wy, wz * wz)));
         const float inv = inv_or_zero(n);
         const float gwx = wx * inv, gwy = wy * inv, gwz = wz * inv;
         const float t = inside ? (gwx * ab.x + gwy * ab.y + gwz * ab.z) : 0.f;   // d/dh
@@ -69,11 +69,11 @@ __device__ __forceinline__ float prim_grad(int op, const float4* P, float x, flo
         return n - p0.w;
     }
     if (op == OP_DISK) {                                     // primitives.py:69-82
-        const float ryz = __fsqrt_rn(fmaf(y, y, z * z));
+        const float ryz = sqrt_rn_inline(fmaf(y, y, z * z));
         const float rim = ryz - P[0].x;
         const bool pos = rim > 0.f;
         const float m = pos ? rim : 0.f;
-        const float d = __fsqrt_rn(fmaf(x, x, m * m));
+        const float d = sqrt_rn_inline(fmaf(x, x, m * m));
         const float inv = inv_or_zero(d);
         const float grim = pos ? m * inv : 0.f;
         const float iyz = inv_or_zero(ryz);
@@ -82,9 +82,9 @@ __device__ __forceinline__ float prim_grad(int op, const float4* P, float x, flo
         return d;
     }
     if (op == OP_TORUS) {                                    // primitives.py:91-102
-        const float rxz = __fsqrt_rn(fmaf(x, x, z * z));
+        const float rxz = sqrt_rn_inline(fmaf(x, x, z * z));
         const float a = rxz - P[0].x;
-        const float n = __fsqrt_rn(fmaf(a, a, y * y));
+        const float n = sqrt_rn_inline(fmaf(a, a, y * y));
         const float inv = inv_or_zero(n);
         const float u0 = a * inv, ixz = inv_or_zero(rxz);
         gq[0] = u0 * x * ixz; gq[1] = y * inv; gq[2] = u0 * z * ixz;
@@ -122,7 +122,7 @@ template <int K, int CAP>
 __device__ __forceinline__ void eval_record(const TapeCode<CAP>& C, const int n_instr,
                                             const float4* __restrict__ spar, const float (&px)[K],
                                             const float (&py)[K], const float (&pz)[K],
-                                            NodeRecords<K>& rec, float (&out)[K]) {
+                                            NodeRecords<K, CAP>& rec, float (&out)[K]) {
     eval_scene<K, false, CAP, 0, true>(C, n_instr, spar, px, py, pz, out, nullptr, nullptr, &rec);
 }
 

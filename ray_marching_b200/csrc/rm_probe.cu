@@ -2,6 +2,7 @@
 // for bench.py (MEASURED_PEAKS.json has no FP32 CUDA-core figure); not on the
 // render path.
 #include "rm_host.h"
+#include "rm_math.cuh"
 
 namespace rm {
 
@@ -23,7 +24,28 @@ __global__ void __launch_bounds__(256) ffma_probe_kernel(int iters, float seed, 
     if (s == 123.456f) sink[0] = s;           // never true; keeps the loop alive
 }
 
+// Test hook for rm_math.cuh: the branch-free correctly rounded sqrt / div / reciprocal next to the
+// compiler's sqrt.rn / div.rn on the same operands.
+__global__ void math_probe_kernel(const float* a, const float* b, int64_t n, float* out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    out[i] = sqrt_rn_inline(a[i]);
+    out[n + i] = __fsqrt_rn(a[i]);
+    out[2 * n + i] = div_rn_inline(a[i], b[i]);
+    out[3 * n + i] = __fdiv_rn(a[i], b[i]);
+    out[4 * n + i] = rcp_or_zero(b[i]);
+    out[5 * n + i] = (b[i] > 0.f && b[i] < CUDART_INF_F) ? __fdiv_rn(1.f, b[i]) : 0.f;
+}
+
 }  // namespace rm
+
+extern "C" int rm_probe_math(const float* a, const float* b, int64_t n, float* out, void* stream) {
+    if (n < 0 || (n > 0 && (!a || !b || !out))) return rm::fail(RM_ERR_INVALID, "rm_probe_math: bad arguments");
+    if (n == 0) return RM_OK;
+    rm::math_probe_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(a, b, n, out);
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+}
 
 // Launches blocks x 256 threads; every thread issues iters * 128 FFMA (= 256 flop).
 extern "C" int rm_probe_ffma(int32_t blocks, int32_t iters, float* sink, void* stream) {

@@ -89,7 +89,7 @@ template <int K, int CAP>
 __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_instr,
                                           const float4* __restrict__ spar, const float (&px)[K],
                                           const float (&py)[K], const float (&pz)[K],
-                                          const float (&abar)[K], const NodeRecords<K>& rec,
+                                          const float (&abar)[K], const NodeRecords<K, CAP>& rec,
                                           const GradAcc acc, float (&gx)[K], float (&gy)[K],
                                           float (&gz)[K]) {
     OpenNode<K> cur;
@@ -109,7 +109,7 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
             if (op == OP_OPEN_SMOOTH) {
                 float g = 0.f;
 #pragma unroll
-                for (int k = 0; k < K; ++k) g += cur.a[k] != 0.f ? __fdiv_rn(cur.s[k] - cur.a[k] * cur.d[k], cur.c) : 0.f;
+                for (int k = 0; k < K; ++k) g += cur.a[k] != 0.f ? div_rn_inline(cur.s[k] - cur.a[k] * cur.d[k], cur.c) : 0.f;
                 acc.add(off * 4, g);
             }
             if (!(head & HEAD_ROOT)) cur = stk[--sp];
@@ -154,18 +154,10 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
 #pragma unroll
             for (int k = 0; k < K; ++k) live |= (cur.win[k] == ordinal) && cur.a[k] != 0.f;
         } else if (fold == FOLD_SMOOTH) {
-            // value only (no gradients) -> softmax weight; the d/dk sum needs it for every child
+            // softmax weight from the child's value recorded by pass 1 (no re-evaluation)
 #pragma unroll
             for (int k = 0; k < K; ++k) {
-                const float qx = fmaf(r0.x, px[k], fmaf(r0.y, py[k], fmaf(r0.z, pz[k], r0.w)));
-                const float qy = fmaf(r1.x, px[k], fmaf(r1.y, py[k], fmaf(r1.z, pz[k], r1.w)));
-                const float qz = fmaf(r2.x, px[k], fmaf(r2.y, py[k], fmaf(r2.z, pz[k], r2.w)));
-                raw[k] = prim_eval<false>(op, spar + prim_rec, qx, qy, qz);
-            }
-            posts_forward<K>(head, pv, raw, y, sg);
-#pragma unroll
-            for (int k = 0; k < K; ++k) {
-                const float w = expf(cur.c * (y[k] - cur.d[k]));
+                const float w = expf(cur.c * (rec.y[pc][k] - cur.d[k]));
                 live |= cur.a[k] != 0.f && w >= CULL_EPS;
             }
         } else {

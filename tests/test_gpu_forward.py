@@ -284,3 +284,32 @@ def test_culling_matches_full_evaluation(n_prims):
         settled = gb["dists"].reshape(-1).abs() < 1e-4       # grazing rays are still moving at step 32
         assert settled.float().mean().item() > 0.9
         assert ((depth(cul).cpu() - dref).abs() / dref)[settled].max().item() < 1e-4
+
+
+@pytest.mark.gpu
+def test_inline_rounded_math_is_bit_identical_to_ieee():
+    """csrc/rm_math.cuh: the branch-free sqrt / div / reciprocal the IEEE-policy kernels use are the
+    in-range instruction sequences of sqrt.rn / div.rn; they must agree bit for bit with the
+    compiler's versions (specials included) on this path's operand range."""
+    import ctypes as C
+    from ray_marching_b200 import _lib
+    g = torch.Generator().manual_seed(7)
+    n = 1 << 20
+    mag = torch.exp2(torch.empty(n).uniform_(-58.0, 58.0, generator=g))      # quotients stay inside 2^+-98
+    a = mag * torch.where(torch.rand(n, generator=g) < 0.5, -1.0, 1.0)
+    b = torch.exp2(torch.empty(n).uniform_(-40.0, 40.0, generator=g)) * torch.where(torch.rand(n, generator=g) < 0.5, -1.0, 1.0)
+    a[:16] = torch.tensor([0.0, -0.0, float("inf"), float("-inf"), float("nan"), 1.0, 4.0, 2.0, 1e-38, 1e-40, 1e-44,
+                           3e38, 0.0, 5.0, float("inf"), 1.0])
+    b[:16] = torch.tensor([1.0, 1.0, 2.0, 2.0, 1.0, 0.0, -0.0, float("inf"), 1e-10, 1.0, 1.0,
+                           1.0, 0.0, float("nan"), float("inf"), 3.0])
+    a_d, b_d = a.cuda(), b.cuda()
+    out = torch.empty(6, n, device="cuda")
+    st = _lib.lib().rm_probe_math(C.c_void_p(a_d.data_ptr()), C.c_void_p(b_d.data_ptr()), n,
+                                  C.c_void_p(out.data_ptr()), C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    _lib.check(st, "rm_probe_math")
+    bits = out.cpu().view(torch.int32)
+    nan = torch.isnan(out.cpu())
+    for mine, ref, what in ((0, 1, "sqrt"), (2, 3, "div"), (4, 5, "rcp")):
+        same = (bits[mine] == bits[ref]) | (nan[mine] & nan[ref])
+        bad = (~same).nonzero().flatten()
+        assert bad.numel() == 0, (what, a[bad[:5]], b[bad[:5]], out[mine].cpu()[bad[:5]], out[ref].cpu()[bad[:5]])
