@@ -110,24 +110,34 @@ __device__ __forceinline__ void traj_load(float* traj, int s, float (&x)[KB], fl
     }
 }
 
-// Shared memory: [tape par (n_par floats) | accumulators (n_par x cols floats)], see GradAcc.
-__device__ __forceinline__ GradAcc stage_accumulators(unsigned char* smem, int n_par, int shift) {
-    GradAcc acc;
+// Shared memory: [tape par (n_par floats) | accumulator columns], see GradAcc (rm_sweep.cuh).
+template <int MODE>
+__device__ __forceinline__ GradAcc<MODE> stage_accumulators(unsigned char* smem, int n_par, int acc_shared) {
+    GradAcc<MODE> acc;
     acc.base = reinterpret_cast<float*>(smem + (size_t)n_par * sizeof(float));
-    acc.shift = shift;
-    acc.cmask = (1 << shift) - 1;
-    const int total = n_par << shift;
-    for (int i = threadIdx.x; i < total; i += blockDim.x) acc.base[i] = 0.f;
+    acc.n_par = n_par;
+    acc.shared = acc_shared != 0;
+    const int cols = MODE == ACC_LANES ? BLOCK_B : (acc.shared ? 1 : BLOCK_B / 32);
+    for (int i = threadIdx.x; i < n_par * cols; i += BLOCK_B) acc.base[i] = 0.f;
     return acc;
 }
-// One pass per block: column sums (rotated start -> conflict-free) and one global atomic per
-// parameter.
-__device__ __forceinline__ void flush_accumulators(const GradAcc acc, float* dpar, int n_par) {
+// One pass per block: column sums, then one global atomic per parameter (ACC_WARPS) or per
+// parameter and warp (ACC_LANES).
+template <int MODE>
+__device__ __forceinline__ void flush_accumulators(const GradAcc<MODE> acc, float* dpar, int n_par) {
     __syncthreads();
-    for (int i = threadIdx.x; i < n_par; i += blockDim.x) {
-        float v = 0.f;
-        for (int j = 0; j <= acc.cmask; ++j) v += acc.base[(i << acc.shift) + ((j + threadIdx.x) & acc.cmask)];
-        if (v != 0.f) atomicAdd(dpar + i, v);
+    if (MODE == ACC_LANES) {
+        for (int r = 0; r < n_par; ++r) {
+            const float v = warp_sum(acc.base[r * BLOCK_B + threadIdx.x]);
+            if ((threadIdx.x & 31) == 0 && v != 0.f) atomicAdd(dpar + r, v);
+        }
+    } else {
+        const int cols = acc.shared ? 1 : BLOCK_B / 32;
+        for (int i = threadIdx.x; i < n_par; i += BLOCK_B) {
+            float v = 0.f;
+            for (int w = 0; w < cols; ++w) v += acc.base[w * n_par + i];
+            if (v != 0.f) atomicAdd(dpar + i, v);
+        }
     }
 }
 
@@ -210,10 +220,10 @@ __device__ __forceinline__ void forward_pass(const TapeCode<CAP>& code, int n_in
 //          with a_0 (S_n - 1), S_n = sum_{j<n} c^j, n = S - conv: the implicit-surface adjoint of the
 //          hit point truncated to the n steps the reference unrolls; O(tol) from the step-by-step sum.
 //   7..    exact steps s = max_warp(conv) - 1 .. 0 of the unrolled graph.
-template <int CAP>
+template <int CAP, int MODE>
 __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                              int steps, const Stencil* st, const StencilAdjoint* sa,
-                                             float* traj, const GradAcc sacc, const int (&conv)[KB],
+                                             float* traj, const GradAcc<MODE> sacc, const int (&conv)[KB],
                                              const float (&psx)[KB], const float (&psy)[KB],
                                              const float (&psz)[KB],
                                              const float (&vx)[KB], const float (&vy)[KB],
@@ -264,7 +274,7 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
         }
         NodeRecords<KB, CAP> rec;
         eval_record<KB, CAP>(code, n_instr, spar, x, y, z, rec, f);
-        sweep_vjp<KB, CAP>(code, n_instr, spar, x, y, z, a, rec, sacc, gx, gy, gz);
+        sweep_vjp<KB, CAP, MODE>(code, n_instr, spar, x, y, z, a, rec, sacc, gx, gy, gz);
         if (task < 5) {
 #pragma unroll
             for (int k = 0; k < KB; ++k) { lx[k] += gx[k]; ly[k] += gy[k]; lz[k] += gz[k]; }
@@ -308,13 +318,13 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
 }
 
 // Grid-stride over sample groups so the number of blocks (and global atomics) stays bounded.
-template <int CAP>
+template <int CAP, int MODE>
 __global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
 sdf_vjp_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
-               int acc_shift, int iters, const float* __restrict__ pts, const float* __restrict__ gout, int64_t n,
+               int acc_shared, int iters, const float* __restrict__ pts, const float* __restrict__ gout, int64_t n,
                float* __restrict__ dpts, float* __restrict__ dpar) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const GradAcc sacc = stage_accumulators(smem, n_par, acc_shift);
+    const GradAcc<MODE> sacc = stage_accumulators<MODE>(smem, n_par, acc_shared);
     const float4* spar = stage_params(par, n_par, smem);                // syncs
     for (int it = 0; it < iters; ++it) {                    // block-uniform trip count (see backward_grid)
         const int64_t g = ((int64_t)it * gridDim.x + blockIdx.x) * BLOCK_B + threadIdx.x;
@@ -324,20 +334,20 @@ sdf_vjp_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int
         load1k(gout, first, n, a);
         NodeRecords<KB, CAP> rec;
         eval_record<KB, CAP>(code, n_instr, spar, x, y, z, rec, f);
-        sweep_vjp<KB, CAP>(code, n_instr, spar, x, y, z, a, rec, sacc, gx, gy, gz);
+        sweep_vjp<KB, CAP, MODE>(code, n_instr, spar, x, y, z, a, rec, sacc, gx, gy, gz);
         store3k(dpts, first, n, gx, gy, gz);
     }
     flush_accumulators(sacc, dpar, n_par);
 }
 
-template <int CAP>
+template <int CAP, int MODE>
 __global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
 march_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
-                 int acc_shift, int iters, const float* __restrict__ origin, const float* __restrict__ dirs,
+                 int acc_shared, int iters, const float* __restrict__ origin, const float* __restrict__ dirs,
                  const float* __restrict__ gpos, int64_t n, int steps, float tol, float* __restrict__ traj,
                  float* __restrict__ dorigin, float* __restrict__ ddirs, float* __restrict__ dpar) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const GradAcc sacc = stage_accumulators(smem, n_par, acc_shift);
+    const GradAcc<MODE> sacc = stage_accumulators<MODE>(smem, n_par, acc_shared);
     const float4* spar = stage_params(par, n_par, smem);
     for (int it = 0; it < iters; ++it) {                    // block-uniform trip count (see backward_grid)
         const int64_t g = ((int64_t)it * gridDim.x + blockIdx.x) * BLOCK_B + threadIdx.x;
@@ -352,7 +362,7 @@ march_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, i
         load3k(gpos, first, n, lx, ly, lz);
 #pragma unroll
         for (int k = 0; k < KB; ++k) dvx[k] = dvy[k] = dvz[k] = 0.f;
-        reverse_pass<CAP>(code, n_instr, spar, steps, nullptr, nullptr, traj, sacc, conv, px, py, pz,
+        reverse_pass<CAP, MODE>(code, n_instr, spar, steps, nullptr, nullptr, traj, sacc, conv, px, py, pz,
                           vx, vy, vz, lx, ly, lz, dvx, dvy, dvz);
         store3k(dorigin, first, n, lx, ly, lz);
         store3k(ddirs, first, n, dvx, dvy, dvz);
@@ -362,7 +372,7 @@ march_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, i
 
 // ---- fused G-buffer backward ------------------------------------------------------------------
 struct RenderBwdParams {
-    int acc_shift;
+    int acc_shared;
     int iters;
     CamParams cam;
     Stencil st;
@@ -410,12 +420,12 @@ __device__ __forceinline__ void flush_pose_grad(float* dposes, int view, const f
     }
 }
 
-template <int CAP>
+template <int CAP, int MODE>
 __global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
 render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
                   const float* __restrict__ poses, const __grid_constant__ RenderBwdParams P) {
     extern __shared__ __align__(16) unsigned char smem[];
-    const GradAcc sacc = stage_accumulators(smem, n_par, P.acc_shift);
+    const GradAcc<MODE> sacc = stage_accumulators<MODE>(smem, n_par, P.acc_shared);
     const float4* spar = stage_params(par, n_par, smem);
     const int64_t n = P.n_rays;
     const bool need_stencil = P.g.normals != nullptr || P.g.laplacian != nullptr;
@@ -475,7 +485,7 @@ render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, 
         // ---- reverse pass: stencil samples, converged tail, exact steps ----
         float dvx[KB], dvy[KB], dvz[KB];
         load3k(P.g.dirs, first, n, dvx, dvy, dvz);
-        reverse_pass<CAP>(code, n_instr, spar, P.steps, &P.st,
+        reverse_pass<CAP, MODE>(code, n_instr, spar, P.steps, &P.st,
                           (need_stencil || P.g.sdf != nullptr) ? &sa : nullptr, P.traj, sacc, conv,
                           px, py, pz, vx, vy, vz, lx, ly, lz, dvx, dvy, dvz);
         float gox[KB], goy[KB], goz[KB];
@@ -537,15 +547,34 @@ inline unsigned backward_grid(int64_t n) {
     const int64_t blocks = (want + it - 1) / it;
     return (unsigned)(blocks > 0 ? blocks : 1);
 }
-// log2 of the accumulator columns: as many lane-private columns as fit in ~40 KB per block
-inline int backward_acc_shift(const RmTape* t) {
-    int shift = 5;
-    while (shift > 0 && ((size_t)t->n_par << shift) * sizeof(float) > RM_ACC_BYTES) --shift;
-    return shift;
+// Accumulator layout for a tape (GradAcc): lane columns when n_par x BLOCK_B floats fit the budget,
+// else warp columns, shared by all warps when even those do not fit.
+inline int backward_acc_mode(const RmTape* t) {
+    return (size_t)t->n_par * BLOCK_B * sizeof(float) <= RM_ACC_BYTES ? ACC_LANES : ACC_WARPS;
+}
+inline int backward_acc_shared(const RmTape* t) {
+    return backward_acc_mode(t) == ACC_WARPS && (size_t)t->n_par * (BLOCK_B / 32) * sizeof(float) > RM_ACC_BYTES;
 }
 inline size_t backward_smem(const RmTape* t) {
-    return (size_t)t->n_par * sizeof(float) * (1 + ((size_t)1 << backward_acc_shift(t)));
+    const size_t cols = backward_acc_mode(t) == ACC_LANES ? BLOCK_B : (backward_acc_shared(t) ? 1 : BLOCK_B / 32);
+    return (size_t)t->n_par * sizeof(float) * (1 + cols);
 }
+
+// Picks the kernel instantiation: lane columns exist only for the small code capacity (a tape of
+// <= 96 parameter floats never has more than 96 instructions).
+#define RM_BWD_LAUNCH(tape, KERNEL, grid, sm, stream, ...)                                              \
+    RM_WITH_CODE(tape, {                                                                                \
+        if (CAP == rm::CODE_CAP_SMALL && rm::backward_acc_mode(tape) == rm::ACC_LANES) {                \
+            rm::TapeCode<rm::CODE_CAP_SMALL> small;                                                     \
+            rm::expand_code((tape)->code_host, (tape)->n_instr, small.ins);                             \
+            if (int s_ = rm::prepare_smem(KERNEL<rm::CODE_CAP_SMALL, rm::ACC_LANES>, sm)) return s_;    \
+            KERNEL<rm::CODE_CAP_SMALL, rm::ACC_LANES><<<grid, rm::BLOCK_B, sm, (cudaStream_t)stream>>>( \
+                small, __VA_ARGS__);                                                                    \
+        } else {                                                                                        \
+            if (int s_ = rm::prepare_smem(KERNEL<CAP, rm::ACC_WARPS>, sm)) return s_;                   \
+            KERNEL<CAP, rm::ACC_WARPS><<<grid, rm::BLOCK_B, sm, (cudaStream_t)stream>>>(code, __VA_ARGS__); \
+        }                                                                                               \
+    })
 
 }  // namespace rm
 
@@ -565,12 +594,8 @@ extern "C" int rm_sdf_vjp(const RmTape* tape, const float* points, const float* 
         RM_CUDA(cudaMemsetAsync(dpar, 0, (size_t)tape->n_par * sizeof(float), (cudaStream_t)stream));
     if (n == 0) return RM_OK;
     const size_t sm = backward_smem(tape);
-    RM_WITH_CODE(tape, {
-        if (int s = prepare_smem(sdf_vjp_kernel<CAP>, sm)) return s;
-        sdf_vjp_kernel<CAP><<<backward_grid(n), BLOCK_B, sm, (cudaStream_t)stream>>>(
-            code, tape->par, tape->n_instr, tape->n_par, backward_acc_shift(tape), backward_iters(n), points, grad_sdf, n,
-            dpoints, dpar);
-    });
+    RM_BWD_LAUNCH(tape, sdf_vjp_kernel, backward_grid(n), sm, stream, tape->par, tape->n_instr, tape->n_par,
+                  backward_acc_shared(tape), backward_iters(n), points, grad_sdf, n, dpoints, dpar);
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }
@@ -586,13 +611,9 @@ extern "C" int rm_march_bwd(const RmTape* tape, const float* origin, const float
         RM_CUDA(cudaMemsetAsync(dpar, 0, (size_t)tape->n_par * sizeof(float), (cudaStream_t)stream));
     if (n == 0) return RM_OK;
     const size_t sm = backward_smem(tape);
-    RM_WITH_CODE(tape, {
-        if (int s = prepare_smem(march_bwd_kernel<CAP>, sm)) return s;
-        march_bwd_kernel<CAP><<<backward_grid(n), BLOCK_B, sm, (cudaStream_t)stream>>>(
-            code, tape->par, tape->n_instr, tape->n_par, backward_acc_shift(tape), backward_iters(n), origin, dirs, grad_pos,
-            n, steps,
-            converge_tol, traj_scratch, dorigin, ddirs, dpar);
-    });
+    RM_BWD_LAUNCH(tape, march_bwd_kernel, backward_grid(n), sm, stream, tape->par, tape->n_instr, tape->n_par,
+                  backward_acc_shared(tape), backward_iters(n), origin, dirs, grad_pos, n, steps, converge_tol,
+                  traj_scratch, dorigin, ddirs, dpar);
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }
@@ -621,16 +642,13 @@ extern "C" int rm_render_bwd(const RmTape* tape, const RmCamera* cam, const floa
     if (a->n_rays == 0) return RM_OK;
     make_stencil(a->normals_eps, &P.st);
     P.ray_begin = a->ray_begin; P.n_rays = a->n_rays; P.steps = a->steps;
-    P.acc_shift = backward_acc_shift(tape);
+    P.acc_shared = backward_acc_shared(tape);
     P.iters = backward_iters(a->n_rays);
     P.tol = a->bwd_converge_tol;
     P.g = *grads; P.traj = traj_scratch; P.dpar = dpar; P.dposes = dposes;
     const size_t sm = backward_smem(tape);
-    RM_WITH_CODE(tape, {
-        if (int s = prepare_smem(render_bwd_kernel<CAP>, sm)) return s;
-        render_bwd_kernel<CAP><<<backward_grid(a->n_rays), BLOCK_B, sm, (cudaStream_t)stream>>>(
-            code, tape->par, tape->n_instr, tape->n_par, poses, P);
-    });
+    RM_BWD_LAUNCH(tape, render_bwd_kernel, backward_grid(a->n_rays), sm, stream, tape->par, tape->n_instr,
+                  tape->n_par, poses, P);
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }

@@ -64,17 +64,71 @@ __device__ __forceinline__ void child_adjoint(int fold, int ordinal, OpenNode<K>
     }
 }
 
-// Shared-memory gradient accumulators: `cols` (power of two <= 32) lane-private columns per tape
-// parameter, element (addr, lane & (cols-1)).  With cols = 32 every lane of a warp adds to its own
-// bank (conflict-free ATOMS, no warp reduction at all); large tapes use fewer columns, where the
-// hardware serialises the lanes that share a column.  One reduction over the columns per block
-// (flush_accumulators) replaces a warp butterfly per leaf, step and ray.
+// Shared-memory gradient accumulators.  Shared-memory float atomicAdd is a compare-and-swap loop
+// on this architecture (LDS, FADD, ATOMS.CAST.SPIN, BRA), so both layouts avoid atomics:
+//   ACC_LANES  one column per THREAD of the block: element (addr, thread).  A lane adds with a
+//              plain read-modify-write into its own word (conflict-free banks, no reduction at
+//              all).  n_par x block floats: tapes up to 96 parameter floats (the registry scenes).
+//   ACC_WARPS  one column per WARP: the 27 partials of a leaf (12 frame, <= 12 primitive, <= 3
+//              post-op) are summed across the warp by a transposing butterfly (31 shuffles; lane L
+//              ends up with the total of value L) and lane L adds it to row addr(L) of its warp's
+//              column.  n_par x warps floats; tapes too large even for that share ONE column and
+//              lane L uses atomicAdd (`shared`).
+// flush_accumulators (rm_backward.cu) sums the columns once per block.
+enum : int { ACC_LANES = 0, ACC_WARPS = 1 };
+template <int MODE>
 struct GradAcc {
     float* base;
-    int cmask;        // cols - 1
-    int shift;        // log2(cols)
-    __device__ __forceinline__ void add(int addr, float v) const {
-        if (v != 0.f) atomicAdd(base + (addr << shift) + ((int)threadIdx.x & cmask), v);
+    int n_par;
+    bool shared;      // ACC_WARPS: all warps add into one column with atomics
+
+    __device__ __forceinline__ void put(int addr, float v) const {       // ACC_WARPS, one lane per row
+        if (shared) atomicAdd(base + addr, v);
+        else base[(threadIdx.x >> 5) * n_par + addr] += v;
+    }
+    // One value per lane.  ACC_WARPS: every lane of the warp must call.
+    __device__ __forceinline__ void add1(int addr, float v) const {
+        if (MODE == ACC_LANES) {
+            if (v != 0.f) base[addr * blockDim.x + threadIdx.x] += v;
+        } else {
+            v = warp_sum(v);
+            if ((threadIdx.x & 31) == 0 && v != 0.f) put(addr, v);
+        }
+    }
+    // The partials of one leaf: frame rows at `frame_row` (when has_frame), n_prim primitive floats at
+    // `prim_row`, np post-op floats at `post_row` (rows in floats).  ACC_WARPS: every lane must call.
+    __device__ __forceinline__ void add_leaf(bool has_frame, int frame_row, int n_prim, int prim_row, int np,
+                                             int post_row, const float (&fr)[12], const float (&pr)[12],
+                                             const float (&gpost)[3]) const {
+        if (MODE == ACC_LANES) {
+            float* col = base + threadIdx.x;
+            const int stride = blockDim.x;
+            if (has_frame) {
+#pragma unroll
+                for (int i = 0; i < 12; ++i)
+                    if (fr[i] != 0.f) col[(frame_row + i) * stride] += fr[i];
+            }
+#pragma unroll
+            for (int i = 0; i < 12; ++i)
+                if (i < n_prim && pr[i] != 0.f) col[(prim_row + i) * stride] += pr[i];
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+                if (i < np && gpost[i] != 0.f) col[(post_row + i) * stride] += gpost[i];
+        } else {
+            const int lane = threadIdx.x & 31;
+            float v[32];
+#pragma unroll
+            for (int i = 0; i < 12; ++i) { v[i] = fr[i]; v[12 + i] = pr[i]; }
+#pragma unroll
+            for (int i = 0; i < 3; ++i) v[24 + i] = gpost[i];
+#pragma unroll
+            for (int i = 27; i < 32; ++i) v[i] = 0.f;
+            const float tot = warp_transpose_sum(v, lane);
+            const int j = lane < 12 ? lane : (lane < 24 ? lane - 12 : lane - 24);
+            const bool valid = lane < 12 ? has_frame : (lane < 24 ? j < n_prim : (lane < 27 && j < np));
+            const int row = lane < 12 ? frame_row : (lane < 24 ? prim_row : post_row);
+            if (valid && tot != 0.f) put(row + j, tot);
+        }
     }
 };
 
@@ -85,12 +139,12 @@ constexpr float CULL_EPS = 1e-9f;
 // The reverse sweep.  Outputs g{x,y,z}[k] = abar[k] * grad_p f(p_k) and adds d f / d par into
 // `acc`.  All 32 lanes of the warp must call this together (warp votes skip leaves whose adjoint
 // is zero in every lane: the losing children of a hard union, culled children of a smooth one).
-template <int K, int CAP>
+template <int K, int CAP, int MODE>
 __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_instr,
                                           const float4* __restrict__ spar, const float (&px)[K],
                                           const float (&py)[K], const float (&pz)[K],
                                           const float (&abar)[K], const NodeRecords<K, CAP>& rec,
-                                          const GradAcc acc, float (&gx)[K], float (&gy)[K],
+                                          const GradAcc<MODE> acc, float (&gx)[K], float (&gy)[K],
                                           float (&gz)[K]) {
     OpenNode<K> cur;
     OpenNode<K> stk[MAX_DEPTH];
@@ -110,7 +164,7 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
                 float g = 0.f;
 #pragma unroll
                 for (int k = 0; k < K; ++k) g += cur.a[k] != 0.f ? div_rn_inline(cur.s[k] - cur.a[k] * cur.d[k], cur.c) : 0.f;
-                acc.add(off * 4, g);
+                acc.add1(off * 4, g);
             }
             if (!(head & HEAD_ROOT)) cur = stk[--sp];
             continue;
@@ -128,7 +182,7 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
             posts_backward<K>(head, sg, a, gpost);
 #pragma unroll
             for (int i = 0; i < 3; ++i)
-                if (i < np) acc.add(off * 4 + i, gpost[i]);
+                if (i < np) acc.add1(off * 4 + i, gpost[i]);
             if (!(head & HEAD_ROOT)) stk[sp++] = cur;
 #pragma unroll
             for (int k = 0; k < K; ++k) {
@@ -210,17 +264,7 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
 #pragma unroll
             for (int i = 0; i < 12; ++i) pr[i] = fmaf(ak, gp[i], pr[i]);
         }
-        if (has_frame) {
-#pragma unroll
-            for (int i = 0; i < 12; ++i) acc.add(off * 4 + i, fr[i]);
-        }
-        const int n_prim = 4 * prim_f4(op);
-#pragma unroll
-        for (int i = 0; i < 12; ++i)
-            if (i < n_prim) acc.add(prim_rec * 4 + i, pr[i]);
-#pragma unroll
-        for (int i = 0; i < 3; ++i)
-            if (i < np) acc.add(post_rec * 4 + i, gpost[i]);
+        acc.add_leaf(has_frame, off * 4, 4 * prim_f4(op), prim_rec * 4, np, post_rec * 4, fr, pr, gpost);
     }
 }
 
