@@ -291,6 +291,30 @@ def run_gpu(args):
                      "note": "per-GPU, bounding-sphere culling of smooth-union children inside march "
                              "steps; executed < algorithmic work, so no roofline fraction is quoted"}
 
+    # the same frame as ONE CUDA-graph replay (reduce init + render + finalize captured once, the way
+    # ray_marching_b200.frames.FrameLoop runs a display loop): c1 is launch-latency scale
+    graph_info = None
+    if not wl["backward"] and world == 1:
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, capture_error_mode="relaxed"):
+            gpu_step()
+        n_g = 200 if rays <= (1 << 22) else 5
+        for _ in range(3):
+            g.replay()
+        ge0, ge1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ge0.record()
+        for _ in range(n_g):
+            g.replay()
+        ge1.record()
+        ge1.synchronize()
+        g_ms = ge0.elapsed_time(ge1) / n_g
+        graph_info = {"ms_per_frame": g_ms, "value": rays / (g_ms * 1e-3) / 1e6, "unit": "Mrays/s",
+                      "replays": n_g,
+                      "note": "back-to-back CUDA-graph replays of the whole frame, no L2 flush (the path "
+                              "reads nothing per ray; outputs are write-only)"}
+        del g
+
     # end-to-end: pinned host pose in, images out to pinned host memory, every step
     e2e = measure_e2e(frame, wl, q, t, dev, args, barrier) if not wl["backward"] else \
         extra["e2e"](args, barrier)
@@ -327,6 +351,8 @@ def run_gpu(args):
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks,
         }
+        if graph_info is not None:
+            line["frame_graph"] = graph_info
         if cull_info is not None:
             line["culling"] = cull_info
         if kern_ms is not None:

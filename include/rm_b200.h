@@ -123,6 +123,18 @@ int rm_sdf_eval(const RmTape* tape, const float* points, int64_t n_points, float
 int rm_camera_rays(const RmCamera* cam, const float* poses, int64_t ray_begin, int64_t n_rays,
                    float* origin_out, float* dirs_out, void* stream);
 
+/* Camera-state integration of EventAggregator.get_state (control.py:148-165), in place on the
+ * device pose records [n_views][RM_POSE_STRIDE]:
+ *     t <- t + Q.rotation(translation_input * translation_sensitivity, q)        (old q)
+ *     q <- normalize(Q.multiply(q, Q.to_versor(orientation_input * rotation_sensitivity)))
+ * inputs: device [n_frames][n_views][6] = (translation input x,y,z, orientation input yz,zx,xy) --
+ * the two vectors get_state builds from the keyboard / mouse state.  frame_counter: device int32;
+ * frame (*frame_counter mod n_frames) is applied and the counter incremented, so a scripted path
+ * advances inside a captured CUDA graph with no host work; NULL is allowed when n_frames == 1. */
+int rm_camera_update(float* poses, const float* inputs, int32_t n_views, int32_t n_frames,
+                     float translation_sensitivity, float rotation_sensitivity,
+                     int32_t* frame_counter, void* stream);
+
 /* SDFMarcher.forward (rendering/ray_marching.py:72-84): p <- f(p) v + p, `steps` times. */
 int rm_march(const RmTape* tape, const float* origin, const float* dirs, int64_t n_rays,
              int32_t steps, int32_t fast_math, float* pos_out, void* stream);

@@ -201,6 +201,32 @@ def gen_grads(ref, out):
              for (_, p), gp in zip(params, grads2[2:])]))
 
 
+def gen_camera_path(ref, out):
+    """A scripted 24-frame path of 3 cameras through control.py:148-165 (the reference's own source)."""
+    import types
+    g = torch.Generator().manual_seed(23)
+    n_frames, n_views = 24, 3
+    script = torch.cat([torch.randn(n_frames, n_views, 3, generator=g),
+                        torch.randn(n_frames, n_views, 3, generator=g) * 2.0], dim=-1)
+    script[5, :, :3] = 0.0                      # pure rotation frame
+    script[9, :, 3:] = 0.0                      # pure translation frame
+    state = types.SimpleNamespace(
+        position=torch.tensor([[0.0, 0.0, 1.0], [0.5, -0.25, -2.0], [-1.0, 2.0, 0.5]]),
+        orientation=torch.nn.functional.normalize(torch.randn(n_views, 4, generator=g), dim=-1),
+        translation_sensitivity=0.05, rotation_sensitivity=0.02)
+    out["path/script"] = np32(script)
+    out["path/position0"] = np32(state.position)
+    out["path/orientation0"] = np32(state.orientation)
+    out["path/sens"] = np.array([state.translation_sensitivity, state.rotation_sensitivity], np.float32)
+    pos, ori = [], []
+    for f in range(n_frames):
+        ref.camera_state_update(state, script[f, :, :3], script[f, :, 3:])
+        pos.append(np32(state.position).copy())
+        ori.append(np32(state.orientation).copy())
+    out["path/positions"] = np.stack(pos)
+    out["path/orientations"] = np.stack(ori)
+
+
 def main():
     assert ref_import.available(), "needs /root/reference (build container only)"
     torch.manual_seed(0)
@@ -208,7 +234,7 @@ def main():
     ref = ref_import.load()
     os.makedirs(OUT, exist_ok=True)
     for name, fn in (("quaternion", gen_quaternion), ("nodes", gen_nodes), ("camera", gen_camera),
-                     ("render", gen_render), ("grads", gen_grads)):
+                     ("render", gen_render), ("grads", gen_grads), ("camera_path", gen_camera_path)):
         out = {}
         fn(ref, out)
         path = os.path.join(OUT, f"{name}.npz")

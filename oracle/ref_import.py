@@ -65,4 +65,22 @@ def load():
         with _cwd(REF), contextlib.redirect_stdout(io.StringIO()):
             return ref_loop_cls(*a, **k).float()
     ns.RenderLoop = make_render_loop
+
+    # control.py:148-165: the two state-update assignments of EventAggregator.get_state, executed
+    # from the reference's own source text against a stand-in `self`
+    cls = next(n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "EventAggregator")
+    fn = next(n for n in cls.body if isinstance(n, ast.FunctionDef) and n.name == "get_state")
+    upd = [n for n in fn.body if isinstance(n, ast.Assign) and isinstance(n.targets[0], ast.Attribute)
+           and n.targets[0].attr in ("position", "orientation")
+           and isinstance(n.targets[0].value, ast.Name) and n.targets[0].value.id == "self"]
+    assert [n.targets[0].attr for n in upd] == ["position", "orientation"], "control.py:148-165 moved"
+    code = compile(ast.Module(body=upd, type_ignores=[]), "control.py", "exec")
+    torch = __import__("torch")
+
+    def camera_state_update(state, translation_input, orientation_input):
+        """state: namespace with position (N,3), orientation (N,4), translation_sensitivity,
+        rotation_sensitivity; updated in place like EventAggregator's attributes."""
+        exec(code, {"Q": Q, "F": torch.nn.functional, "self": state,
+                    "translation_input": translation_input, "orientation_input": orientation_input})
+    ns.camera_state_update = camera_state_update
     return ns

@@ -82,6 +82,20 @@ def q_to_versor(v: Tensor) -> Tensor:
     return torch.cat([w, v], dim=-1)
 
 
+def camera_state_update(position: Tensor, orientation: Tensor, translation_input: Tensor,
+                        orientation_input: Tensor, translation_sensitivity: float,
+                        rotation_sensitivity: float):
+    """One camera-state integration step of EventAggregator.get_state (control.py:148-165):
+    position (N,3), orientation (N,4); inputs (1,3) or (N,3).  Returns the new (position, orientation);
+    the position update uses the OLD orientation."""
+    new_position = q_rotation((translation_input * translation_sensitivity).expand_as(position),
+                              orientation) + position
+    new_orientation = torch.nn.functional.normalize(
+        q_multiply(orientation, q_to_versor(orientation_input * rotation_sensitivity).expand_as(orientation)),
+        p=2, dim=-1, eps=0)
+    return new_position, new_orientation
+
+
 def q_to_so3(q: Tensor) -> Tensor:
     """Row-major 3x3 from pair products, flattened to (-1,3,3) (quaternion.py:114-124)."""
     w, x, y, z = q.unbind(-1)

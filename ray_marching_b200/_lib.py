@@ -58,6 +58,8 @@ _SIGNATURES = {
                                  C.c_void_p, C.c_void_p, C.c_void_p]),
     "rm_march": (C.c_int, [C.POINTER(RmTape), C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                            C.c_int32, C.c_void_p, C.c_void_p]),
+    "rm_camera_update": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_float, C.c_float,
+                                   C.c_void_p, C.c_void_p]),
     "rm_normals": (C.c_int, [C.POINTER(RmTape), C.c_void_p, C.c_int64, C.c_float, C.c_void_p,
                              C.c_void_p, C.c_void_p]),
     "rm_render": (C.c_int, [C.POINTER(RmTape), C.POINTER(RmCamera), C.c_void_p,

@@ -37,6 +37,21 @@ extern "C" int rm_camera_rays(const RmCamera* cam, const float* poses, int64_t r
     return RM_OK;
 }
 
+extern "C" int rm_camera_update(float* poses, const float* inputs, int32_t n_views, int32_t n_frames,
+                                float translation_sensitivity, float rotation_sensitivity,
+                                int32_t* frame_counter, void* stream) {
+    if (n_views < 0 || n_frames < 1 || (n_views > 0 && (poses == nullptr || inputs == nullptr)))
+        return fail(RM_ERR_INVALID, "rm_camera_update: null buffer, negative view count or no frames");
+    if (frame_counter == nullptr && n_frames != 1)
+        return fail(RM_ERR_INVALID, "rm_camera_update: a multi-frame path needs the device frame counter");
+    if (n_views == 0) return RM_OK;
+    camera_update_kernel<<<1, 128, 0, (cudaStream_t)stream>>>(poses, inputs, n_views, n_frames,
+                                                              translation_sensitivity, rotation_sensitivity,
+                                                              frame_counter);
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+}
+
 extern "C" int rm_march(const RmTape* tape, const float* origin, const float* dirs, int64_t n,
                         int32_t steps, int32_t fast_math, float* pos_out, void* stream) {
     if (int s = check_tape(tape)) return s;

@@ -149,6 +149,43 @@ camera_kernel(CamParams cam, const float* __restrict__ poses, int64_t ray_begin,
     store3(dirs, first, n, vx, vy, vz);
 }
 
+// ---- rm_camera_update: the camera-state integration of EventAggregator.get_state ------------
+// control.py:148-165, for every view:
+//   t <- t + Q.rotation(translation_input * t_sens, q)                    (uses the OLD q)
+//   q <- normalize(Q.multiply(q, Q.to_versor(orientation_input * r_sens)), eps = 0)
+// `inputs` holds n_frames x n_views x 6 floats (translation input xyz, orientation input
+// yz/zx/xy); frame `*counter % n_frames` is applied and the device-side counter advanced, so a
+// scripted camera path replays inside a CUDA graph without any host work per frame.
+__global__ void camera_update_kernel(float* __restrict__ poses, const float* __restrict__ inputs,
+                                     int n_views, int n_frames, float t_sens, float r_sens,
+                                     int* __restrict__ counter) {
+    const int frame = counter != nullptr ? (int)((unsigned)*counter % (unsigned)n_frames) : 0;
+    for (int v = threadIdx.x; v < n_views; v += blockDim.x) {
+        const float* in = inputs + ((size_t)frame * n_views + v) * 6;
+        float* ps = poses + (size_t)v * POSE_STRIDE;
+        const float w = ps[0], x = ps[1], y = ps[2], z = ps[3];
+        // Q.rotation (quaternion.py:55-72): t = 2 (q_v x V), V' = V + w t + q_v x t
+        const float ux = in[0] * t_sens, uy = in[1] * t_sens, uz = in[2] * t_sens;
+        const float tx = 2.f * (y * uz - z * uy), ty = 2.f * (z * ux - x * uz), tz = 2.f * (x * uy - y * ux);
+        ps[4] += ux + w * tx + (y * tz - z * ty);
+        ps[5] += uy + w * ty + (z * tx - x * tz);
+        ps[6] += uz + w * tz + (x * ty - y * tx);
+        // Q.to_versor (quaternion.py:75-91): (sqrt(1 - |V|^2), V); NaN when |V| > 1, as in the reference
+        const float bx = in[3] * r_sens, by = in[4] * r_sens, bz = in[5] * r_sens;
+        const float bw = sqrt_rn_inline(1.f - (bx * bx + by * by + bz * bz));
+        // Q.multiply (quaternion.py:24-46), scalar first
+        const float nw = w * bw - x * bx - y * by - z * bz;
+        const float nx = w * bx + x * bw + y * bz - z * by;
+        const float ny = w * by - x * bz + y * bw + z * bx;
+        const float nz = w * bz + x * by - y * bx + z * bw;
+        const float len = sqrt_rn_inline(nw * nw + nx * nx + ny * ny + nz * nz);
+        ps[0] = div_rn_inline(nw, len); ps[1] = div_rn_inline(nx, len);
+        ps[2] = div_rn_inline(ny, len); ps[3] = div_rn_inline(nz, len);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && counter != nullptr) *counter = *counter + 1;
+}
+
 // ---- the march loop (ray_marching.py:78-84): p <- f(p) v + p --------------------------------
 // CULL: see eval_scene.  The union value of the previous step and the step length bound the union
 // value at the new position (|v| = 1, so the ray moved |f(p)|).

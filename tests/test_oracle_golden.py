@@ -178,3 +178,17 @@ def test_config4_gradients(golden, tag, build):
     flat = torch.cat([(gp if gp is not None else torch.zeros_like(p)).reshape(-1)
                       for p, gp in zip(params, grads[2:])])
     same(flat, g[f"grads/{tag}/dparams_flat"], 2e-5)
+
+
+def test_camera_state_update_path(golden):
+    """control.py:148-165 restated (oracle.camera_state_update) against 24 frames x 3 cameras produced
+    by the reference's own get_state source lines."""
+    g = golden("camera_path")
+    pos, ori = t32(g["path/position0"]), t32(g["path/orientation0"])
+    ts, rs = [float(x) for x in g["path/sens"]]
+    script = t32(g["path/script"])
+    for f in range(script.shape[0]):
+        pos, ori = O.camera_state_update(pos, ori, script[f, :, :3], script[f, :, 3:], ts, rs)
+        np.testing.assert_allclose(pos.numpy(), g["path/positions"][f], rtol=0, atol=1e-6)
+        np.testing.assert_allclose(ori.numpy(), g["path/orientations"][f], rtol=0, atol=1e-6)
+    assert np.allclose(np.linalg.norm(g["path/orientations"], axis=-1), 1.0, atol=1e-6)
