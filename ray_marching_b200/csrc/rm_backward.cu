@@ -566,7 +566,7 @@ inline size_t backward_smem(const RmTape* t) {
     RM_WITH_CODE(tape, {                                                                                \
         if (CAP == rm::CODE_CAP_SMALL && rm::backward_acc_mode(tape) == rm::ACC_LANES) {                \
             rm::TapeCode<rm::CODE_CAP_SMALL> small;                                                     \
-            rm::expand_code((tape)->code_host, (tape)->n_instr, small.ins);                             \
+            rm::expand_code((tape)->code_host, (tape)->n_instr, small);                             \
             if (int s_ = rm::prepare_smem(KERNEL<rm::CODE_CAP_SMALL, rm::ACC_LANES>, sm)) return s_;    \
             KERNEL<rm::CODE_CAP_SMALL, rm::ACC_LANES><<<grid, rm::BLOCK_B, sm, (cudaStream_t)stream>>>( \
                 small, __VA_ARGS__);                                                                    \

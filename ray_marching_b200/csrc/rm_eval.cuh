@@ -74,11 +74,19 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
     float stk[MAX_DEPTH * (2 * K + 1)];              // spilled accumulators of enclosing unions
     int sp = 0;
     const char* sbytes = reinterpret_cast<const char*>(spar);
+    // root union without post-ops: start inside it (see TapeCode::hdr); record mode walks everything
+    int pc0 = 0, pc1 = n_instr, rootm = 0;
+    if (!RECORD) {
+        const int4 h = C.hdr;
+        pc0 = h.x; pc1 = h.y; rootm = h.z;
+        if (rootm == 2) c = M::exp_scale(*reinterpret_cast<const float*>(sbytes + h.w));
+    }
+    const float a_init = rootm == 1 ? CUDART_INF_F : (rootm == 2 ? -CUDART_INF_F : 0.f);
 #pragma unroll
-    for (int k = 0; k < K; ++k) { a0[k] = 0.f; a1[k] = 0.f; d[k] = 0.f; }
+    for (int k = 0; k < K; ++k) { a0[k] = a_init; a1[k] = 0.f; d[k] = 0.f; }
 
-    int4 nxt = C.ins[0];
-    for (int pc = 0; pc < n_instr; ++pc) {
+    int4 nxt = C.ins[pc0];
+    for (int pc = pc0; pc < pc1; ++pc) {
         const int4 ins = nxt;
         nxt = C.ins[pc + 1];                          // prefetch (pad entry after the last instruction)
         const float4* P = reinterpret_cast<const float4*>(sbytes + ins.z);
@@ -244,8 +252,16 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
             }
         }
     }
+    if (rootm == 1) {
 #pragma unroll
-    for (int k = 0; k < K; ++k) out[k] = d[k];
+        for (int k = 0; k < K; ++k) out[k] = a0[k];
+    } else if (rootm == 2) {
+#pragma unroll
+        for (int k = 0; k < K; ++k) out[k] = M::div(a0[k] + M::log(a1[k]), c);
+    } else {
+#pragma unroll
+        for (int k = 0; k < K; ++k) out[k] = d[k];
+    }
 }
 
 // Cooperative copy of the tape parameters from global into dynamic shared memory.

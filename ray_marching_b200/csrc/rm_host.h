@@ -56,12 +56,12 @@ inline size_t tape_smem_bytes(const RmTape* t) { return (size_t)t->n_par * 4; }
         if ((tape)->n_instr <= rm::CODE_CAP_SMALL) {                                     \
             constexpr int CAP = rm::CODE_CAP_SMALL;                                      \
             rm::TapeCode<CAP> code;                                                      \
-            rm::expand_code((tape)->code_host, (tape)->n_instr, code.ins, with_cull);   \
+            rm::expand_code((tape)->code_host, (tape)->n_instr, code, with_cull);   \
             __VA_ARGS__                                                                  \
         } else {                                                                         \
             constexpr int CAP = rm::CODE_CAP_LARGE;                                      \
             rm::TapeCode<CAP> code;                                                      \
-            rm::expand_code((tape)->code_host, (tape)->n_instr, code.ins, with_cull);   \
+            rm::expand_code((tape)->code_host, (tape)->n_instr, code, with_cull);   \
             __VA_ARGS__                                                                  \
         }                                                                                \
     } while (0)

@@ -54,6 +54,11 @@ constexpr int CODE_CAP_SMALL = 96;
 constexpr int CODE_CAP_LARGE = 1024;
 template <int CAP>
 struct TapeCode {
+    // x, y: instruction range the forward interpreter walks; z: how it treats the root (0: walk the
+    // whole tape; 1 / 2: the outermost hard / smooth union has no post-ops, so its OPEN and CLOSE are
+    // not dispatched -- the accumulators start as that union's and the result is read from them);
+    // w: byte offset of the root smooth union's record.  A registry scene is 4 leaves + this pair.
+    int4 hdr;
     int4 ins[CAP + 1];     // + one pad entry: the interpreter prefetches ins[pc + 1] unconditionally
 };
 
@@ -67,7 +72,7 @@ __host__ __device__ __forceinline__ int ins_post_off(int w) { return w & 0xFFFFF
 
 // Host: [n][2] words -> expanded instructions.
 // `with_cull`: set the DISP_CULL dispatch flags (only the culling kernels look at them).
-inline void expand_code(const int32_t* words, int n, int4* out, bool with_cull = false) {
+inline void expand_instructions(const int32_t* words, int n, int4* out, bool with_cull) {
     for (int i = 0; i < n; ++i) {
         const int head = words[2 * i], w1 = words[2 * i + 1];
         const int op = head_op(head), np = head_npost(head), fold = head_fold(head);
@@ -87,6 +92,20 @@ inline void expand_code(const int32_t* words, int n, int4* out, bool with_cull =
         out[i] = make_int4(head, w1, off * 16, ((np ? post_f4 * 16 : 0) & 0xFFFFF) | (tail << 20) | (disp << 24));
     }
     out[n] = make_int4(0, 0, 0, 0);
+}
+template <int CAP>
+inline void expand_code(const int32_t* words, int n, TapeCode<CAP>& code, bool with_cull = false) {
+    expand_instructions(words, n, code.ins, with_cull);
+    code.hdr = make_int4(0, n, 0, 0);
+    if (n >= 2) {
+        const int open = words[0], close = words[2 * (n - 1)];
+        const int oop = head_op(open), cop = head_op(close);
+        const bool pair = (open & HEAD_ROOT) && (close & HEAD_ROOT) && head_npost(close) == 0 &&
+                          ((oop == OP_OPEN_MIN && cop == OP_CLOSE_MIN) || (oop == OP_OPEN_SMOOTH && cop == OP_CLOSE_SMOOTH));
+        const bool culled_root = with_cull && word_cull(words[1]);       // the culling set-up lives in OPEN
+        if (pair && !culled_root)
+            code.hdr = make_int4(1, n - 1, oop == OP_OPEN_MIN ? 1 : 2, word_par(words[1]) * 16);
+    }
 }
 
 }  // namespace rm
