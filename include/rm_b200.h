@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define RM_B200_ABI_VERSION 3
+#define RM_B200_ABI_VERSION 4
 
 typedef enum RmStatus {
     RM_OK = 0,

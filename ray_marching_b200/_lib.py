@@ -17,7 +17,7 @@ LIB_PATH = os.environ.get("RM_B200_LIB") or os.path.join(_HERE, "csrc", "librm_b
 
 POSE_STRIDE = 8
 REDUCE_FLOATS = 8
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 
 class RmTape(C.Structure):
