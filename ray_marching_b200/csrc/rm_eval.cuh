@@ -206,7 +206,6 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
 
         // tail = fold * 4 + post case: unary value ops (rounding / onion), then the parent's fold
         const int tail = ins_tail(ins.w);
-        if (tail == 0) continue;                      // the root's CLOSE
         const int post = tail & 3;
         if (post != TAIL_POST_NONE) {
             const float4 pp = *reinterpret_cast<const float4*>(sbytes + ins_post_off(ins.w));
@@ -229,19 +228,8 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
                 }
             }
         }
-        if (tail < 2 * 4) {
-            if (tail >= 4) {                          // FOLD_MIN
-                if (RECORD) {
-                    const int ordinal = head_ordinal(ins.x);
-#pragma unroll
-                    for (int k = 0; k < K; ++k)
-                        if (d[k] < a0[k]) { a0[k] = d[k]; a1[k] = __int_as_float(ordinal); }   // strict: first wins ties
-                } else {
-#pragma unroll
-                    for (int k = 0; k < K; ++k) a0[k] = min_nan(a0[k], d[k]);
-                }
-            }
-        } else {                                      // FOLD_SMOOTH
+        // the parent's fold
+        if (tail & (FOLD_SMOOTH * 4)) {
 #pragma unroll
             for (int k = 0; k < K; ++k) {
                 if (RECORD) rec->y[pc][k] = d[k];
@@ -250,7 +238,17 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
                 a1[k] = (x > a0[k]) ? fmaf(a1[k], e, 1.f) : a1[k] + e;
                 a0[k] = fmaxf(a0[k], x);
             }
-        }
+        } else if (tail & (FOLD_MIN * 4)) {
+            if (RECORD) {
+                const int ordinal = head_ordinal(ins.x);
+#pragma unroll
+                for (int k = 0; k < K; ++k)
+                    if (d[k] < a0[k]) { a0[k] = d[k]; a1[k] = __int_as_float(ordinal); }   // strict: first wins ties
+            } else {
+#pragma unroll
+                for (int k = 0; k < K; ++k) a0[k] = min_nan(a0[k], d[k]);
+            }
+        }                                             // else FOLD_NONE: the root (value stays in d)
     }
     if (rootm == 1) {
 #pragma unroll
