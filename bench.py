@@ -215,7 +215,7 @@ def run_gpu(args):
         return res_holder["res"]
 
     if wl["backward"]:
-        gpu_step, extra = make_backward_step(loop, scene, q, t, dev, world)
+        gpu_step, extra = make_backward_step(loop, scene, q, t, dev, world, wl["name"])
     launches_per_step = (3 if needs_reduce else 1) if not wl["backward"] else extra["launches"]
 
     flush = torch.empty(192 * 1024 * 1024 // 4, device=dev)      # 192 MB > 126 MB L2
@@ -357,9 +357,11 @@ def run_gpu(args):
             line["culling"] = cull_info
         if kern_ms is not None:
             ach = fpr * rays / (kern_max * 1e-3) / 1e12
+            traffic, traffic_src = ncu_traffic("render_kernel", wl["name"])
             line["roofline"] = {
                 "bound": "fp32", "kernel": "render_kernel", "achieved": ach, "peak": peak["tflops"],
-                "unit": "TFLOP/s", "frac": ach / peak["tflops"], "traffic": None,
+                "unit": "TFLOP/s", "frac": ach / peak["tflops"], "traffic": traffic,
+                "traffic_source": traffic_src, "traffic_unit": "bytes of DRAM per launch",
                 "kernel_ms": kern_max, "algorithmic_flops_per_ray": fpr,
                 "peak_source": "measured: FFMA microbenchmark (rm_probe_ffma) on this GPU; "
                                "nominal 74.5 TFLOP/s at 1965 MHz",
@@ -416,7 +418,27 @@ def measure_e2e(frame, wl, q, t, dev, args, barrier):
     return {"ms_total": (time.perf_counter() - t0) * 1e3, "h2d": h2d, "d2h": d2h}
 
 
-def make_backward_step(loop, scene, q, t, dev, world):
+def ncu_traffic(kernel: str, workload: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel (bytes per launch) from the
+    newest committed `ncu --set full` summary of this workload (profiles/rNN/*_<kernel>_<wl>_summary.txt);
+    None when no capture of this workload is committed.  (bench.py never runs under a profiler.)"""
+    import glob
+    import re
+    tag = {"render_kernel": "render", "render_bwd_kernel": "render_bwd"}[kernel]
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*", f"*_{tag}_{workload}_summary.txt")))
+    if not files:
+        return None, None
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    total, seen = 0.0, 0
+    for line in open(files[-1]):
+        m = re.match(r"dram__bytes_(read|write)\.sum\s+(\w+)\s+([0-9.,]+)", line)
+        if m:
+            total += float(m.group(3).replace(",", "")) * scale.get(m.group(2), 1.0)
+            seen += 1
+    return (total, os.path.relpath(files[-1], ROOT)) if seen == 2 else (None, None)
+
+
+def make_backward_step(loop, scene, q, t, dev, world, wl_name="c4"):
     """c4: one Adam step of inverse rendering -- forward (camera, march, stencil, lambertian + raw
     depth), MSE loss against a target rendered from perturbed parameters, backward through the
     replay kernels, all-reduce of the flat gradient over ranks (one view per rank), Adam update."""
@@ -482,8 +504,10 @@ def make_backward_step(loop, scene, q, t, dev, world):
         bwd_flops = 2.0 * (63 + STEPS * (F + 6) + F + 4 * F + 45)   # 2x the differentiated forward region
         alg = bwd_flops * rays_n
         ach = alg / (kms * 1e-3) / 1e12
+        traffic, traffic_src = ncu_traffic("render_bwd_kernel", wl_name)
         return {"bound": "fp32", "kernel": "render_bwd_kernel", "achieved": ach, "peak": peak["tflops"],
-                "unit": "TFLOP/s", "frac": ach / peak["tflops"], "traffic": None, "kernel_ms": kms,
+                "unit": "TFLOP/s", "frac": ach / peak["tflops"], "traffic": traffic,
+                "traffic_source": traffic_src, "traffic_unit": "bytes of DRAM per launch", "kernel_ms": kms,
                 "algorithmic_flops_per_ray": bwd_flops,
                 "step_algorithmic_tflops": 3.0 * fwd_flops * rays_n / (ms_step * 1e-3) / 1e12,
                 "peak_source": "measured: FFMA microbenchmark (rm_probe_ffma) on this GPU; "
