@@ -225,6 +225,18 @@ def run_gpu(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # small tapes: the tape-specialised kernel (nvcc at scene-build time, cached in build/spec/);
+    # any failure (no nvcc on the box) leaves the interpreter in place and says so
+    spec_on, spec_note = False, "interpreter"
+    if not wl["backward"] and args.specialise == "on" and not args.cull:
+        from ray_marching_b200 import specialise as SPEC
+        if tape.n_instr <= SPEC.MAX_SPEC_INSTR:
+            try:
+                loop.specialise(True)
+                spec_on, spec_note = True, "tape-specialised (RenderLoop.specialise())"
+            except Exception as exc:
+                spec_note = f"interpreter (specialisation unavailable: {str(exc)[:120]})"
+
     peak = measure_fp32_peak(dev)
     for _ in range(max(args.warmup, 3)):
         gpu_step()
@@ -291,6 +303,30 @@ def run_gpu(args):
                      "note": "per-GPU, bounding-sphere culling of smooth-union children inside march "
                              "steps; executed < algorithmic work, so no roofline fraction is quoted"}
 
+    # the same frame through the general tape INTERPRETER when the headline ran the tape-specialised
+    # kernel (specialise.py): reported beside it
+    interp_info = None
+    if spec_on:
+        loop.specialise(False)
+        for _ in range(3):
+            gpu_step()
+        torch.cuda.synchronize()
+        xs = []
+        for _ in range(max(3, min(args.steps, 20))):
+            flush.zero_()
+            xe0, xe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            xe0.record()
+            gpu_step()
+            xe1.record()
+            xe1.synchronize()
+            xs.append(xe0.elapsed_time(xe1))
+        x_ms = sum(xs) / len(xs)
+        interp_info = {"ms_per_step": x_ms, "value": rays / (x_ms * 1e-3) / 1e6, "unit": "Mrays/s",
+                       "frac_of_fp32_peak_whole_step": fpr * rays / (x_ms * 1e-3) / 1e12 / peak["tflops"],
+                       "note": "per-GPU, same frame through the general tape interpreter (the default of "
+                               "RenderLoop; the headline uses RenderLoop.specialise())"}
+        loop.specialise(True)
+
     # the same frame as ONE CUDA-graph replay (reduce init + render + finalize captured once, the way
     # ray_marching_b200.frames.FrameLoop runs a display loop): c1 is launch-latency scale
     graph_info = None
@@ -344,6 +380,7 @@ def run_gpu(args):
                        "marching_steps": STEPS, "views": world, "sharding": "one view per GPU",
                        "l2": "flushed between timed iterations (192 MB memset, untimed)",
                        "early_exit": bool(args.early_exit), "cull": bool(args.cull), "tape": tape.describe(),
+                       "render_kernel": spec_note,
                        "msteps_per_s": value * STEPS * (wl["bounces"] + 1),
                        "wall_s_timed_region": wall},
             "e2e": {"value": rays * world / (e2e_ms / args.steps * 1e-3) / 1e6, "unit": "Mrays/s",
@@ -351,6 +388,8 @@ def run_gpu(args):
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks,
         }
+        if interp_info is not None:
+            line["interpreter"] = interp_info
         if graph_info is not None:
             line["frame_graph"] = graph_info
         if cull_info is not None:
@@ -636,6 +675,9 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--specialise", default="on", choices=["off", "on"],
+                    help="forward workloads with small tapes (c1, c2) run the tape-specialised render kernel "
+                         "(RenderLoop.specialise()); the interpreter timing is reported as an extra key")
     ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c4", "c4b", "c5"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--early-exit", type=int, default=0,

@@ -47,6 +47,16 @@ class RenderLoop(nn.Module):
         self.fast_math = True            # approximate sqrt/exp inside march steps only
         self.cull = False                # bounding-sphere culling of smooth-union children (march steps)
 
+    def specialise(self, enable: bool = True) -> "RenderLoop":
+        """Compiles (nvcc, once per scene structure, cached under build/spec/) and selects a render
+        kernel with this scene's tape unrolled into straight-line code instead of interpreted
+        (``specialise.py``); parameters stay run-time data.  Small tapes only; ``enable=False``
+        returns to the interpreter.  Affects the fused no-autograd path."""
+        from . import specialise as S
+        tape = tape_of(self.scene)
+        tape.spec_lib = S.specialised_lib(tape) if enable else None
+        return self
+
     # ---- fused, no autograd -------------------------------------------------------------
     def render_planes(self, orientations: Tensor, translations: Tensor, *, modes: Sequence[int] = (),
                       gbuffer: bool = False, display_mode: int = -1, degree: int = 1,

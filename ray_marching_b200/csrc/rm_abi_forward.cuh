@@ -9,6 +9,7 @@ inline unsigned grid_for(int64_t n) { return (unsigned)((n + (int64_t)BLOCK * K 
 
 using namespace rm;
 
+#ifndef RM_SPEC_INC      // a tape-specialised library exports rm_render only (plus version / error)
 extern "C" int rm_sdf_eval(const RmTape* tape, const float* points, int64_t n, float* out, void* stream) {
     if (int s = check_tape(tape)) return s;
     if (n < 0 || (n > 0 && (points == nullptr || out == nullptr)))
@@ -103,6 +104,8 @@ extern "C" int rm_reduce_init(float* reduce, void* stream) {
     return RM_OK;
 }
 
+#endif  // RM_SPEC_INC
+
 extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* poses,
                          const RmRenderArgs* a, const RmRenderOut* out, void* stream) {
     if (int s = check_tape(tape)) return s;
@@ -133,6 +136,26 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
     P.display_mode = a->display_mode; P.degree = a->degree; P.early_exit = a->early_exit;
     P.cmap = a->cmap; P.out = *out;
     const size_t sm = tape_smem_bytes(tape);
+#ifdef RM_SPEC_INC
+    // specialised library: one code capacity, no culling variant; refuses any other tape
+    if (tape->n_instr > CODE_CAP_SMALL || tape_code_hash(tape) != RM_SPEC_HASH)
+        return fail(RM_ERR_INVALID, "rm_render: this library is specialised for another tape (hash %08x)",
+                    (unsigned)RM_SPEC_HASH);
+    {
+        constexpr int CAP = CODE_CAP_SMALL;
+        TapeCode<CAP> code;
+        expand_code(tape->code_host, tape->n_instr, code, false);
+        if (a->fast_math) {
+            if (int s = prepare_smem(render_kernel<true, CAP, false>, sm)) return s;
+            render_kernel<true, CAP, false><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+                code, tape->par, tape->n_instr, tape->n_par, poses, P);
+        } else {
+            if (int s = prepare_smem(render_kernel<false, CAP, false>, sm)) return s;
+            render_kernel<false, CAP, false><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+                code, tape->par, tape->n_instr, tape->n_par, poses, P);
+        }
+    }
+#else
     RM_WITH_CODE_EX(tape, a->fast_math >= 2, {
         if (a->fast_math >= 2) {
             if (int s = prepare_smem(render_kernel<true, CAP, true>, sm)) return s;
@@ -148,10 +171,12 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
         }
     });
+#endif  // RM_SPEC_INC
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }
 
+#ifndef RM_SPEC_INC
 extern "C" int rm_shade_finalize(const float* reduce, uint32_t mode_mask, int64_t n,
                                  float* const* image, float* rgba, int32_t display_mode, void* stream) {
     if (reduce == nullptr || n < 0) return fail(RM_ERR_INVALID, "rm_shade_finalize: null scratch");
@@ -167,3 +192,4 @@ extern "C" int rm_shade_finalize(const float* reduce, uint32_t mode_mask, int64_
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }
+#endif  // RM_SPEC_INC

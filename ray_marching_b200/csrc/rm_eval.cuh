@@ -52,6 +52,18 @@ struct NodeRecords {
     float y[CAP][K];           // per instruction: value a child of a smooth union fed into the blend
 };
 
+// Tape-specialised build (ray_marching_b200/specialise.py): the translation unit is compiled once
+// per scene STRUCTURE with RM_SPEC_INC naming a generated header that defines
+//     template <int K, bool FAST> eval_spec(spar, px, py, pz, out)
+// -- the straight-line sequence of exactly the statements the interpreter below executes for that
+// tape (same primitive bodies, same fold order, constant record offsets) -- and the non-recording
+// interpreter call sites use it instead of decoding.  Parameters still come from the staged block.
+#ifdef RM_SPEC_INC
+}  // namespace rm
+#include RM_SPEC_INC
+namespace rm {
+#endif
+
 // CULLMODE: 0 = the code carries no culling flags; 1 = flags present (a culling launch) but this
 // instance evaluates every child (IEEE stencil samples); 2 = cull.
 template <int K, bool FAST, int CAP, int CULLMODE = 0, bool RECORD = false>
@@ -61,6 +73,12 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
                                            float (&out)[K], float* hint = nullptr,
                                            const float* move = nullptr,
                                            NodeRecords<K, CAP>* rec = nullptr) {
+#ifdef RM_SPEC_INC
+    if constexpr (!RECORD && CULLMODE != 2) {
+        eval_spec<K, FAST>(spar, px, py, pz, out);
+        return;
+    }
+#endif
     using M = Math<FAST>;
     constexpr bool CULL = CULLMODE == 2;
     float seed[CULL ? K : 1];                        // lower bound of the culled union's largest term

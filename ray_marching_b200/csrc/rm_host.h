@@ -50,6 +50,15 @@ inline int check_tape(const RmTape* t) {
 inline size_t tape_smem_bytes(const RmTape* t) { return (size_t)t->n_par * 4; }
 
 // Runs BODY with `CAP` (constexpr) and `code` (TapeCode<CAP>, filled from the host block) in scope.
+// FNV-1a over the instruction words: identifies the scene structure a specialised library was
+// generated for (ray_marching_b200/specialise.py computes the same value).
+inline uint32_t tape_code_hash(const RmTape* t) {
+    uint32_t h = 2166136261u;
+    const unsigned char* b = reinterpret_cast<const unsigned char*>(t->code_host);
+    for (size_t i = 0; i < (size_t)t->n_instr * 8; ++i) { h ^= b[i]; h *= 16777619u; }
+    return h;
+}
+
 #define RM_WITH_CODE(tape, ...) RM_WITH_CODE_EX(tape, false, __VA_ARGS__)
 #define RM_WITH_CODE_EX(tape, with_cull, ...)                                            \
     do {                                                                                 \

@@ -210,8 +210,14 @@ def render(tape, cam: RmCamera, poses: Tensor, *, steps: int = 32, normals_eps: 
                          int(mode_mask), int(display_mode), int(degree), int(early_exit),
                          int(fast_math), ptr(cmap), 0.0)
         t = _tape_struct(tape.code_tensor(dev), par, tape.n_nodes, tape.max_depth)
-        check(lib().rm_render(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(o),
-                              stream_ptr(dev)), "rm_render")
+        # a tape-specialised library (specialise.py) exports rm_render with the same ABI
+        spec = getattr(tape, "spec_lib", None) if fast_math < 2 else None
+        status = (spec or lib()).rm_render(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(o),
+                                           stream_ptr(dev))
+        if status != 0 and spec is not None:
+            raise _lib.RmError(f"rm_render (specialised) failed with status {status}: "
+                               f"{spec.rm_last_error().decode(errors='replace')}")
+        check(status, "rm_render")
         res._keep = (par, poses, cmap)       # keep inputs alive until the stream has consumed them
         if finalize and (full_mask & NORMALISED_MODES):
             shade_finalize(res, mode_mask, display_mode)

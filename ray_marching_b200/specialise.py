@@ -1,0 +1,192 @@
+"""Tape-specialised render kernels: the scene STRUCTURE compiled into the kernel at scene-build time.
+
+The general path interprets the tape (csrc/rm_eval.cuh).  For small tapes the interpreter's control
+-- loop, dispatch chain, tail selection -- is ~40 % of the issued instructions (profiles/r01/
+variants.md).  This module emits, for one tape, the straight-line sequence of exactly the statements
+the interpreter would execute (the same hand-written primitive bodies of csrc/rm_prims.cuh, the same
+fold order, constant record offsets), and compiles the unchanged forward translation unit around it
+with nvcc for sm_100a into ``build/spec/librm_spec_<hash>.so``, which exports ``rm_render`` with the
+ABI of include/rm_b200.h.  Scene PARAMETERS stay run-time data (staged from ``par`` as before): an
+optimiser step never recompiles.  Structure hash = FNV-1a of the instruction words, checked by the
+library at every launch.
+
+Opt-in: ``RenderLoop.specialise()`` / :func:`specialised_lib`.  Without nvcc, or for tapes above
+``MAX_SPEC_INSTR``, callers keep the interpreter.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from typing import List, Optional
+
+import numpy as np
+
+from . import _lib, tape as T
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+SPEC_DIR = os.environ.get("RM_B200_SPEC_DIR", os.path.join(ROOT, "build", "spec"))
+MAX_SPEC_INSTR = 40          # straight-line code beyond this stops fitting the instruction cache
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+
+_PRIM_CALL = {
+    T.OP_SPHERE: "prim_sphere<FAST>(P[{p}], x, y, z)",
+    T.OP_BOX: "prim_box<FAST>(P[{p}], x, y, z)",
+    T.OP_TORUS: "prim_torus<FAST>(P[{p}], x, y, z)",
+    T.OP_DISK: "prim_disk<FAST>(P[{p}], x, y, z)",
+    T.OP_LINE: "prim_line<FAST>(P[{p}], P[{p1}], P[{p2}], x, y, z)",
+    T.OP_PLANE: "x",
+}
+_PRIM_F4 = {T.OP_SPHERE: 1, T.OP_BOX: 1, T.OP_PLANE: 0, T.OP_LINE: 3, T.OP_DISK: 1, T.OP_TORUS: 1}
+
+
+def code_hash(code: np.ndarray) -> int:
+    """FNV-1a over the instruction words (csrc/rm_host.h: tape_code_hash)."""
+    h = 2166136261
+    for b in np.ascontiguousarray(code, dtype=np.int32).tobytes():
+        h = ((h ^ b) * 16777619) & 0xFFFFFFFF
+    return h
+
+
+def generate_source(tape) -> str:
+    """The generated header: ``eval_spec<K, FAST>`` for this tape + its structure hash."""
+    out: List[str] = []
+    emit = out.append
+    stack: List[int] = []                       # ids of the open unions, innermost last
+    n_unions = 0
+
+    def fold_into_parent(fold: int):
+        if fold == T.FOLD_NONE:
+            return
+        u = stack[-1]
+        if fold == T.FOLD_MIN:
+            emit(f"    RM_FORK a0_{u}[k] = min_nan(a0_{u}[k], d[k]);")
+        else:
+            emit(f"    RM_FORK {{ const float x = c_{u} * d[k]; const float e = M::exp(-fabsf(x - a0_{u}[k]));")
+            emit(f"              a1_{u}[k] = (x > a0_{u}[k]) ? fmaf(a1_{u}[k], e, 1.f) : a1_{u}[k] + e;")
+            emit(f"              a0_{u}[k] = fmaxf(a0_{u}[k], x); }}")
+
+    def posts_of(kinds_, rec):
+        if not kinds_:
+            return
+        emit(f"    {{ const float4 pp = P[{rec}];")
+        for i, kind in enumerate(kinds_):
+            comp = "xyz"[i]
+            if kind == T.POST_ONION:
+                emit(f"      RM_FORK d[k] = fabsf(d[k]) - pp.{comp};")
+            else:
+                emit(f"      RM_FORK d[k] = d[k] - pp.{comp};")
+        emit("    }")
+
+    for w0, w1 in np.asarray(tape.code).tolist():
+        op, frame, fold, root, posts, ordinal, off, node, cull = T.decode(w0, w1)
+        if op in (T.OP_OPEN_MIN, T.OP_OPEN_SMOOTH):
+            u = n_unions
+            n_unions += 1
+            stack.append(u)
+            if op == T.OP_OPEN_MIN:
+                emit(f"    float a0_{u}[K]; RM_FORK a0_{u}[k] = CUDART_INF_F;")
+            else:
+                emit(f"    const float c_{u} = M::exp_scale(P[{off}].x);")
+                emit(f"    float a0_{u}[K], a1_{u}[K]; RM_FORK {{ a0_{u}[k] = -CUDART_INF_F; a1_{u}[k] = 0.f; }}")
+            continue
+        if op in (T.OP_CLOSE_MIN, T.OP_CLOSE_SMOOTH):
+            u = stack.pop()
+            if op == T.OP_CLOSE_MIN:
+                emit(f"    RM_FORK d[k] = a0_{u}[k];")
+            else:
+                emit(f"    RM_FORK d[k] = M::div(a0_{u}[k] + M::log(a1_{u}[k]), c_{u});")
+            posts_of(posts, off)
+            fold_into_parent(fold)
+            continue
+        # leaf
+        prim = off + (3 if frame else 0)
+        call = _PRIM_CALL[op].format(p=prim, p1=prim + 1, p2=prim + 2)
+        if frame:
+            emit(f"    {{ const float4 r0 = P[{off}], r1 = P[{off + 1}], r2 = P[{off + 2}];")
+            emit("      RM_FORK { const float x = fmaf(r0.x, px[k], fmaf(r0.y, py[k], fmaf(r0.z, pz[k], r0.w)));")
+            emit("                const float y = fmaf(r1.x, px[k], fmaf(r1.y, py[k], fmaf(r1.z, pz[k], r1.w)));")
+            emit("                const float z = fmaf(r2.x, px[k], fmaf(r2.y, py[k], fmaf(r2.z, pz[k], r2.w)));")
+            emit(f"                (void)y; (void)z; d[k] = {call}; }} }}")
+        else:
+            emit("    RM_FORK { const float x = px[k], y = py[k], z = pz[k]; (void)y; (void)z;")
+            emit(f"              d[k] = {call}; }}")
+        posts_of(posts, prim + _PRIM_F4[op])
+        fold_into_parent(fold)
+    assert not stack, "unbalanced tape"
+    body = "\n".join(out)
+    return f"""// GENERATED by ray_marching_b200/specialise.py for {tape.describe()}
+// Straight-line form of the tape: the statements csrc/rm_eval.cuh executes for it, in order.
+#pragma once
+#define RM_SPEC_HASH 0x{code_hash(tape.code):08x}u
+#define RM_FORK _Pragma("unroll") for (int k = 0; k < K; ++k)
+namespace rm {{
+template <int K, bool FAST>
+__device__ __forceinline__ void eval_spec(const float4* __restrict__ P, const float (&px)[K],
+                                          const float (&py)[K], const float (&pz)[K], float (&out)[K]) {{
+    using M = Math<FAST>;
+    float d[K];
+    RM_FORK d[k] = 0.f;
+{body}
+    RM_FORK out[k] = d[k];
+}}
+}}  // namespace rm
+#undef RM_FORK
+"""
+
+
+def spec_paths(tape):
+    h = code_hash(tape.code)
+    return os.path.join(SPEC_DIR, f"rm_spec_{h:08x}.inc"), os.path.join(SPEC_DIR, f"librm_spec_{h:08x}.so")
+
+
+def build(tape, force: bool = False) -> str:
+    """Generates and compiles the specialised library of ``tape`` (cached by structure hash)."""
+    if tape.n_instr > MAX_SPEC_INSTR:
+        raise ValueError(f"tape has {tape.n_instr} instructions; specialisation is for <= {MAX_SPEC_INSTR}")
+    inc, lib = spec_paths(tape)
+    src = generate_source(tape)
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))]
+    deps.append(os.path.join(ROOT, "include", "rm_b200.h"))
+    fresh = (os.path.exists(lib) and os.path.exists(inc) and open(inc).read() == src
+             and os.path.getmtime(lib) >= max(os.path.getmtime(p) for p in deps))
+    if fresh and not force:
+        return lib
+    if not os.path.exists(NVCC):
+        raise RuntimeError(f"nvcc not found at {NVCC}: cannot specialise (the interpreter path is unaffected)")
+    os.makedirs(SPEC_DIR, exist_ok=True)
+    with open(inc, "w") as f:
+        f.write(src)
+    tmp = lib + f".tmp{os.getpid()}"
+    cmd = [NVCC, "-shared", "-o", tmp, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo",
+           "-std=c++17", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", f'-DRM_SPEC_INC="{inc}"',
+           os.path.join(CSRC, "rm_host.cu"), os.path.join(CSRC, "rm_forward.cu")]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed for the specialised library:\n" + res.stdout + res.stderr)
+    os.replace(tmp, lib)
+    return lib
+
+
+_loaded = {}
+
+
+def specialised_lib(tape, build_if_missing: bool = True) -> Optional[C.CDLL]:
+    """ctypes handle of the library specialised for ``tape`` (its ``rm_render`` has the signature
+    of the general one), or None when it does not exist and may not be built."""
+    inc, path = spec_paths(tape)
+    if path in _loaded:
+        return _loaded[path]
+    if build_if_missing:
+        path = build(tape)
+    elif not (os.path.exists(path) and os.path.exists(inc) and open(inc).read() == generate_source(tape)):
+        return None
+    handle = C.CDLL(path)
+    handle.rm_render.restype, handle.rm_render.argtypes = _lib._SIGNATURES["rm_render"]
+    handle.rm_last_error.restype = C.c_char_p
+    if handle.rm_abi_version() != _lib.ABI_VERSION:
+        raise RuntimeError(f"{path}: ABI version mismatch; rebuild")
+    _loaded[path] = handle
+    return handle

@@ -156,6 +156,7 @@ class Tape:
         self._finalise_recipe()
         self._dev_cache = {}
         self._par_cache = None
+        self.spec_lib = None       # ctypes handle of a tape-specialised library (specialise.py), opt-in
         self._code_host = None
 
     # ------------------------------------------------------------------ tree walk

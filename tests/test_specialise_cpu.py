@@ -1,0 +1,54 @@
+"""specialise.py on the CPU side: the generated straight-line source mirrors the tape, the structure
+hash is stable, and (nvcc present) the specialised translation unit compiles for sm_100a."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+from ray_marching_b200 import scene as S, specialise as SP
+from ray_marching_b200.scene.scene_registry import make_test_scene, make_test_scene2
+from ray_marching_b200.scene.synthetic import make_synthetic_scene
+from ray_marching_b200.tape import tape_of
+
+
+def nested_scene():
+    """Two sibling unions (smooth with a rounded onion-layered box, hard) under a hard root with a
+    rounded close: every generator branch (frames, post-op chains, nested folds)."""
+    a = S.SDFSmoothUnion([S.SDFAffineTransformation(S.SDFSphere(0.3), (0.9, 0.1, 0.2, 0.3), (0.2, 0.0, 0.1)),
+                          S.SDFRounding(S.SDFOnion(S.SDFBox((0.2, 0.1, 0.3)), 0.05), 0.01),
+                          S.SDFAffineTransformation(S.SDFPlane(), (1.0, 0.0, 0.0, 0.0), (-2.0, 0.0, 0.0))], blend_k=9.0)
+    b = S.SDFOnion(S.SDFSmoothUnion([S.SDFTorus(0.4, 0.1), S.SDFDisk(0.3),
+                                     S.SDFLine((-0.2, 0.1, 0.0), (0.3, 0.2, 0.1), 0.05)], blend_k=15.0), 0.02)
+    return S.SDFRounding(S.SDFUnion([a, b, S.SDFSphere(0.1)]), 0.005)
+
+
+def test_generated_source_mirrors_the_tape():
+    t = tape_of(make_test_scene2())
+    src = SP.generate_source(t)
+    assert f"0x{SP.code_hash(t.code):08x}u" in src
+    for prim in ("prim_box<FAST>(P[0]", "prim_sphere<FAST>(P[2]", "prim_torus<FAST>(P[3]",
+                 "prim_line<FAST>(P[4], P[5], P[6]"):
+        assert prim in src
+    assert src.count("min_nan") == 4 and "fabsf(d[k]) - pp.x" in src          # 4 children, one onion
+    t2 = tape_of(nested_scene())
+    src2 = SP.generate_source(t2)
+    assert len(re.findall(r"M::exp_scale", src2)) == 2 and src2.count("CUDART_INF_F;") >= 1
+    assert SP.code_hash(t2.code) != SP.code_hash(t.code)
+    assert SP.code_hash(tape_of(make_test_scene2()).code) == SP.code_hash(t.code)   # structure only
+
+
+def test_large_tapes_are_refused():
+    with pytest.raises(ValueError):
+        SP.build(tape_of(make_synthetic_scene(64)))
+
+
+@pytest.mark.skipif(not os.path.exists(SP.NVCC), reason="nvcc not available")
+def test_specialised_translation_unit_compiles(tmp_path, monkeypatch):
+    monkeypatch.setattr(SP, "SPEC_DIR", str(tmp_path))
+    lib = SP.build(tape_of(nested_scene()))
+    assert os.path.exists(lib)
+    out = os.popen(f"nm -D --defined-only {lib}").read()
+    assert " rm_render" in out and " rm_abi_version" in out and " rm_last_error" in out
+    assert " rm_march" not in out and " rm_sdf_eval" not in out          # rm_render only
+    assert SP.build(tape_of(nested_scene())) == lib                          # cached
