@@ -5,6 +5,28 @@ namespace rm {
 
 inline unsigned grid_for(int64_t n) { return (unsigned)((n + (int64_t)BLOCK * K - 1) / ((int64_t)BLOCK * K)); }
 
+
+// rm_render: persistent grid -- at most (SMs x resident blocks per SM) blocks, each walking a
+// contiguous range of warp tiles (render_kernel); never more blocks than tiles.
+inline unsigned render_grid(int64_t n) {
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0, v = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess &&
+            cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && v > 0)
+            sms = v;
+        else
+            sms = 148;
+    }
+#if RM_PERSIST
+    const int64_t tiles = (n + 32 * K - 1) / (32 * K);
+    const int64_t cap = (int64_t)sms * RM_MINB;
+    return (unsigned)(tiles < cap ? tiles : cap);
+#else
+    return grid_for(n);
+#endif
+}
+
 }  // namespace rm
 
 using namespace rm;
@@ -135,6 +157,12 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
     P.hit_tau = a->hit_tau; P.lift_delta = a->lift_delta; P.mode_mask = a->mode_mask;
     P.display_mode = a->display_mode; P.degree = a->degree; P.early_exit = a->early_exit;
     P.cmap = a->cmap; P.out = *out;
+    {
+        const int64_t tiles = (a->n_rays + 32 * K - 1) / (32 * K);
+        if (tiles > 0x7fffffff) return fail(RM_ERR_INVALID, "rm_render: ray range too large for one launch");
+        const unsigned g = render_grid(a->n_rays);
+        P.tile_base = (int)(tiles / g); P.tile_rem = (int)(tiles % g);
+    }
     const size_t sm = tape_smem_bytes(tape);
 #ifdef RM_SPEC_INC
     // specialised library: one code capacity, no culling variant; refuses any other tape
@@ -147,11 +175,11 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
         expand_code(tape->code_host, tape->n_instr, code, false);
         if (a->fast_math) {
             if (int s = prepare_smem(render_kernel<true, CAP, false>, sm)) return s;
-            render_kernel<true, CAP, false><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+            render_kernel<true, CAP, false><<<render_grid(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
         } else {
             if (int s = prepare_smem(render_kernel<false, CAP, false>, sm)) return s;
-            render_kernel<false, CAP, false><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+            render_kernel<false, CAP, false><<<render_grid(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
         }
     }
@@ -159,15 +187,15 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
     RM_WITH_CODE_EX(tape, a->fast_math >= 2, {
         if (a->fast_math >= 2) {
             if (int s = prepare_smem(render_kernel<true, CAP, true>, sm)) return s;
-            render_kernel<true, CAP, true><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+            render_kernel<true, CAP, true><<<render_grid(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
         } else if (a->fast_math) {
             if (int s = prepare_smem(render_kernel<true, CAP, false>, sm)) return s;
-            render_kernel<true, CAP, false><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+            render_kernel<true, CAP, false><<<render_grid(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
         } else {
             if (int s = prepare_smem(render_kernel<false, CAP, false>, sm)) return s;
-            render_kernel<false, CAP, false><<<grid_for(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+            render_kernel<false, CAP, false><<<render_grid(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
         }
     });

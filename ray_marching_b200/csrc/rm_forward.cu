@@ -29,6 +29,10 @@
 #define RM_MINB 4
 #endif
 
+#ifndef RM_PERSIST
+#define RM_PERSIST 0            // 1: persistent balanced tiling in render_kernel (measured slower: profiles/r01/variants.md)
+#endif
+
 namespace rm {
 
 constexpr int K = RM_K;         // rays per thread (multiple of 4: float4 plane I/O)
@@ -127,14 +131,19 @@ sdf_eval_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, in
 __device__ __forceinline__ void make_rays(const CamParams& cam, const float* poses, int64_t ray0,
                                           float (&ox)[K], float (&oy)[K], float (&oz)[K],
                                           float (&vx)[K], float (&vy)[K], float (&vz)[K]) {
-    int cur_view = -1;
-    Pose pose;
+    PixelCursor c = pixel_cursor(cam, ray0);
+    int cur_view = c.view;
+    Pose pose = load_pose(poses, c.view);
 #pragma unroll
     for (int k = 0; k < K; ++k) {
         float ob[3], vb[3], ow[3], vw[3];
-        world_ray(cam, poses, ray0 + k, pose, cur_view, ob, vb, ow, vw);
-        ox[k] = ow[0]; oy[k] = ow[1]; oz[k] = ow[2];
+        if (c.view != cur_view) { pose = load_pose(poses, c.view); cur_view = c.view; }
+        base_ray(cam, c.row, c.col, ob, vb);
+        mat_apply(pose.R, ob, ow);
+        mat_apply(pose.R, vb, vw);
+        ox[k] = ow[0] + pose.t[0]; oy[k] = ow[1] + pose.t[1]; oz[k] = ow[2] + pose.t[2];
         vx[k] = vw[0]; vy[k] = vw[1]; vz[k] = vw[2];
+        pixel_next(cam, c);
     }
 }
 
@@ -199,6 +208,24 @@ __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_inst
     float hint[CULL ? K : 1], move[CULL ? K : 1];
 #pragma unroll
     for (int k = 0; k < (CULL ? K : 1); ++k) { hint[k] = CUDART_INF_F; move[k] = 0.f; }
+#ifdef RM_SPEC_INC
+    // Tape-specialised build: the evaluation is a few dozen straight-line instructions, so the
+    // fixed-point test below (12 compares, the old/new register rotation, a vote) would be ~15 % of
+    // the loop even when predicated off.  Launches without early exit take this loop instead.
+    if (!CULL && !early_exit) {
+#pragma unroll 2
+        for (int s = 0; s < steps; ++s) {
+            eval_scene<K, FAST, CAP, 0>(code, n_instr, spar, px, py, pz, d);
+#pragma unroll
+            for (int k = 0; k < K; ++k) {
+                px[k] = fmaf(d[k], vx[k], px[k]);
+                py[k] = fmaf(d[k], vy[k], py[k]);
+                pz[k] = fmaf(d[k], vz[k], pz[k]);
+            }
+        }
+        return;
+    }
+#endif
     for (int s = 0; s < steps; ++s) {                 // one interpreter instance (instruction cache)
         eval_scene<K, FAST, CAP, CULL ? 2 : 0>(code, n_instr, spar, px, py, pz, d, hint, move);
         bool moved = false;

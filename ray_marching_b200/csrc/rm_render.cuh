@@ -13,6 +13,7 @@ struct RenderParams {
     float hit_tau, lift_delta;
     unsigned mode_mask;
     int display_mode, degree, early_exit;
+    int tile_base, tile_rem;           // persistent tiling: see render_kernel
     const float* cmap;
     RmRenderOut out;
 };
@@ -72,21 +73,44 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
     __shared__ float red[BLOCK / 32][3];
     const float4* spar = stage_params(par, n_par, smem);
     const int64_t n = P.n_rays;
-    const int64_t first = ((int64_t)blockIdx.x * BLOCK + threadIdx.x) * K;
+    // Persistent, balanced tiling.  A tile = the 32 K consecutive rays one warp owns.  The host
+    // launches at most (SMs x resident blocks) blocks; block b takes the contiguous tile range
+    // [T b / G, T (b + 1) / G) and its warps stride through it, so every SM sub-partition ends up
+    // within one tile of the mean (c2: 16 200 tiles over 592 sub-partitions = 27.4 each, where
+    // 2 025 one-shot blocks over 592 block slots ran 4 waves for 3.4 waves of work).  The warp
+    // index comes from a warp reduction so that ptxas knows the trip count is warp-uniform.
     // No thread-dependent control flow around the march: every thread marches K rays (tail threads
     // march clamped duplicates that are never stored), so the interpreter's decode stays on the
     // uniform datapath and all threads reach the block reductions below.
+    constexpr int WARPS = BLOCK / 32;
+    const int lane = threadIdx.x & 31;
+    const int warp = (int)(__reduce_min_sync(0xffffffffu, threadIdx.x) >> 5);   // REDUX: lands in a uniform register
+    // tiles = tile_base * gridDim.x + tile_rem (host): the first tile_rem blocks take one more.  No
+    // division here -- a divide is a subroutine call whose result ptxas treats as thread-dependent,
+    // which would push everything inside the tile loop off the uniform datapath.
+    const int bx = (int)blockIdx.x;
+    const int t0 = bx * P.tile_base + min(bx, P.tile_rem);
+    const int t1 = t0 + P.tile_base + (bx < P.tile_rem ? 1 : 0);
+    // co-resident blocks start their round-robin on different sub-partitions
+    const int rot = (int)(blockIdx.x + blockIdx.x / 148u);
     const unsigned mask = P.mode_mask | (P.display_mode >= 0 ? (1u << P.display_mode) : 0u);
     const bool need_stencil =
         (mask & (RM_MODE_LAMBERTIAN | RM_MODE_NORMAL | RM_MODE_LAPLACIAN | RM_MODE_TANGENT |
                  RM_MODE_SPIN)) || P.out.normals || P.out.laplacian || P.bounces > 0;
 
-    float ox[K], oy[K], oz[K], vx[K], vy[K], vz[K];
-    float px[K], py[K], pz[K], f[K], nx[K], ny[K], nz[K], lap[K];
     MinMax mm_dist, mm_prox, mm_lap;
     mm_dist.init(); mm_prox.init(); mm_lap.init();
 
-    {
+#if RM_PERSIST
+    for (int t = t0 + ((warp + rot) & (WARPS - 1)); t < t1; t += WARPS) {
+#else
+    {   // one tile per warp (the host launches ceil(tiles / WARPS) blocks)
+        const int t = (int)blockIdx.x * WARPS + (int)(threadIdx.x >> 5);
+        (void)warp; (void)t0; (void)t1; (void)rot;
+#endif
+        const int64_t first = ((int64_t)t * 32 + lane) * K;
+        float ox[K], oy[K], oz[K], vx[K], vy[K], vz[K];
+        float px[K], py[K], pz[K], f[K], nx[K], ny[K], nz[K], lap[K];
         make_rays(P.cam, poses, P.ray_begin + first, ox, oy, oz, vx, vy, vz);
         store3(P.out.origin, first, n, ox, oy, oz);
 #pragma unroll
@@ -118,7 +142,6 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
         store1(P.out.laplacian, first, n, lap);
 
         // ---- per-pixel shaders (rendering/shader.py); pixel position = ray origin ----
-        const int64_t per_view = (int64_t)P.cam.width * P.cam.height;
         float img[K], rgb0[K], rgb1[K], rgb2[K];
         const int dm = P.display_mode;
         float dr[K], dg[K], db[K];
@@ -154,12 +177,14 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
             if (P.mode_mask & RM_MODE_PROXIMITY) store1(P.out.image[2], first, n, img);
         }
         if (mask & (RM_MODE_VIGNETTE | RM_MODE_TANGENT | RM_MODE_SPIN)) {
+            // the camera pose of each ray's view (one divide per thread, as in make_rays)
+            PixelCursor cur = pixel_cursor(P.cam, P.ray_begin + first);
+            int pose_view = cur.view;
+            Pose pose = load_pose(poses, cur.view);
 #pragma unroll
             for (int k = 0; k < K; ++k) {
-                int64_t r = P.ray_begin + first + k;
-                const int64_t total = per_view * P.cam.n_views;
-                if (r >= total) r = total - 1;
-                const Pose pose = load_pose(poses, (int)(r / per_view));
+                if (cur.view != pose_view) { pose = load_pose(poses, cur.view); pose_view = cur.view; }
+                pixel_next(P.cam, cur);
                 const float v3[3] = {vx[k], vy[k], vz[k]}, n3[3] = {nx[k], ny[k], nz[k]};
                 if (mask & RM_MODE_VIGNETTE) {
                     img[k] = shade_vignette(v3, pose.fwd);
@@ -175,12 +200,13 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
             if (P.mode_mask & RM_MODE_VIGNETTE) store1(P.out.image[3], first, n, img);
             if (P.mode_mask & RM_MODE_TANGENT) store3(P.out.image[6], first, n, rgb0, rgb1, rgb2);
             if (mask & RM_MODE_SPIN) {
+                cur = pixel_cursor(P.cam, P.ray_begin + first);
+                pose_view = cur.view;
+                pose = load_pose(poses, cur.view);
 #pragma unroll
                 for (int k = 0; k < K; ++k) {
-                    int64_t r = P.ray_begin + first + k;
-                    const int64_t total = per_view * P.cam.n_views;
-                    if (r >= total) r = total - 1;
-                    const Pose pose = load_pose(poses, (int)(r / per_view));
+                    if (cur.view != pose_view) { pose = load_pose(poses, cur.view); pose_view = cur.view; }
+                    pixel_next(P.cam, cur);
                     const float n3[3] = {nx[k], ny[k], nz[k]};
                     float c3[3];
                     shade_spin(pose, n3, P.cmap, P.degree, c3);

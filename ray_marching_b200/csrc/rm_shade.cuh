@@ -52,10 +52,42 @@ __device__ __forceinline__ void base_ray(const CamParams& c, int row, int col, f
     o[0] = c.half_w * gx;
     o[1] = c.neg_half_h * gy;
     o[2] = 0.f;
-    const float n = __fsqrt_rn(o[0] * o[0] + o[1] * o[1] + c.focal * c.focal);
-    v[0] = __fdiv_rn(o[0], n);
-    v[1] = __fdiv_rn(o[1], n);
-    v[2] = __fdiv_rn(c.focal, n);
+    // correctly rounded, branch-free (rm_math.cuh): n >= focal > 0 is far inside the in-range window
+    const float n = sqrt_rn_inline(o[0] * o[0] + o[1] * o[1] + c.focal * c.focal);
+    v[0] = div_rn_inline(o[0], n);
+    v[1] = div_rn_inline(o[1], n);
+    v[2] = div_rn_inline(c.focal, n);
+}
+
+// (view, row, col) of a global ray index, clamped to the batch (tail lanes recompute the last ray).
+// One divide per THREAD: consecutive rays advance the cursor with compares.  Batches below 2^31
+// rays take 32-bit divides (inline); the 64-bit divide is a subroutine call.
+struct PixelCursor { int view, row, col; };
+__device__ __forceinline__ PixelCursor pixel_cursor(const CamParams& cam, int64_t r) {
+    const int64_t per_view = (int64_t)cam.width * cam.height;
+    const int64_t total = per_view * cam.n_views;
+    if (r >= total) r = total - 1;
+    PixelCursor c;
+    if (total <= 0x7fffffffLL) {
+        const unsigned ru = (unsigned)r, pv = (unsigned)per_view;
+        c.view = (int)(ru / pv);
+        const unsigned pix = ru - (unsigned)c.view * pv;
+        c.row = (int)(pix / (unsigned)cam.width);
+        c.col = (int)(pix - (unsigned)c.row * (unsigned)cam.width);
+    } else {
+        c.view = (int)(r / per_view);
+        const int pix = (int)(r - (int64_t)c.view * per_view);
+        c.row = pix / cam.width;
+        c.col = pix - c.row * cam.width;
+    }
+    return c;
+}
+__device__ __forceinline__ void pixel_next(const CamParams& cam, PixelCursor& c) {
+    if (++c.col == cam.width) {
+        c.col = 0;
+        if (++c.row == cam.height) { c.row = 0; ++c.view; }
+    }
+    if (c.view >= cam.n_views) { c.view = cam.n_views - 1; c.row = cam.height - 1; c.col = cam.width - 1; }
 }
 
 __device__ __forceinline__ void mat_apply(const float (&R)[9], const float (&x)[3], float (&y)[3]) {
@@ -75,14 +107,9 @@ __device__ __forceinline__ void mat_apply_t(const float (&R)[9], const float (&x
 __device__ __forceinline__ void world_ray(const CamParams& cam, const float* poses, int64_t r,
                                           Pose& pose, int& cur_view, float (&ob)[3], float (&vb)[3],
                                           float (&ow)[3], float (&vw)[3]) {
-    const int64_t per_view = (int64_t)cam.width * cam.height;
-    const int64_t total = per_view * cam.n_views;
-    if (r >= total) r = total - 1;                     // tail lanes recompute the last ray
-    const int view = (int)(r / per_view);
-    const int pix = (int)(r - (int64_t)view * per_view);
-    const int row = pix / cam.width, col = pix - row * cam.width;
-    if (view != cur_view) { pose = load_pose(poses, view); cur_view = view; }
-    base_ray(cam, row, col, ob, vb);
+    const PixelCursor c = pixel_cursor(cam, r);        // tail lanes recompute the last ray
+    if (c.view != cur_view) { pose = load_pose(poses, c.view); cur_view = c.view; }
+    base_ray(cam, c.row, c.col, ob, vb);
     mat_apply(pose.R, ob, ow);
     mat_apply(pose.R, vb, vw);
     ow[0] += pose.t[0]; ow[1] += pose.t[1]; ow[2] += pose.t[2];

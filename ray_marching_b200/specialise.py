@@ -27,7 +27,7 @@ from . import _lib, tape as T
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
-SPEC_DIR = os.environ.get("RM_B200_SPEC_DIR", os.path.join(ROOT, "build", "spec"))
+SPEC_DIR = os.path.abspath(os.environ.get("RM_B200_SPEC_DIR", os.path.join(ROOT, "build", "spec")))
 MAX_SPEC_INSTR = 40          # straight-line code beyond this stops fitting the instruction cache
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
@@ -57,10 +57,22 @@ def generate_source(tape) -> str:
     stack: List[int] = []                       # ids of the open unions, innermost last
     n_unions = 0
 
+    folded = {}                                 # union id -> children folded so far
+
     def fold_into_parent(fold: int):
         if fold == T.FOLD_NONE:
             return
         u = stack[-1]
+        first = folded.get(u, 0) == 0
+        folded[u] = folded.get(u, 0) + 1
+        if first:
+            # first child: min(+inf, d) = d, resp. the online log-sum-exp started at (x, 1) -- what
+            # the general statements below give from the initial (-inf, 0) for every finite x
+            if fold == T.FOLD_MIN:
+                emit(f"    RM_FORK a0_{u}[k] = d[k];")
+            else:
+                emit(f"    RM_FORK {{ a0_{u}[k] = c_{u} * d[k]; a1_{u}[k] = 1.f; }}")
+            return
         if fold == T.FOLD_MIN:
             emit(f"    RM_FORK a0_{u}[k] = min_nan(a0_{u}[k], d[k]);")
         else:
@@ -87,13 +99,15 @@ def generate_source(tape) -> str:
             n_unions += 1
             stack.append(u)
             if op == T.OP_OPEN_MIN:
-                emit(f"    float a0_{u}[K]; RM_FORK a0_{u}[k] = CUDART_INF_F;")
+                emit(f"    float a0_{u}[K];")
             else:
                 emit(f"    const float c_{u} = M::exp_scale(P[{off}].x);")
-                emit(f"    float a0_{u}[K], a1_{u}[K]; RM_FORK {{ a0_{u}[k] = -CUDART_INF_F; a1_{u}[k] = 0.f; }}")
+                emit(f"    float a0_{u}[K], a1_{u}[K];")
             continue
         if op in (T.OP_CLOSE_MIN, T.OP_CLOSE_SMOOTH):
             u = stack.pop()
+            if not folded.get(u):
+                raise ValueError("union without children cannot be specialised")
             if op == T.OP_CLOSE_MIN:
                 emit(f"    RM_FORK d[k] = a0_{u}[k];")
             else:
@@ -162,6 +176,7 @@ def build(tape, force: bool = False) -> str:
     tmp = lib + f".tmp{os.getpid()}"
     cmd = [NVCC, "-shared", "-o", tmp, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo",
            "-std=c++17", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", f'-DRM_SPEC_INC="{inc}"',
+           *os.environ.get("RM_B200_SPEC_FLAGS", "").split(),      # launch-shape experiments
            os.path.join(CSRC, "rm_host.cu"), os.path.join(CSRC, "rm_forward.cu")]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:

@@ -30,10 +30,13 @@ def test_generated_source_mirrors_the_tape():
     for prim in ("prim_box<FAST>(P[0]", "prim_sphere<FAST>(P[2]", "prim_torus<FAST>(P[3]",
                  "prim_line<FAST>(P[4], P[5], P[6]"):
         assert prim in src
-    assert src.count("min_nan") == 4 and "fabsf(d[k]) - pp.x" in src          # 4 children, one onion
+    # 4 children, the first one assigned (min(+inf, d) = d), one onion
+    assert src.count("min_nan") == 3 and "a0_0[k] = d[k];" in src and "fabsf(d[k]) - pp.x" in src
     t2 = tape_of(nested_scene())
     src2 = SP.generate_source(t2)
-    assert len(re.findall(r"M::exp_scale", src2)) == 2 and src2.count("CUDART_INF_F;") >= 1
+    assert len(re.findall(r"M::exp_scale", src2)) == 2
+    assert src2.count("a1_1[k] = 1.f;") == 1 and src2.count("a1_2[k] = 1.f;") == 1   # log-sum-exp starts at (x, 1)
+    assert "CUDART_INF_F" not in src2                                           # no accumulator is initialised
     assert SP.code_hash(t2.code) != SP.code_hash(t.code)
     assert SP.code_hash(tape_of(make_test_scene2()).code) == SP.code_hash(t.code)   # structure only
 
