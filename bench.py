@@ -214,8 +214,21 @@ def run_gpu(args):
         res_holder["res"] = frame(q, t, res_holder.get("res"))
         return res_holder["res"]
 
+    # small tapes: the tape-specialised kernel (nvcc at scene-build time, cached in build/spec/);
+    # any failure (no nvcc on the box) leaves the interpreter in place and says so
+    spec_on, spec_note = False, "interpreter"
+    if args.specialise == "on" and not args.cull:       # forward AND backward kernels (c1, c2, c4)
+        from ray_marching_b200 import specialise as SPEC
+        if tape.n_instr <= SPEC.MAX_SPEC_INSTR:
+            try:
+                loop.specialise(True)
+                spec_on, spec_note = True, "tape-specialised (RenderLoop.specialise())"
+            except Exception as exc:
+                spec_note = f"interpreter (specialisation unavailable: {str(exc)[:120]})"
+
     if wl["backward"]:
-        gpu_step, extra = make_backward_step(loop, scene, q, t, dev, world, wl["name"])
+        gpu_step, extra = make_backward_step(loop, scene, q, t, dev, world, wl["name"],
+                                             graph=bool(args.graph) and tape.n_instr <= 40)
     launches_per_step = (3 if needs_reduce else 1) if not wl["backward"] else extra["launches"]
 
     flush = torch.empty(192 * 1024 * 1024 // 4, device=dev)      # 192 MB > 126 MB L2
@@ -224,18 +237,6 @@ def run_gpu(args):
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-
-    # small tapes: the tape-specialised kernel (nvcc at scene-build time, cached in build/spec/);
-    # any failure (no nvcc on the box) leaves the interpreter in place and says so
-    spec_on, spec_note = False, "interpreter"
-    if not wl["backward"] and args.specialise == "on" and not args.cull:
-        from ray_marching_b200 import specialise as SPEC
-        if tape.n_instr <= SPEC.MAX_SPEC_INSTR:
-            try:
-                loop.specialise(True)
-                spec_on, spec_note = True, "tape-specialised (RenderLoop.specialise())"
-            except Exception as exc:
-                spec_note = f"interpreter (specialisation unavailable: {str(exc)[:120]})"
 
     peak = measure_fp32_peak(dev)
     for _ in range(max(args.warmup, 3)):
@@ -308,21 +309,25 @@ def run_gpu(args):
     interp_info = None
     if spec_on:
         loop.specialise(False)
+        # backward workloads: the headline step may be a captured graph (which keeps the kernels it was
+        # captured with), so the interpreter comparison runs the eager step
+        x_step = extra["eager_step"] if wl["backward"] else gpu_step
         for _ in range(3):
-            gpu_step()
+            x_step()
         torch.cuda.synchronize()
         xs = []
         for _ in range(max(3, min(args.steps, 20))):
             flush.zero_()
             xe0, xe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             xe0.record()
-            gpu_step()
+            x_step()
             xe1.record()
             xe1.synchronize()
             xs.append(xe0.elapsed_time(xe1))
         x_ms = sum(xs) / len(xs)
         interp_info = {"ms_per_step": x_ms, "value": rays / (x_ms * 1e-3) / 1e6, "unit": "Mrays/s",
-                       "frac_of_fp32_peak_whole_step": fpr * rays / (x_ms * 1e-3) / 1e12 / peak["tflops"],
+                       "frac_of_fp32_peak_whole_step": (None if wl["backward"] else
+                                                        fpr * rays / (x_ms * 1e-3) / 1e12 / peak["tflops"]),
                        "note": "per-GPU, same frame through the general tape interpreter (the default of "
                                "RenderLoop; the headline uses RenderLoop.specialise())"}
         loop.specialise(True)
@@ -381,6 +386,7 @@ def run_gpu(args):
                        "l2": "flushed between timed iterations (192 MB memset, untimed)",
                        "early_exit": bool(args.early_exit), "cull": bool(args.cull), "tape": tape.describe(),
                        "render_kernel": spec_note,
+                       **({"step": extra["note"]()} if wl["backward"] else {}),
                        "msteps_per_s": value * STEPS * (wl["bounces"] + 1),
                        "wall_s_timed_region": wall},
             "e2e": {"value": rays * world / (e2e_ms / args.steps * 1e-3) / 1e6, "unit": "Mrays/s",
@@ -477,7 +483,7 @@ def ncu_traffic(kernel: str, workload: str):
     return (total, os.path.relpath(files[-1], ROOT)) if seen == 2 else (None, None)
 
 
-def make_backward_step(loop, scene, q, t, dev, world, wl_name="c4"):
+def make_backward_step(loop, scene, q, t, dev, world, wl_name="c4", graph=True):
     """c4: one Adam step of inverse rendering -- forward (camera, march, stencil, lambertian + raw
     depth), MSE loss against a target rendered from perturbed parameters, backward through the
     replay kernels, all-reduce of the flat gradient over ranks (one view per rank), Adam update."""
@@ -504,18 +510,38 @@ def make_backward_step(loop, scene, q, t, dev, world, wl_name="c4"):
     with torch.no_grad():
         for p, s0 in zip(params, saved):
             p.copy_(s0)
-    opt = torch.optim.Adam(params + [q, t], lr=1e-2, foreach=True)
-    state = {}
+    opt = torch.optim.Adam(params + [q, t], lr=1e-2, foreach=True, capturable=True)
+    state = {"graph": None, "graph_note": "eager launches"}
 
-    def step():
-        opt.zero_grad(set_to_none=True)
+    def body():
         lam, depth, rays = gbuf()
         loss = ((lam - lam_t) ** 2).mean() + ((depth - depth_t) ** 2).mean()
         loss.backward()
         if world > 1:          # one NCCL SUM over the flat gradient buffer (scene params + q, t)
             parallel.allreduce_gradients(params + [q, t], average=True)
         opt.step()
-        state["loss"], state["rays"] = loss, rays
+        return loss
+
+    def eager_step():
+        opt.zero_grad(set_to_none=True)
+        return body()
+
+    # the whole step as ONE CUDA-graph replay (frames.GraphedStep) when the kernels are short enough
+    # for launch overhead to matter (registry scenes); single GPU only: the NCCL all-reduce of the
+    # sharded job stays an eager launch
+    if graph and world == 1:
+        try:
+            from ray_marching_b200.frames import GraphedStep
+            state["graph"] = GraphedStep(body, opt)
+            state["graph_note"] = "whole step (forward, loss, backward, Adam) = one CUDA-graph replay"
+        except Exception as exc:        # capture refused: keep the eager step and say so
+            torch.cuda.synchronize()
+            state["graph"] = None
+            state["graph_note"] = f"eager launches (graph capture failed: {str(exc)[:160]})"
+
+    def step():
+        loss = state["graph"]() if state["graph"] is not None else eager_step()
+        state["loss"] = loss
         return loss
 
     rays_n = loop.px_width * loop.px_height
@@ -566,7 +592,8 @@ def make_backward_step(loop, scene, q, t, dev, world, wl_name="c4"):
         return {"ms_total": (time.perf_counter() - t0) * 1e3, "h2d": 0, "d2h": 4}
 
     # my kernels per step: render_kernel (G-buffer forward), render_bwd_kernel
-    return step, {"launches": 2, "roofline": roofline, "e2e": e2e}
+    return step, {"launches": 2, "roofline": roofline, "e2e": e2e, "eager_step": eager_step,
+                  "note": lambda: state["graph_note"]}
 
 
 # ---------------------------------------------------------------------------- CPU arm
@@ -676,8 +703,11 @@ def main():
     ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--specialise", default="on", choices=["off", "on"],
-                    help="forward workloads with small tapes (c1, c2) run the tape-specialised render kernel "
+                    help="workloads with small tapes (c1, c2, c4) run the tape-specialised kernels "
                          "(RenderLoop.specialise()); the interpreter timing is reported as an extra key")
+    ap.add_argument("--graph", type=int, default=1,
+                    help="c4 on a registry scene: 1 = the whole optimisation step is one CUDA-graph replay "
+                         "(frames.GraphedStep), 0 = eager launches")
     ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c4", "c4b", "c5"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--early-exit", type=int, default=0,

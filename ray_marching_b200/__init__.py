@@ -7,7 +7,7 @@ scene_registry), ``rendering`` (PinholeCamera, SDFMarcher, SDFNormals, Shader) a
 """
 from . import quaternion, scene, tape  # noqa: F401
 from .control import RenderLoop, make_reflection_directions  # noqa: F401
-from .frames import CameraPath, FrameLoop, write_png, write_npy  # noqa: F401
+from .frames import CameraPath, FrameLoop, GraphedStep, write_png, write_npy  # noqa: F401
 from .rendering.ray_marching import PinholeCamera, SDFMarcher, SDFNormals  # noqa: F401
 from .rendering.shader import Shader  # noqa: F401
 

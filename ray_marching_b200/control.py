@@ -51,10 +51,12 @@ class RenderLoop(nn.Module):
         """Compiles (nvcc, once per scene structure, cached under build/spec/) and selects a render
         kernel with this scene's tape unrolled into straight-line code instead of interpreted
         (``specialise.py``); parameters stay run-time data.  Small tapes only; ``enable=False``
-        returns to the interpreter.  Affects the fused no-autograd path."""
+        returns to the interpreter.  Affects the fused no-autograd path and the autograd path
+        (G-buffer forward and the fused backward kernel)."""
         from . import specialise as S
         tape = tape_of(self.scene)
         tape.spec_lib = S.specialised_lib(tape) if enable else None
+        S.select(tape, tape.spec_lib)            # the autograd path (render_gbuffer / render_bwd) follows
         return self
 
     # ---- fused, no autograd -------------------------------------------------------------

@@ -531,6 +531,11 @@ inline int check_backward_tape(const RmTape* t) {
     if (t->n_nodes > MAX_NODES)
         return fail(RM_ERR_UNSUPPORTED, "backward supports at most %d union nodes (tape has %d)",
                     MAX_NODES, t->n_nodes);
+#ifdef RM_SPEC_INC
+    // specialised library: the tape is compiled in; refuses any other structure
+    if (t->n_instr != RM_SPEC_N || tape_code_hash(t) != RM_SPEC_HASH)
+        return fail(RM_ERR_INVALID, "this library is specialised for another tape (hash %08x)", (unsigned)RM_SPEC_HASH);
+#endif
     return RM_OK;
 }
 // The kernels loop `iters` times over a grid of `blocks`; both are chosen so that every block runs
@@ -562,6 +567,23 @@ inline size_t backward_smem(const RmTape* t) {
 
 // Picks the kernel instantiation: lane columns exist only for the small code capacity (a tape of
 // <= 96 parameter floats never has more than 96 instructions).
+#ifdef RM_SPEC_INC
+// specialised library: one code capacity (the kernels read the compiled-in tape, not `code`)
+#define RM_BWD_LAUNCH(tape, KERNEL, grid, sm, stream, ...)                                              \
+    do {                                                                                                \
+        rm::TapeCode<rm::CODE_CAP_SMALL> small;                                                         \
+        rm::expand_code((tape)->code_host, (tape)->n_instr, small);                                     \
+        if (rm::backward_acc_mode(tape) == rm::ACC_LANES) {                                             \
+            if (int s_ = rm::prepare_smem(KERNEL<rm::CODE_CAP_SMALL, rm::ACC_LANES>, sm)) return s_;    \
+            KERNEL<rm::CODE_CAP_SMALL, rm::ACC_LANES><<<grid, rm::BLOCK_B, sm, (cudaStream_t)stream>>>( \
+                small, __VA_ARGS__);                                                                    \
+        } else {                                                                                        \
+            if (int s_ = rm::prepare_smem(KERNEL<rm::CODE_CAP_SMALL, rm::ACC_WARPS>, sm)) return s_;    \
+            KERNEL<rm::CODE_CAP_SMALL, rm::ACC_WARPS><<<grid, rm::BLOCK_B, sm, (cudaStream_t)stream>>>( \
+                small, __VA_ARGS__);                                                                    \
+        }                                                                                               \
+    } while (0)
+#else
 #define RM_BWD_LAUNCH(tape, KERNEL, grid, sm, stream, ...)                                              \
     RM_WITH_CODE(tape, {                                                                                \
         if (CAP == rm::CODE_CAP_SMALL && rm::backward_acc_mode(tape) == rm::ACC_LANES) {                \
@@ -575,6 +597,7 @@ inline size_t backward_smem(const RmTape* t) {
             KERNEL<CAP, rm::ACC_WARPS><<<grid, rm::BLOCK_B, sm, (cudaStream_t)stream>>>(code, __VA_ARGS__); \
         }                                                                                               \
     })
+#endif
 
 }  // namespace rm
 

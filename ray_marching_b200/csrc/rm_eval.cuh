@@ -58,10 +58,26 @@ struct NodeRecords {
 // -- the straight-line sequence of exactly the statements the interpreter below executes for that
 // tape (same primitive bodies, same fold order, constant record offsets) -- and the non-recording
 // interpreter call sites use it instead of decoding.  Parameters still come from the staged block.
+//
+// The RECORDING interpreter and the reverse sweep (backward kernels) are specialised by the compiler
+// instead: the generated header also carries the tape words as a switch (spec_word), the tape loops
+// below fetch through tape_ins() and are fully unrolled, so every decode, dispatch and stack index
+// constant-folds and what remains is the straight-line code of that tape.
 #ifdef RM_SPEC_INC
 }  // namespace rm
 #include RM_SPEC_INC
 namespace rm {
+template <int CAP>
+__device__ __forceinline__ int4 tape_ins(const TapeCode<CAP>&, int pc) {
+    return expand_one(spec_word(pc, 0), spec_word(pc, 1), false);
+}
+#define RM_TAPE_LEN(n_instr) RM_SPEC_N
+#define RM_TAPE_LOOP _Pragma("unroll")
+#else
+template <int CAP>
+__device__ __forceinline__ int4 tape_ins(const TapeCode<CAP>& C, int pc) { return C.ins[pc]; }
+#define RM_TAPE_LEN(n_instr) (n_instr)
+#define RM_TAPE_LOOP
 #endif
 
 // CULLMODE: 0 = the code carries no culling flags; 1 = flags present (a culling launch) but this
@@ -93,7 +109,7 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
     int sp = 0;
     const char* sbytes = reinterpret_cast<const char*>(spar);
     // root union without post-ops: start inside it (see TapeCode::hdr); record mode walks everything
-    int pc0 = 0, pc1 = n_instr, rootm = 0;
+    int pc0 = 0, pc1 = RM_TAPE_LEN(n_instr), rootm = 0;
     if (!RECORD) {
         const int4 h = C.hdr;
         pc0 = h.x; pc1 = h.y; rootm = h.z;
@@ -103,10 +119,11 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
 #pragma unroll
     for (int k = 0; k < K; ++k) { a0[k] = a_init; a1[k] = 0.f; d[k] = 0.f; }
 
-    int4 nxt = C.ins[pc0];
+    int4 nxt = tape_ins(C, pc0);
+    RM_TAPE_LOOP
     for (int pc = pc0; pc < pc1; ++pc) {
         const int4 ins = nxt;
-        nxt = C.ins[pc + 1];                          // prefetch (pad entry after the last instruction)
+        nxt = tape_ins(C, pc + 1);                    // prefetch (pad entry after the last instruction)
         const float4* P = reinterpret_cast<const float4*>(sbytes + ins.z);
         const int disp_raw = ins_disp(ins.w);
         const int disp = CULLMODE ? (disp_raw & ~DISP_CULL) : disp_raw;  // flags are only set for culling launches

@@ -153,8 +153,9 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
     for (int k = 0; k < K; ++k) { gx[k] = gy[k] = gz[k] = 0.f; cur.a[k] = cur.d[k] = cur.s[k] = 0.f; cur.win[k] = -1; }
     cur.c = 0.f;
 
-    for (int pc = n_instr - 1; pc >= 0; --pc) {
-        const int4 ins = C.ins[pc];
+    RM_TAPE_LOOP
+    for (int pc = RM_TAPE_LEN(n_instr) - 1; pc >= 0; --pc) {
+        const int4 ins = tape_ins(C, pc);
         const int head = ins.x, op = head_op(head);
         const int fold = head_fold(head), np = head_npost(head);
         const int off = word_par(ins.y), node = word_node(ins.y), ordinal = head_ordinal(head);

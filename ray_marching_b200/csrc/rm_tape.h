@@ -70,27 +70,29 @@ __host__ __device__ __forceinline__ int ins_disp(int w) { return (int)((unsigned
 __host__ __device__ __forceinline__ int ins_tail(int w) { return (w >> 20) & 15; }
 __host__ __device__ __forceinline__ int ins_post_off(int w) { return w & 0xFFFFF; }
 
-// Host: [n][2] words -> expanded instructions.
-// `with_cull`: set the DISP_CULL dispatch flags (only the culling kernels look at them).
-inline void expand_instructions(const int32_t* words, int n, int4* out, bool with_cull) {
-    for (int i = 0; i < n; ++i) {
-        const int head = words[2 * i], w1 = words[2 * i + 1];
-        const int op = head_op(head), np = head_npost(head), fold = head_fold(head);
-        const int off = word_par(w1);
-        int disp, post_f4 = off;
-        if (op < OP_OPEN_MIN) {
-            disp = op | ((head & HEAD_FRAME) ? DISP_FRAME : 0);
-            post_f4 = off + ((head & HEAD_FRAME) ? 3 : 0) + prim_f4(op);
-        } else {
-            disp = DISP_OPEN_MIN + (op - OP_OPEN_MIN);
-        }
-        int post_case = TAIL_POST_NONE;
-        if (np == 1) post_case = head_post(head, 0) == POST_ONION ? TAIL_POST_ONION : TAIL_POST_ROUND;
-        else if (np > 1) post_case = TAIL_POST_CHAIN;
-        const int tail = (op == OP_OPEN_MIN || op == OP_OPEN_SMOOTH) ? 0 : fold * 4 + post_case;
-        if (with_cull && word_cull(w1) && op != OP_OPEN_MIN && op != OP_CLOSE_MIN) disp |= DISP_CULL;
-        out[i] = make_int4(head, w1, off * 16, ((np ? post_f4 * 16 : 0) & 0xFFFFF) | (tail << 20) | (disp << 24));
+// One instruction: (word0, word1) -> expanded 16 bytes.
+// `with_cull`: set the DISP_CULL dispatch flag (only the culling kernels look at it).
+__host__ __device__ __forceinline__ int4 expand_one(int head, int w1, bool with_cull) {
+    const int op = head_op(head), np = head_npost(head), fold = head_fold(head);
+    const int off = word_par(w1);
+    int disp, post_f4 = off;
+    if (op < OP_OPEN_MIN) {
+        disp = op | ((head & HEAD_FRAME) ? DISP_FRAME : 0);
+        post_f4 = off + ((head & HEAD_FRAME) ? 3 : 0) + prim_f4(op);
+    } else {
+        disp = DISP_OPEN_MIN + (op - OP_OPEN_MIN);
     }
+    int post_case = TAIL_POST_NONE;
+    if (np == 1) post_case = head_post(head, 0) == POST_ONION ? TAIL_POST_ONION : TAIL_POST_ROUND;
+    else if (np > 1) post_case = TAIL_POST_CHAIN;
+    const int tail = (op == OP_OPEN_MIN || op == OP_OPEN_SMOOTH) ? 0 : fold * 4 + post_case;
+    if (with_cull && word_cull(w1) && op != OP_OPEN_MIN && op != OP_CLOSE_MIN) disp |= DISP_CULL;
+    return make_int4(head, w1, off * 16, ((np ? post_f4 * 16 : 0) & 0xFFFFF) | (tail << 20) | (disp << 24));
+}
+
+// Host: [n][2] words -> expanded instructions.
+inline void expand_instructions(const int32_t* words, int n, int4* out, bool with_cull) {
+    for (int i = 0; i < n; ++i) out[i] = expand_one(words[2 * i], words[2 * i + 1], with_cull);
     out[n] = make_int4(0, 0, 0, 0);
 }
 template <int CAP>

@@ -12,6 +12,8 @@ Replaces the interactive tail of the reference's ``main.py:52-88`` -- ``EventAgg
                         ``Window.draw`` consumes (``torchwindow/window.py:146-174``) in a static
                         device buffer -- no host work, allocation or launch overhead per frame
                         (config 1 is launch-latency scale: SURVEY.md §8(d));
+* :class:`GraphedStep` an inverse-rendering step (forward, loss, backward, Adam) captured as one CUDA
+                        graph -- the training-side counterpart of :class:`FrameLoop`;
 * :func:`write_png` / :func:`write_npy`  the ``save_frame`` branch the reference left commented out
                         (``main.py:72-77``).
 """
@@ -166,6 +168,49 @@ class FrameLoop:
         self.path.poses.copy_(saved[0])
         self.path.counter.copy_(saved[1])
         self._graph = g
+
+
+class GraphedStep:
+    """An optimisation step (forward kernels, loss, ``backward()``, optimiser update) captured ONCE
+    as a CUDA graph; :meth:`__call__` replays it and returns the static loss tensor.
+
+    The inverse-rendering loop of config 4 on a registry scene is launch-bound -- the G-buffer and
+    backward kernels take ~0.6 ms of GPU time per step, the ~60 launches of the loss algebra, the
+    parameter lowering and Adam cost more than that in host time -- so, like a display frame
+    (:class:`FrameLoop`), the step is replayed from a graph.  ``body()`` must run the step WITHOUT
+    ``zero_grad`` and return the loss; it may not synchronise or read tensors back.  The optimiser
+    must be created with ``capturable=True``.  Gradients live in the graph's memory pool and are
+    overwritten by every replay (``zero_grad(set_to_none=True)`` is applied once before capture)."""
+
+    def __init__(self, body, optimizer, *, warmup: int = 3):
+        self.optimizer = optimizer
+        params = [p for group in optimizer.param_groups for p in group["params"]]
+        saved = [p.detach().clone() for p in params]
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(max(warmup, 1)):          # allocator warm-up + optimiser state allocation
+                optimizer.zero_grad(set_to_none=True)
+                body()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        # the warm-up steps must not count: restore the parameters and return the optimiser state
+        # (allocated now, as graph capture needs) to its initial zeros
+        with torch.no_grad():
+            for p, p0 in zip(params, saved):
+                p.copy_(p0)
+            for st in optimizer.state.values():
+                for v in st.values():
+                    if torch.is_tensor(v):
+                        v.zero_()
+        optimizer.zero_grad(set_to_none=True)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self.loss = body()
+
+    def __call__(self) -> Tensor:
+        self.graph.replay()
+        return self.loss
 
 
 def to_rgba8(rgba: Tensor) -> np.ndarray:

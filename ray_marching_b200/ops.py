@@ -14,7 +14,7 @@ from typing import List, Optional, Tuple
 import torch
 from torch import Tensor
 
-from . import _lib
+from . import _lib, specialise as _spec
 from ._lib import (RmCamera, RmRenderArgs, RmRenderGrads, RmRenderOut, RmTape, check, lib, ptr,
                    stream_ptr)
 
@@ -252,8 +252,13 @@ def _sdf_vjp(code: Tensor, par: Tensor, points: Tensor, grad: Tensor, n_nodes: i
     dpts = torch.empty_like(pts)
     dpar = torch.empty_like(par)
     tape = _tape_struct(code, par, n_nodes, max_depth)
-    check(lib().rm_sdf_vjp(C.byref(tape), ptr(pts), ptr(g), pts.shape[0], ptr(dpts), ptr(dpar),
-                           stream_ptr(dev)), "rm_sdf_vjp")
+    spec = _spec.selected_for(code)
+    if spec is not None:
+        _spec.spec_check(spec, spec.rm_sdf_vjp(C.byref(tape), ptr(pts), ptr(g), pts.shape[0], ptr(dpts),
+                                               ptr(dpar), stream_ptr(dev)), "rm_sdf_vjp")
+    else:
+        check(lib().rm_sdf_vjp(C.byref(tape), ptr(pts), ptr(g), pts.shape[0], ptr(dpts), ptr(dpar),
+                               stream_ptr(dev)), "rm_sdf_vjp")
     return dpar, dpts.reshape(points.shape)
 
 
@@ -283,12 +288,19 @@ def _march_bwd(code: Tensor, par: Tensor, origin: Tensor, dirs: Tensor, grad_pos
     dev = _lib.require_cuda(par, origin, dirs, grad_pos)
     o, v, g = _flat3(origin), _flat3(dirs), _flat3(grad_pos)
     n = o.shape[0]
-    traj = torch.empty(max(int(lib().rm_bwd_scratch_floats(n, steps)), 1), device=dev, dtype=torch.float32)
+    spec = _spec.selected_for(code)
+    traj = torch.empty(max(int((spec or lib()).rm_bwd_scratch_floats(n, steps)), 1), device=dev,
+                       dtype=torch.float32)
     do, dv = torch.empty_like(o), torch.empty_like(v)
     dpar = torch.empty_like(par)
     tape = _tape_struct(code, par, n_nodes, max_depth)
-    check(lib().rm_march_bwd(C.byref(tape), ptr(o), ptr(v), ptr(g), n, steps, float(tol), ptr(traj), ptr(do),
-                             ptr(dv), ptr(dpar), stream_ptr(dev)), "rm_march_bwd")
+    if spec is not None:
+        _spec.spec_check(spec, spec.rm_march_bwd(C.byref(tape), ptr(o), ptr(v), ptr(g), n, steps, float(tol),
+                                                 ptr(traj), ptr(do), ptr(dv), ptr(dpar), stream_ptr(dev)),
+                         "rm_march_bwd")
+    else:
+        check(lib().rm_march_bwd(C.byref(tape), ptr(o), ptr(v), ptr(g), n, steps, float(tol), ptr(traj),
+                                 ptr(do), ptr(dv), ptr(dpar), stream_ptr(dev)), "rm_march_bwd")
     return dpar, do.reshape(origin.shape), dv.reshape(dirs.shape)
 
 
@@ -333,8 +345,13 @@ def _render_gbuffer(code: Tensor, par: Tensor, poses: Tensor, n_views: int, widt
     a = RmRenderArgs(0, n, int(steps), 0, float(eps), 0.0, 0.0, 0, -1, 1, 0, 0, 0, 0.0)   # IEEE math
     cam = camera_struct(n_views, width, height, focal, sensor_w, sensor_h)
     t = _tape_struct(code, par, n_nodes, max_depth)
-    check(lib().rm_render(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(o),
-                          stream_ptr(dev)), "rm_render")
+    spec = _spec.selected_for(code)
+    if spec is not None:
+        _spec.spec_check(spec, spec.rm_render(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(o),
+                                              stream_ptr(dev)), "rm_render")
+    else:
+        check(lib().rm_render(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(o),
+                              stream_ptr(dev)), "rm_render")
     return origin, dirs, pos, sdf, nrm, lap
 
 
@@ -356,15 +373,22 @@ def _render_bwd(code: Tensor, par: Tensor, poses: Tensor, n_views: int, width: i
     cont = lambda g: None if g is None else g.contiguous()
     gs = [cont(g) for g in (g_origin, g_dirs, g_pos, g_sdf, g_normals, g_lap)]
     grads = RmRenderGrads(*[ptr(g) for g in gs])
-    traj = torch.empty(max(int(lib().rm_bwd_scratch_floats(n, steps)), 1), device=dev, dtype=torch.float32)
+    spec = _spec.selected_for(code)                 # the scratch size belongs to the library that runs
+    traj = torch.empty(max(int((spec or lib()).rm_bwd_scratch_floats(n, steps)), 1), device=dev,
+                       dtype=torch.float32)
     dpar = torch.empty_like(par)
     poses = poses.contiguous()
     dposes = torch.empty_like(poses)
     a = RmRenderArgs(0, n, int(steps), 0, float(eps), 0.0, 0.0, 0, -1, 1, 0, 0, 0, float(tol))
     cam = camera_struct(n_views, width, height, focal, sensor_w, sensor_h)
     t = _tape_struct(code, par, n_nodes, max_depth)
-    check(lib().rm_render_bwd(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(grads),
-                              ptr(traj), ptr(dpar), ptr(dposes), stream_ptr(dev)), "rm_render_bwd")
+    if spec is not None:
+        _spec.spec_check(spec, spec.rm_render_bwd(C.byref(t), C.byref(cam), ptr(poses), C.byref(a),
+                                                  C.byref(grads), ptr(traj), ptr(dpar), ptr(dposes),
+                                                  stream_ptr(dev)), "rm_render_bwd")
+    else:
+        check(lib().rm_render_bwd(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(grads),
+                                  ptr(traj), ptr(dpar), ptr(dposes), stream_ptr(dev)), "rm_render_bwd")
     return dpar, dposes
 
 

@@ -5,8 +5,10 @@ The general path interprets the tape (csrc/rm_eval.cuh).  For small tapes the in
 variants.md).  This module emits, for one tape, the straight-line sequence of exactly the statements
 the interpreter would execute (the same hand-written primitive bodies of csrc/rm_prims.cuh, the same
 fold order, constant record offsets), and compiles the unchanged forward translation unit around it
-with nvcc for sm_100a into ``build/spec/librm_spec_<hash>.so``, which exports ``rm_render`` with the
-ABI of include/rm_b200.h.  Scene PARAMETERS stay run-time data (staged from ``par`` as before): an
+with nvcc for sm_100a into ``build/spec/librm_spec_<hash>.so``, which exports ``rm_render`` and the
+backward entry points (``rm_render_bwd``, ``rm_march_bwd``, ``rm_sdf_vjp``) with the ABI of
+include/rm_b200.h.  The backward kernels are specialised by the compiler: the header carries the tape
+words as a switch, their tape loops are fully unrolled and every decode constant-folds (rm_eval.cuh).  Scene PARAMETERS stay run-time data (staged from ``par`` as before): an
 optimiser step never recompiles.  Structure hash = FNV-1a of the instruction words, checked by the
 library at every launch.
 
@@ -131,10 +133,24 @@ def generate_source(tape) -> str:
         fold_into_parent(fold)
     assert not stack, "unbalanced tape"
     body = "\n".join(out)
+    words = np.asarray(tape.code, dtype=np.int64).reshape(-1, 2)
+    cases = "\n".join(f"        case {2 * i + j}: return (int)0x{int(w) & 0xFFFFFFFF:08x}u;"
+                      for i, row in enumerate(words.tolist()) for j, w in enumerate(row))
     return f"""// GENERATED by ray_marching_b200/specialise.py for {tape.describe()}
 // Straight-line form of the tape: the statements csrc/rm_eval.cuh executes for it, in order.
 #pragma once
 #define RM_SPEC_HASH 0x{code_hash(tape.code):08x}u
+#define RM_SPEC_N {tape.n_instr}
+namespace rm {{
+// the tape words (rm_tape.h encoding): constant-folded by the unrolled tape loops of the recording
+// interpreter and the reverse sweep
+__host__ __device__ __forceinline__ int spec_word(int pc, int j) {{
+    switch (pc * 2 + j) {{
+{cases}
+        default: return 0;
+    }}
+}}
+}}  // namespace rm
 #define RM_FORK _Pragma("unroll") for (int k = 0; k < K; ++k)
 namespace rm {{
 template <int K, bool FAST>
@@ -177,7 +193,8 @@ def build(tape, force: bool = False) -> str:
     cmd = [NVCC, "-shared", "-o", tmp, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo",
            "-std=c++17", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", f'-DRM_SPEC_INC="{inc}"',
            *os.environ.get("RM_B200_SPEC_FLAGS", "").split(),      # launch-shape experiments
-           os.path.join(CSRC, "rm_host.cu"), os.path.join(CSRC, "rm_forward.cu")]
+           os.path.join(CSRC, "rm_host.cu"), os.path.join(CSRC, "rm_forward.cu"),
+           os.path.join(CSRC, "rm_backward.cu")]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed for the specialised library:\n" + res.stdout + res.stderr)
@@ -186,6 +203,33 @@ def build(tape, force: bool = False) -> str:
 
 
 _loaded = {}
+# entry points a specialised library exports besides rm_abi_version / rm_last_error
+SPEC_EXPORTS = ("rm_render", "rm_render_bwd", "rm_march_bwd", "rm_sdf_vjp", "rm_bwd_scratch_floats")
+
+# Libraries selected by RenderLoop.specialise(), keyed by the tape's code bytes: the autograd ops
+# (ops.py: render_gbuffer / render_bwd) receive the code tensor, not the Tape object.
+_selected = {}
+
+
+def select(tape, handle: Optional[C.CDLL]) -> None:
+    key = np.ascontiguousarray(tape.code, dtype=np.int32).tobytes()
+    if handle is None:
+        _selected.pop(key, None)
+    else:
+        _selected[key] = handle
+
+
+def selected_for(code) -> Optional[C.CDLL]:
+    """The specialised library selected for this code block (a host int32 tensor), or None."""
+    if not _selected:
+        return None
+    return _selected.get(code.numpy().tobytes())
+
+
+def spec_check(handle: C.CDLL, status: int, what: str) -> None:
+    if status != 0:
+        raise _lib.RmError(f"{what} (specialised) failed with status {status}: "
+                           f"{handle.rm_last_error().decode(errors='replace')}")
 
 
 def specialised_lib(tape, build_if_missing: bool = True) -> Optional[C.CDLL]:
@@ -199,7 +243,9 @@ def specialised_lib(tape, build_if_missing: bool = True) -> Optional[C.CDLL]:
     elif not (os.path.exists(path) and os.path.exists(inc) and open(inc).read() == generate_source(tape)):
         return None
     handle = C.CDLL(path)
-    handle.rm_render.restype, handle.rm_render.argtypes = _lib._SIGNATURES["rm_render"]
+    for name in SPEC_EXPORTS:
+        fn = getattr(handle, name)
+        fn.restype, fn.argtypes = _lib._SIGNATURES[name]
     handle.rm_last_error.restype = C.c_char_p
     if handle.rm_abi_version() != _lib.ABI_VERSION:
         raise RuntimeError(f"{path}: ABI version mismatch; rebuild")

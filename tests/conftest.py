@@ -35,3 +35,15 @@ def golden():
             cache[name] = np.load(os.path.join(GOLDEN, f"{name}.npz"))
         return cache[name]
     return load
+
+
+@pytest.fixture(autouse=True)
+def _no_leftover_specialisation():
+    """RenderLoop.specialise() selects a library per scene STRUCTURE (process-wide); tests start
+    and end with the interpreter."""
+    yield
+    try:
+        from ray_marching_b200 import specialise
+        specialise._selected.clear()
+    except Exception:
+        pass

@@ -91,3 +91,51 @@ def test_frame_equals_display_frame_and_recaptures_on_parameter_change(tmp_path)
     frames.write_png(tmp_path / "f.png", c)
     assert (frames.read_png(tmp_path / "f.png") == frames.to_rgba8(c)).all()
     assert c[..., 3].min().item() == 1.0
+
+
+@pytest.mark.parametrize("specialise", [False, True])
+def test_graphed_optimisation_step_follows_the_eager_trajectory(specialise):
+    """frames.GraphedStep: config-4 style inverse rendering (lambertian + depth MSE, Adam on the scene
+    parameters and the camera) -- five replays of the captured step against five eager steps from the
+    same start (the warm-up steps of the capture must not count)."""
+    def setup():
+        torch.manual_seed(0)
+        scene = make_test_scene2()
+        loop = make_loop(scene, 64, 48)
+        if specialise:
+            loop.specialise()
+        q = torch.nn.functional.normalize(torch.tensor([[0.99, 0.03, -0.08, 0.05]], device="cuda"), dim=-1)
+        t = torch.tensor([[0.05, 0.1, 1.0]], device="cuda")
+        with torch.no_grad():
+            gb = loop.gbuffer(q, t, 32)
+            lam_t = (-(gb["dirs"] * gb["normals"]).sum(-1, keepdim=True)).clamp(0, 1) * 0.9
+            depth_t = (gb["pos"] - gb["origin"]).norm(dim=-1, keepdim=True) * 1.05
+        q, t = q.clone().requires_grad_(True), t.clone().requires_grad_(True)
+        params = list(scene.parameters()) + [q, t]
+        opt = torch.optim.Adam(params, lr=1e-2, foreach=True, capturable=True)
+
+        def body():
+            gb = loop.gbuffer(q, t, 32)
+            lam = (-(gb["dirs"] * gb["normals"]).sum(-1, keepdim=True)).clamp(0, 1)
+            depth = (gb["pos"] - gb["origin"]).norm(dim=-1, keepdim=True)
+            loss = ((lam - lam_t) ** 2).mean() + ((depth - depth_t) ** 2).mean()
+            loss.backward()
+            opt.step()
+            return loss
+        return params, opt, body
+
+    params, opt, body = setup()
+    eager_losses = []
+    for _ in range(5):
+        opt.zero_grad(set_to_none=True)
+        eager_losses.append(body().item())
+    eager = torch.cat([p.detach().reshape(-1) for p in params]).clone()
+
+    params, opt, body = setup()
+    step = frames.GraphedStep(body, opt)
+    graph_losses = [step().item() for _ in range(5)]
+    graphed = torch.cat([p.detach().reshape(-1) for p in params])
+    assert eager_losses[-1] < eager_losses[0]                       # it optimises
+    np.testing.assert_allclose(graph_losses, eager_losses, rtol=1e-4)
+    # atomics order differs run to run; Adam's normalised update amplifies that slightly
+    assert (graphed - eager).abs().max().item() < 2e-4

@@ -53,5 +53,7 @@ def test_specialised_translation_unit_compiles(tmp_path, monkeypatch):
     assert os.path.exists(lib)
     out = os.popen(f"nm -D --defined-only {lib}").read()
     assert " rm_render" in out and " rm_abi_version" in out and " rm_last_error" in out
-    assert " rm_march" not in out and " rm_sdf_eval" not in out          # rm_render only
+    for name in SP.SPEC_EXPORTS:                                             # render + the backward entry points
+        assert f" {name}\n" in out, name
+    assert " rm_march\n" not in out and " rm_sdf_eval" not in out          # no stand-alone forward ops
     assert SP.build(tape_of(nested_scene())) == lib                          # cached
