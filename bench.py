@@ -219,7 +219,7 @@ def run_gpu(args):
     spec_on, spec_note = False, "interpreter"
     if args.specialise == "on" and not args.cull:       # forward AND backward kernels (c1, c2, c4)
         from ray_marching_b200 import specialise as SPEC
-        if tape.n_instr <= SPEC.MAX_SPEC_INSTR:
+        if tape.n_instr <= (SPEC.MAX_SPEC_INSTR_BWD if wl["backward"] else SPEC.MAX_SPEC_INSTR):
             try:
                 loop.specialise(True)
                 spec_on, spec_note = True, "tape-specialised (RenderLoop.specialise())"
@@ -394,6 +394,13 @@ def run_gpu(args):
             "gpu_launches": launches_per_step * args.steps,
             "clocks": clocks,
         }
+        if "f16_ms_total" in e2e:
+            line["e2e_f16_planes"] = {
+                "value": rays / (e2e["f16_ms_total"] / args.steps * 1e-3) / 1e6, "unit": "Mrays/s",
+                "d2h_bytes_per_step": e2e["f16_d2h"],
+                "note": "rank 0's own loop (per GPU): the e2e loop with binary16 image planes on the wire "
+                        "(rm_planes_to_f16, float32 arithmetic, pixels exact to 2.4e-4); the headline "
+                        "e2e keeps the reference's float32 planes"}
         if interp_info is not None:
             line["interpreter"] = interp_info
         if graph_info is not None:
@@ -460,7 +467,43 @@ def measure_e2e(frame, wl, q, t, dev, args, barrier):
         step(i)
     torch.cuda.synchronize()
     barrier()
-    return {"ms_total": (time.perf_counter() - t0) * 1e3, "h2d": h2d, "d2h": d2h}
+    out = {"ms_total": (time.perf_counter() - t0) * 1e3, "h2d": h2d, "d2h": d2h}
+
+    # the same loop with binary16 image planes on the wire (rm_planes_to_f16): float32
+    # arithmetic, pixels exact to 2.4e-4 -- reported beside the float32 headline, never instead of it
+    mask = sum(1 << m for m in modes)
+    host16 = [{m: torch.empty(rays, ops.MODE_CHANNELS[m], dtype=torch.float16).pin_memory() for m in modes}
+              for _ in range(2)]
+    half, copied16 = [None, None], [None, None]
+
+    def step16(i):
+        b = i & 1
+        if copied16[b] is not None:
+            main.wait_event(copied16[b])
+        qd, td = q_h.to(dev, non_blocking=True), t_h.to(dev, non_blocking=True)
+        bufs[b] = frame(qd, td, bufs[b])
+        half[b] = ops.planes_to_half(bufs[b], mask, out=half[b])
+        rendered = torch.cuda.Event()
+        rendered.record(main)
+        with torch.cuda.stream(side):
+            side.wait_event(rendered)
+            for m in modes:
+                host16[b][m].copy_(half[b][m], non_blocking=True)
+            copied16[b] = torch.cuda.Event()
+            copied16[b].record(side)
+
+    for i in range(4):
+        step16(i)
+    torch.cuda.synchronize()
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        step16(i)
+    torch.cuda.synchronize()
+    barrier()
+    out["f16_ms_total"] = (time.perf_counter() - t0) * 1e3
+    out["f16_d2h"] = d2h // 2
+    return out
 
 
 def ncu_traffic(kernel: str, workload: str):
@@ -513,27 +556,34 @@ def make_backward_step(loop, scene, q, t, dev, world, wl_name="c4", graph=True):
     opt = torch.optim.Adam(params + [q, t], lr=1e-2, foreach=True, capturable=True)
     state = {"graph": None, "graph_note": "eager launches"}
 
-    def body():
+    def forward_backward():
         lam, depth, rays = gbuf()
         loss = ((lam - lam_t) ** 2).mean() + ((depth - depth_t) ** 2).mean()
         loss.backward()
-        if world > 1:          # one NCCL SUM over the flat gradient buffer (scene params + q, t)
-            parallel.allreduce_gradients(params + [q, t], average=True)
-        opt.step()
         return loss
+
+    def allreduce():           # one NCCL SUM over the flat gradient buffer (scene params + q, t)
+        parallel.allreduce_gradients(params + [q, t], average=True)
 
     def eager_step():
         opt.zero_grad(set_to_none=True)
-        return body()
+        loss = forward_backward()
+        if world > 1:
+            allreduce()
+        opt.step()
+        return loss
 
-    # the whole step as ONE CUDA-graph replay (frames.GraphedStep) when the kernels are short enough
-    # for launch overhead to matter (registry scenes); single GPU only: the NCCL all-reduce of the
-    # sharded job stays an eager launch
-    if graph and world == 1:
+    # the step as CUDA-graph replays (frames.GraphedStep) when the kernels are short enough for launch
+    # overhead to matter (registry scenes): one graph at N = 1; at N > 1 two graphs (forward+backward,
+    # Adam) with the NCCL all-reduce launched eagerly between them
+    if graph:
         try:
             from ray_marching_b200.frames import GraphedStep
-            state["graph"] = GraphedStep(body, opt)
-            state["graph_note"] = "whole step (forward, loss, backward, Adam) = one CUDA-graph replay"
+            state["graph"] = GraphedStep(forward_backward, opt, between=allreduce if world > 1 else None)
+            state["graph_note"] = ("whole step (forward, loss, backward, Adam) = one CUDA-graph replay"
+                                   if world == 1 else
+                                   "two CUDA-graph replays (forward+loss+backward | Adam) around one eager "
+                                   "NCCL all-reduce of the flat gradient buffer")
         except Exception as exc:        # capture refused: keep the eager step and say so
             torch.cuda.synchronize()
             state["graph"] = None

@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define RM_B200_ABI_VERSION 4
+#define RM_B200_ABI_VERSION 5
 
 typedef enum RmStatus {
     RM_OK = 0,
@@ -156,6 +156,14 @@ int rm_reduce_init(float* reduce, void* stream);
  * 81-89): applies the global min/max normalisation and the 1/2.33 gamma in place. */
 int rm_shade_finalize(const float* reduce, uint32_t mode_mask, int64_t n_rays,
                       float* const* image, float* rgba, int32_t display_mode, void* stream);
+
+/* Half-precision copies of the shaded image planes for transport (the reference's
+ * own CUDA run dtype is float16, main.py:21; all arithmetic here stays float32).  For every mode m in
+ * mode_mask with image_f16[m] != NULL converts image[m] ([n] or [n][3] float32, finalised) to IEEE
+ * binary16 with round-to-nearest-even; one launch for all planes.  Shaded pixels lie in [0, 1], where
+ * binary16 is exact to 2.4e-4 -- inside the 1e-3 pixel tolerance. */
+int rm_planes_to_f16(uint32_t mode_mask, int64_t n_rays, const float* const* image,
+                     uint16_t* const* image_f16, void* stream);
 
 /* Backward of a scene evaluation (what torch.autograd does through the nn.Module tree of
  * scene/primitives.py + scene/transformations.py): given d loss / d sdf at n points, writes

@@ -17,7 +17,7 @@ LIB_PATH = os.environ.get("RM_B200_LIB") or os.path.join(_HERE, "csrc", "librm_b
 
 POSE_STRIDE = 8
 REDUCE_FLOATS = 8
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 
 class RmTape(C.Structure):
@@ -67,6 +67,8 @@ _SIGNATURES = {
     "rm_reduce_init": (C.c_int, [C.c_void_p, C.c_void_p]),
     "rm_shade_finalize": (C.c_int, [C.c_void_p, C.c_uint32, C.c_int64, C.POINTER(C.c_void_p),
                                     C.c_void_p, C.c_int32, C.c_void_p]),
+    "rm_planes_to_f16": (C.c_int, [C.c_uint32, C.c_int64, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                   C.c_void_p]),
     "rm_sdf_vjp": (C.c_int, [C.POINTER(RmTape), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p,
                              C.c_void_p, C.c_void_p]),
     "rm_march_bwd": (C.c_int, [C.POINTER(RmTape), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,

@@ -55,8 +55,9 @@ class RenderLoop(nn.Module):
         (G-buffer forward and the fused backward kernel)."""
         from . import specialise as S
         tape = tape_of(self.scene)
-        tape.spec_lib = S.specialised_lib(tape) if enable else None
-        S.select(tape, tape.spec_lib)            # the autograd path (render_gbuffer / render_bwd) follows
+        handle = S.specialised_lib(tape) if enable else None
+        tape.spec_lib = handle if (handle is not None and handle.has_forward) else None
+        S.select(tape, handle)                   # the autograd path (render_gbuffer / render_bwd) follows
         return self
 
     # ---- fused, no autograd -------------------------------------------------------------

@@ -6,9 +6,24 @@ namespace rm {
 inline unsigned grid_for(int64_t n) { return (unsigned)((n + (int64_t)BLOCK * K - 1) / ((int64_t)BLOCK * K)); }
 
 
+// rm_render: threads per block.  A small frame in 256-thread blocks leaves the SMs unevenly filled
+// (c1: 300 blocks on 148 SMs = 2 or 3 blocks each, at most 24 of 64 warp slots); blocks of 128 or 64
+// threads spread the same warps evenly.  Large grids keep 256 (measured best, profiles/r01/
+// variants.md); so do tapes whose staged parameters are too big to replicate per small block.
+inline unsigned render_threads(int64_t n, size_t smem_bytes) {
+    int dev = 0, sms = 148;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+        sms = 148;
+    const int64_t tiles = (n + 32 * K - 1) / (32 * K);
+    unsigned threads = BLOCK;
+    while (threads > 64 && smem_bytes <= 8 * 1024 && tiles / (threads / 32) < (int64_t)sms * 8) threads /= 2;
+    return threads;
+}
+
 // rm_render: persistent grid -- at most (SMs x resident blocks per SM) blocks, each walking a
 // contiguous range of warp tiles (render_kernel); never more blocks than tiles.
-inline unsigned render_grid(int64_t n) {
+inline unsigned render_grid(int64_t n, unsigned threads = BLOCK) {
     static int sms = 0;
     if (sms == 0) {
         int dev = 0, v = 0;
@@ -21,9 +36,12 @@ inline unsigned render_grid(int64_t n) {
 #if RM_PERSIST
     const int64_t tiles = (n + 32 * K - 1) / (32 * K);
     const int64_t cap = (int64_t)sms * RM_MINB;
+    (void)threads;
     return (unsigned)(tiles < cap ? tiles : cap);
 #else
-    return grid_for(n);
+    (void)sms;
+    const int64_t per_block = (int64_t)threads * K;
+    return (unsigned)((n + per_block - 1) / per_block);
 #endif
 }
 
@@ -157,13 +175,18 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
     P.hit_tau = a->hit_tau; P.lift_delta = a->lift_delta; P.mode_mask = a->mode_mask;
     P.display_mode = a->display_mode; P.degree = a->degree; P.early_exit = a->early_exit;
     P.cmap = a->cmap; P.out = *out;
+    const size_t sm = tape_smem_bytes(tape);
+#if RM_PERSIST
+    const unsigned threads = BLOCK;
+#else
+    const unsigned threads = render_threads(a->n_rays, sm);
+#endif
+    const unsigned grid = render_grid(a->n_rays, threads);
     {
         const int64_t tiles = (a->n_rays + 32 * K - 1) / (32 * K);
         if (tiles > 0x7fffffff) return fail(RM_ERR_INVALID, "rm_render: ray range too large for one launch");
-        const unsigned g = render_grid(a->n_rays);
-        P.tile_base = (int)(tiles / g); P.tile_rem = (int)(tiles % g);
+        P.tile_base = (int)(tiles / grid); P.tile_rem = (int)(tiles % grid);     // persistent tiling only
     }
-    const size_t sm = tape_smem_bytes(tape);
 #ifdef RM_SPEC_INC
     // specialised library: one code capacity, no culling variant; refuses any other tape
     if (tape->n_instr > CODE_CAP_SMALL || tape_code_hash(tape) != RM_SPEC_HASH)
@@ -175,11 +198,11 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
         expand_code(tape->code_host, tape->n_instr, code, false);
         if (a->fast_math) {
             if (int s = prepare_smem(render_kernel<true, CAP, false>, sm)) return s;
-            render_kernel<true, CAP, false><<<render_grid(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+            render_kernel<true, CAP, false><<<grid, threads, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
         } else {
             if (int s = prepare_smem(render_kernel<false, CAP, false>, sm)) return s;
-            render_kernel<false, CAP, false><<<render_grid(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+            render_kernel<false, CAP, false><<<grid, threads, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
         }
     }
@@ -187,15 +210,15 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
     RM_WITH_CODE_EX(tape, a->fast_math >= 2, {
         if (a->fast_math >= 2) {
             if (int s = prepare_smem(render_kernel<true, CAP, true>, sm)) return s;
-            render_kernel<true, CAP, true><<<render_grid(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+            render_kernel<true, CAP, true><<<grid, threads, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
         } else if (a->fast_math) {
             if (int s = prepare_smem(render_kernel<true, CAP, false>, sm)) return s;
-            render_kernel<true, CAP, false><<<render_grid(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+            render_kernel<true, CAP, false><<<grid, threads, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
         } else {
             if (int s = prepare_smem(render_kernel<false, CAP, false>, sm)) return s;
-            render_kernel<false, CAP, false><<<render_grid(a->n_rays), BLOCK, sm, (cudaStream_t)stream>>>(
+            render_kernel<false, CAP, false><<<grid, threads, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
         }
     });
@@ -217,6 +240,31 @@ extern "C" int rm_shade_finalize(const float* reduce, uint32_t mode_mask, int64_
     int64_t blocks = ((n >> 2) + 1 + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
     shade_finalize_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(reduce, F);
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+}
+
+extern "C" int rm_planes_to_f16(uint32_t mode_mask, int64_t n, const float* const* image,
+                                uint16_t* const* image_f16, void* stream) {
+    if (n < 0 || image == nullptr || image_f16 == nullptr)
+        return fail(RM_ERR_INVALID, "rm_planes_to_f16: null plane table or negative count");
+    HalfParams H;
+    int64_t longest = 0;
+    for (int m = 0; m < 8; ++m) {
+        const bool on = (mode_mask >> m & 1u) && image_f16[m] != nullptr;
+        if (on && image[m] == nullptr)
+            return fail(RM_ERR_INVALID, "rm_planes_to_f16: mode %d requested but image[%d] is null", m, m);
+        const int channels = (m == 4 || m == 6 || m == 7) ? 3 : 1;
+        H.src[m] = image[m];
+        H.dst[m] = reinterpret_cast<__half*>(image_f16[m]);
+        H.count[m] = on ? n * channels : 0;
+        if (H.count[m] > longest) longest = H.count[m];
+    }
+    if (longest == 0) return RM_OK;
+    int64_t blocks = ((longest >> 2) + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks < 1) blocks = 1;
+    planes_to_half_kernel<<<dim3((unsigned)blocks, 8), 256, 0, (cudaStream_t)stream>>>(H);
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }

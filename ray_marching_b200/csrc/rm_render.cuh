@@ -2,6 +2,7 @@
 // f(p) -> stencil -> shaders, one kernel, nothing but the requested planes touches HBM.
 // Included by rm_forward.cu.
 #pragma once
+#include <cuda_fp16.h>
 
 namespace rm {
 
@@ -56,7 +57,7 @@ __device__ __forceinline__ void block_minmax(MinMax m, float* gmin, float* gmax,
     if (lane == 0) { sh[warp][0] = m.mn; sh[warp][1] = m.mx; sh[warp][2] = m.nan; }
     __syncthreads();
     if (threadIdx.x == 0) {
-        for (int w = 1; w < BLOCK / 32; ++w) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); ++w) {
             m.mn = fminf(m.mn, sh[w][0]); m.mx = fmaxf(m.mx, sh[w][1]); m.nan = fmaxf(m.nan, sh[w][2]);
         }
         if (gmin && m.mn != CUDART_INF_F) atomic_max_f(gmin, -m.mn);    // minima are stored negated
@@ -82,7 +83,7 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
     // No thread-dependent control flow around the march: every thread marches K rays (tail threads
     // march clamped duplicates that are never stored), so the interpreter's decode stays on the
     // uniform datapath and all threads reach the block reductions below.
-    constexpr int WARPS = BLOCK / 32;
+    const int WARPS = (int)(blockDim.x >> 5);         // 2, 4 or 8 (rm_abi_forward.cuh: render_threads)
     const int lane = threadIdx.x & 31;
     const int warp = (int)(__reduce_min_sync(0xffffffffu, threadIdx.x) >> 5);   // REDUX: lands in a uniform register
     // tiles = tile_base * gridDim.x + tile_rem (host): the first tile_rem blocks take one more.  No
@@ -304,6 +305,35 @@ shade_finalize_kernel(const float* __restrict__ reduce, const FinalizeParams F) 
             }
         }
     }
+}
+
+struct HalfParams {
+    const float* src[8];
+    __half* dst[8];
+    int64_t count[8];        // floats per plane (n or 3 n); 0 = plane not converted
+};
+
+// float32 -> binary16 copies of the image planes: HBM-bound (4 B read + 2 B written per value),
+// 128-bit loads and 64-bit stores, one launch for every plane (blockIdx.y = shader mode).
+__global__ void __launch_bounds__(256)
+planes_to_half_kernel(const HalfParams H) {
+    const int m = blockIdx.y;
+    const int64_t count = H.count[m];
+    if (count == 0) return;
+    const float* __restrict__ src = H.src[m];
+    __half* __restrict__ dst = H.dst[m];
+    const int64_t n4 = count >> 2;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
+        const __half2 lo = __floats2half2_rn(v.x, v.y), hi = __floats2half2_rn(v.z, v.w);
+        uint2 packed;
+        packed.x = *reinterpret_cast<const unsigned*>(&lo);
+        packed.y = *reinterpret_cast<const unsigned*>(&hi);
+        reinterpret_cast<uint2*>(dst)[i] = packed;
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (count & 3))
+        dst[n4 * 4 + threadIdx.x] = __float2half_rn(src[n4 * 4 + threadIdx.x]);
 }
 
 }  // namespace rm

@@ -175,15 +175,19 @@ class GraphedStep:
     as a CUDA graph; :meth:`__call__` replays it and returns the static loss tensor.
 
     The inverse-rendering loop of config 4 on a registry scene is launch-bound -- the G-buffer and
-    backward kernels take ~0.6 ms of GPU time per step, the ~60 launches of the loss algebra, the
+    backward kernels take ~0.55 ms of GPU time per step, the ~60 launches of the loss algebra, the
     parameter lowering and Adam cost more than that in host time -- so, like a display frame
-    (:class:`FrameLoop`), the step is replayed from a graph.  ``body()`` must run the step WITHOUT
-    ``zero_grad`` and return the loss; it may not synchronise or read tensors back.  The optimiser
-    must be created with ``capturable=True``.  Gradients live in the graph's memory pool and are
-    overwritten by every replay (``zero_grad(set_to_none=True)`` is applied once before capture)."""
+    (:class:`FrameLoop`), the step is replayed from a graph.
 
-    def __init__(self, body, optimizer, *, warmup: int = 3):
-        self.optimizer = optimizer
+    ``forward_backward()`` runs the forward, the loss and ``loss.backward()`` and returns the loss; it
+    may not synchronise, read tensors back, or call ``zero_grad`` / ``optimizer.step()`` (this class
+    does).  ``between`` -- e.g. the NCCL all-reduce of the gradients of a view-sharded job -- runs
+    eagerly between the two halves; with it the step is two graphs (forward+backward, optimiser
+    update), without it one.  The optimiser must be created with ``capturable=True``.  Gradients live
+    in the graph's memory pool and are overwritten by every replay."""
+
+    def __init__(self, forward_backward, optimizer, *, between=None, warmup: int = 3):
+        self.optimizer, self.between = optimizer, between
         params = [p for group in optimizer.param_groups for p in group["params"]]
         saved = [p.detach().clone() for p in params]
         side = torch.cuda.Stream()
@@ -191,7 +195,10 @@ class GraphedStep:
         with torch.cuda.stream(side):
             for _ in range(max(warmup, 1)):          # allocator warm-up + optimiser state allocation
                 optimizer.zero_grad(set_to_none=True)
-                body()
+                forward_backward()
+                if between is not None:
+                    between()
+                optimizer.step()
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()
         # the warm-up steps must not count: restore the parameters and return the optimiser state
@@ -205,11 +212,31 @@ class GraphedStep:
                         v.zero_()
         optimizer.zero_grad(set_to_none=True)
         self.graph = torch.cuda.CUDAGraph()
+        self.update_graph = None
         with torch.cuda.graph(self.graph):
-            self.loss = body()
+            self.loss = forward_backward()
+            if between is None:
+                optimizer.step()
+        if between is not None:
+            between()
+            self.update_graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.update_graph, pool=self.graph.pool()):
+                optimizer.step()
+            # the capture above ran one real update: undo it
+            torch.cuda.synchronize()
+            with torch.no_grad():
+                for p, p0 in zip(params, saved):
+                    p.copy_(p0)
+                for st in optimizer.state.values():
+                    for v in st.values():
+                        if torch.is_tensor(v):
+                            v.zero_()
 
     def __call__(self) -> Tensor:
         self.graph.replay()
+        if self.update_graph is not None:
+            self.between()
+            self.update_graph.replay()
         return self.loss
 
 

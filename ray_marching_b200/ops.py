@@ -233,6 +233,26 @@ def shade_finalize(res: RenderResult, mode_mask: int, display_mode: int = -1) ->
                                   int(display_mode), stream_ptr(dev)), "rm_shade_finalize")
 
 
+def planes_to_half(res: RenderResult, mode_mask: int, out: Optional[List[Optional[Tensor]]] = None
+                   ) -> List[Optional[Tensor]]:
+    """float16 copies of the (finalised) image planes of ``mode_mask`` for transport -- the
+    reference's own CUDA run dtype (main.py:21); arithmetic stays float32.  One launch
+    (``rm_planes_to_f16``); ``out`` reuses buffers of an earlier call."""
+    first = next(t for t in res.images if t is not None)
+    dev, n = first.device, first.shape[0]
+    half = list(out) if out is not None else [None] * 8
+    for m in range(8):
+        if mode_mask >> m & 1:
+            if res.images[m] is None:
+                raise _lib.RmError(f"planes_to_half: mode {m} was not rendered")
+            if half[m] is None:
+                half[m] = torch.empty(n, MODE_CHANNELS[m], device=dev, dtype=torch.float16)
+    src = (C.c_void_p * 8)(*[ptr(t) for t in res.images])
+    dst = (C.c_void_p * 8)(*[ptr(t) if (mode_mask >> m & 1) else None for m, t in enumerate(half)])
+    check(lib().rm_planes_to_f16(int(mode_mask), n, src, dst, stream_ptr(dev)), "rm_planes_to_f16")
+    return half
+
+
 def pose_records(orientations: Tensor, translations: Tensor) -> Tensor:
     """``(N,4),(N,3) -> (N,8)`` pose records ``(q, t, 0)`` (differentiable: one concatenate).  The
     kernels expand them to the rotation polynomial of ``Q.rotation`` (ray_marching.py:58-63) and
@@ -346,7 +366,7 @@ def _render_gbuffer(code: Tensor, par: Tensor, poses: Tensor, n_views: int, widt
     cam = camera_struct(n_views, width, height, focal, sensor_w, sensor_h)
     t = _tape_struct(code, par, n_nodes, max_depth)
     spec = _spec.selected_for(code)
-    if spec is not None:
+    if spec is not None and spec.has_forward:
         _spec.spec_check(spec, spec.rm_render(C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(o),
                                               stream_ptr(dev)), "rm_render")
     else:

@@ -31,6 +31,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 SPEC_DIR = os.path.abspath(os.environ.get("RM_B200_SPEC_DIR", os.path.join(ROOT, "build", "spec")))
 MAX_SPEC_INSTR = 40          # straight-line code beyond this stops fitting the instruction cache
+MAX_SPEC_INSTR_BWD = int(os.environ.get("RM_B200_SPEC_BWD_LIMIT", "40"))   # backward-only libraries up to here
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
 _PRIM_CALL = {
@@ -167,15 +168,23 @@ __device__ __forceinline__ void eval_spec(const float4* __restrict__ P, const fl
 """
 
 
+def backward_only(tape) -> bool:
+    """Tapes between the two limits get a library with the backward entry points only (the forward
+    keeps the interpreter, which already amortises its decode over 4 rays per thread)."""
+    return MAX_SPEC_INSTR < tape.n_instr <= MAX_SPEC_INSTR_BWD
+
+
 def spec_paths(tape):
     h = code_hash(tape.code)
-    return os.path.join(SPEC_DIR, f"rm_spec_{h:08x}.inc"), os.path.join(SPEC_DIR, f"librm_spec_{h:08x}.so")
+    stem = "librm_specb" if backward_only(tape) else "librm_spec"
+    return os.path.join(SPEC_DIR, f"rm_spec_{h:08x}.inc"), os.path.join(SPEC_DIR, f"{stem}_{h:08x}.so")
 
 
 def build(tape, force: bool = False) -> str:
     """Generates and compiles the specialised library of ``tape`` (cached by structure hash)."""
-    if tape.n_instr > MAX_SPEC_INSTR:
-        raise ValueError(f"tape has {tape.n_instr} instructions; specialisation is for <= {MAX_SPEC_INSTR}")
+    if tape.n_instr > MAX_SPEC_INSTR_BWD:
+        raise ValueError(f"tape has {tape.n_instr} instructions; specialisation is for <= {MAX_SPEC_INSTR} "
+                         f"(forward + backward) or <= {MAX_SPEC_INSTR_BWD} (backward only)")
     inc, lib = spec_paths(tape)
     src = generate_source(tape)
     deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))]
@@ -193,7 +202,8 @@ def build(tape, force: bool = False) -> str:
     cmd = [NVCC, "-shared", "-o", tmp, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo",
            "-std=c++17", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", f'-DRM_SPEC_INC="{inc}"',
            *os.environ.get("RM_B200_SPEC_FLAGS", "").split(),      # launch-shape experiments
-           os.path.join(CSRC, "rm_host.cu"), os.path.join(CSRC, "rm_forward.cu"),
+           os.path.join(CSRC, "rm_host.cu"),
+           *([] if backward_only(tape) else [os.path.join(CSRC, "rm_forward.cu")]),
            os.path.join(CSRC, "rm_backward.cu")]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
@@ -244,8 +254,11 @@ def specialised_lib(tape, build_if_missing: bool = True) -> Optional[C.CDLL]:
         return None
     handle = C.CDLL(path)
     for name in SPEC_EXPORTS:
+        if name == "rm_render" and backward_only(tape):
+            continue
         fn = getattr(handle, name)
         fn.restype, fn.argtypes = _lib._SIGNATURES[name]
+    handle.has_forward = not backward_only(tape)
     handle.rm_last_error.restype = C.c_char_p
     if handle.rm_abi_version() != _lib.ABI_VERSION:
         raise RuntimeError(f"{path}: ABI version mismatch; rebuild")

@@ -320,3 +320,32 @@ def test_inline_rounded_math_is_bit_identical_to_ieee():
             same = same | tiny
         bad = (~same).nonzero().flatten()
         assert bad.numel() == 0, (what, a[bad[:5]], b[bad[:5]], out[mine].cpu()[bad[:5]], out[ref].cpu()[bad[:5]])
+
+
+@pytest.mark.gpu
+def test_half_precision_image_planes_for_transport():
+    """rm_planes_to_f16: binary16 copies of the finalised image planes equal
+    torch's round-to-nearest conversion bit for bit, stay within the 1e-3 pixel tolerance, keep NaNs,
+    handle ray counts that are not multiples of 4, and leave unrequested modes alone."""
+    from ray_marching_b200 import RenderLoop, ops
+    from ray_marching_b200.scene.scene_registry import make_test_scene2
+    PXS = 3.45e-6
+    for w, h in ((61, 33), (64, 48)):
+        loop = RenderLoop(make_test_scene2(), num_cameras=1, px_width=w, px_height=h, focal_length=PXS * h,
+                          sensor_width=PXS * w, sensor_height=PXS * h, normals_eps=5e-2).cuda()
+        q = torch.tensor([[1.0, 0.0, 0.0, 0.0]], device="cuda")
+        t = torch.tensor([[0.0, 0.0, 1.0]], device="cuda")
+        res = loop.render_planes(q, t, modes=(0, 1, 2, 3, 4, 5))
+        mask = 0b111101                                    # every rendered mode but distance (1)
+        half = ops.planes_to_half(res, mask)
+        assert half[1] is None and half[6] is None
+        for m in (0, 2, 3, 4, 5):
+            ref = res.images[m].half()
+            assert half[m].dtype == torch.float16 and half[m].shape == res.images[m].shape
+            same = (half[m].view(torch.int16) == ref.view(torch.int16)) | (torch.isnan(half[m]) & torch.isnan(ref))
+            assert same.all(), m
+            err = (half[m].float() - res.images[m]).abs()
+            assert torch.nan_to_num(err, nan=0.0).max().item() < 1e-3, m
+        assert torch.isnan(half[2]).all()                  # proximity is all-NaN on this scene, as in the reference
+        again = ops.planes_to_half(res, mask, out=half)    # buffers are reused
+        assert all(a is b for a, b in zip(again, half))

@@ -93,8 +93,8 @@ def test_frame_equals_display_frame_and_recaptures_on_parameter_change(tmp_path)
     assert c[..., 3].min().item() == 1.0
 
 
-@pytest.mark.parametrize("specialise", [False, True])
-def test_graphed_optimisation_step_follows_the_eager_trajectory(specialise):
+@pytest.mark.parametrize("specialise,two_graphs", [(False, False), (True, False), (True, True)])
+def test_graphed_optimisation_step_follows_the_eager_trajectory(specialise, two_graphs):
     """frames.GraphedStep: config-4 style inverse rendering (lambertian + depth MSE, Adam on the scene
     parameters and the camera) -- five replays of the captured step against five eager steps from the
     same start (the warm-up steps of the capture must not count)."""
@@ -120,7 +120,6 @@ def test_graphed_optimisation_step_follows_the_eager_trajectory(specialise):
             depth = (gb["pos"] - gb["origin"]).norm(dim=-1, keepdim=True)
             loss = ((lam - lam_t) ** 2).mean() + ((depth - depth_t) ** 2).mean()
             loss.backward()
-            opt.step()
             return loss
         return params, opt, body
 
@@ -129,13 +128,18 @@ def test_graphed_optimisation_step_follows_the_eager_trajectory(specialise):
     for _ in range(5):
         opt.zero_grad(set_to_none=True)
         eager_losses.append(body().item())
+        opt.step()
     eager = torch.cat([p.detach().reshape(-1) for p in params]).clone()
 
     params, opt, body = setup()
-    step = frames.GraphedStep(body, opt)
+    calls = []
+    between = (lambda: calls.append(1)) if two_graphs else None     # stands in for the gradient all-reduce
+    step = frames.GraphedStep(body, opt, between=between)
+    calls.clear()
     graph_losses = [step().item() for _ in range(5)]
     graphed = torch.cat([p.detach().reshape(-1) for p in params])
     assert eager_losses[-1] < eager_losses[0]                       # it optimises
+    assert len(calls) == (5 if two_graphs else 0)
     np.testing.assert_allclose(graph_losses, eager_losses, rtol=1e-4)
     # atomics order differs run to run; Adam's normalised update amplifies that slightly
     assert (graphed - eager).abs().max().item() < 2e-4
