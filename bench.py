@@ -209,8 +209,18 @@ def run_gpu(args):
             ops.shade_finalize(out, mode_mask)
         return out
 
+    # sharded job with a normalising shader: frame i's {8-float MAX all-reduce, finalize} run on a side
+    # stream under the render of frame i+1 (parallel.PipelinedFrames); the timed region ends with every
+    # frame finalised.  --pipeline 0 keeps the collective on the critical path.
+    pipe = None
+    if world > 1 and needs_reduce and args.pipeline and not wl["backward"]:
+        pipe = parallel.PipelinedFrames(loop, modes, marching_steps=STEPS, bounces=wl["bounces"])
+
     def gpu_step():
         """One frame with everything resident in HBM."""
+        if pipe is not None:
+            res_holder["res"] = pipe.submit(q, t)
+            return res_holder["res"]
         res_holder["res"] = frame(q, t, res_holder.get("res"))
         return res_holder["res"]
 
@@ -253,6 +263,8 @@ def run_gpu(args):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         gpu_step()
+        if pipe is not None and _ == args.steps - 1:
+            pipe.wait()                              # the last frame's finalize is inside the timed region
         e1.record()
         evs.append((e0, e1))
     barrier()
@@ -386,6 +398,9 @@ def run_gpu(args):
                        "l2": "flushed between timed iterations (192 MB memset, untimed)",
                        "early_exit": bool(args.early_exit), "cull": bool(args.cull), "tape": tape.describe(),
                        "render_kernel": spec_note,
+                       **({"collective": "8-float MAX all-reduce + finalize of frame i on a side stream under "
+                                         "the render of frame i+1 (parallel.PipelinedFrames)"}
+                          if pipe is not None else {}),
                        **({"step": extra["note"]()} if wl["backward"] else {}),
                        "msteps_per_s": value * STEPS * (wl["bounces"] + 1),
                        "wall_s_timed_region": wall},
@@ -758,6 +773,9 @@ def main():
     ap.add_argument("--graph", type=int, default=1,
                     help="c4 on a registry scene: 1 = the whole optimisation step is one CUDA-graph replay "
                          "(frames.GraphedStep), 0 = eager launches")
+    ap.add_argument("--pipeline", type=int, default=1,
+                    help="N > 1 with a normalising shader: 1 = all-reduce + finalize of frame i overlap the "
+                         "render of frame i+1 (parallel.PipelinedFrames), 0 = in sequence")
     ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "c4", "c4b", "c5"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--early-exit", type=int, default=0,

@@ -143,3 +143,35 @@ def test_graphed_optimisation_step_follows_the_eager_trajectory(specialise, two_
     np.testing.assert_allclose(graph_losses, eager_losses, rtol=1e-4)
     # atomics order differs run to run; Adam's normalised update amplifies that slightly
     assert (graphed - eager).abs().max().item() < 2e-4
+
+
+def test_pipelined_frames_equal_the_plain_sequence():
+    """parallel.PipelinedFrames: the all-reduce + finalize of frame i on a side stream under the render
+    of frame i+1 leaves exactly the planes of the plain render -> finalize sequence (single process:
+    the collective is a no-op, stream ordering and buffer rotation are what is tested)."""
+    from ray_marching_b200 import parallel
+    loop = make_loop(make_test_scene2(), 96, 64)
+    modes = (0, 1, 4, 5)
+    pipe = parallel.PipelinedFrames(loop, modes)
+    poses = []
+    for i in range(5):
+        q = torch.nn.functional.normalize(torch.tensor([[1.0, 0.02 * i, -0.03 * i, 0.01]], device="cuda"), dim=-1)
+        t = torch.tensor([[0.02 * i, 0.0, 1.0 - 0.03 * i]], device="cuda")
+        poses.append((q, t))
+    got = []
+    for q, t in poses:
+        res = pipe.submit(q, t)
+        pipe.wait(res)
+        got.append([res.images[m].clone() for m in modes])
+    # back-to-back without waiting in between: only the last two frames are still in their buffers
+    inflight = [pipe.submit(q, t) for q, t in poses]
+    pipe.wait()
+    torch.cuda.synchronize()
+    for (q, t), planes in zip(poses, got):
+        ref = loop.render_planes(q, t, modes=modes)
+        for m, p in zip(modes, planes):
+            assert torch.equal(torch.nan_to_num(p, nan=-7.0), torch.nan_to_num(ref.images[m], nan=-7.0)), m
+    for (q, t), res in list(zip(poses, inflight))[-2:]:
+        ref = loop.render_planes(q, t, modes=modes)
+        for m in modes:
+            assert torch.equal(torch.nan_to_num(res.images[m], nan=-7.0), torch.nan_to_num(ref.images[m], nan=-7.0)), m
