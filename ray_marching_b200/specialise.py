@@ -187,10 +187,12 @@ def build(tape, force: bool = False) -> str:
                          f"(forward + backward) or <= {MAX_SPEC_INSTR_BWD} (backward only)")
     inc, lib = spec_paths(tape)
     src = generate_source(tape)
-    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))]
-    deps.append(os.path.join(ROOT, "include", "rm_b200.h"))
-    fresh = (os.path.exists(lib) and os.path.exists(inc) and open(inc).read() == src
-             and os.path.getmtime(lib) >= max(os.path.getmtime(p) for p in deps))
+    # freshness by CONTENT (file times do not survive a copy to another machine): digest of the
+    # generated header, every kernel source and the extra flags, kept beside the library
+    digest = _source_digest(src)
+    stamp = lib + ".digest"
+    fresh = (os.path.exists(lib) and os.path.exists(inc) and os.path.exists(stamp)
+             and open(stamp).read().strip() == digest and open(inc).read() == src)
     if fresh and not force:
         return lib
     if not os.path.exists(NVCC):
@@ -209,7 +211,22 @@ def build(tape, force: bool = False) -> str:
     if res.returncode != 0:
         raise RuntimeError("nvcc failed for the specialised library:\n" + res.stdout + res.stderr)
     os.replace(tmp, lib)
+    with open(stamp, "w") as f:
+        f.write(digest + "\n")
     return lib
+
+
+def _source_digest(generated: str) -> str:
+    import hashlib
+    h = hashlib.sha1()
+    h.update(generated.encode())
+    h.update(os.environ.get("RM_B200_SPEC_FLAGS", "").encode())
+    deps = sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h")))
+    deps.append(os.path.join(ROOT, "include", "rm_b200.h"))
+    for path in deps:
+        with open(path, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
 
 
 _loaded = {}

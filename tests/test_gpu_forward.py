@@ -349,3 +349,20 @@ def test_half_precision_image_planes_for_transport():
         assert torch.isnan(half[2]).all()                  # proximity is all-NaN on this scene, as in the reference
         again = ops.planes_to_half(res, mask, out=half)    # buffers are reused
         assert all(a is b for a, b in zip(again, half))
+
+
+@pytest.mark.gpu
+def test_planes_to_f16_argument_errors():
+    import ctypes as C
+    from ray_marching_b200 import _lib
+    lib = _lib.lib()
+    stream = torch.cuda.current_stream().cuda_stream
+    src = (C.c_void_p * 8)()
+    dst = (C.c_void_p * 8)()
+    out = torch.empty(4, dtype=torch.float16, device="cuda")
+    dst[0] = out.data_ptr()
+    assert lib.rm_planes_to_f16(1, 4, src, dst, stream) != 0            # mode 0 asked for, source plane missing
+    assert b"image[0] is null" in lib.rm_last_error()
+    assert lib.rm_planes_to_f16(1, -1, src, dst, stream) != 0
+    assert lib.rm_planes_to_f16(0, 4, src, dst, stream) == 0            # nothing requested: no launch
+    assert lib.rm_planes_to_f16(1, 0, src, dst, stream) != 0            # still validates the table

@@ -190,3 +190,23 @@ def test_specialised_march_and_sdf_vjp_follow_the_selection():
     got = run()
     for g, r in zip(got, ref):
         assert _rel(g, r) < 2e-4
+
+
+def test_specialised_backward_refuses_another_tape():
+    """The backward entry points of a specialised library check the structure hash too."""
+    import ctypes as C
+    from ray_marching_b200 import ops, specialise as SP
+    from ray_marching_b200.tape import tape_of
+    loop_a = make_loop(make_test_scene2(), 16, 16).specialise()
+    handle = tape_of(loop_a.scene).spec_lib
+    other = tape_of(make_loop(make_test_scene(), 16, 16).scene)
+    par = other.lowered_params("cuda")
+    t = ops._tape_struct(other.code_tensor("cuda"), par, other.n_nodes, other.max_depth)
+    pts = torch.zeros(8, 3, device="cuda")
+    g = torch.ones(8, device="cuda")
+    dpts, dpar = torch.empty_like(pts), torch.empty_like(par)
+    st = handle.rm_sdf_vjp(C.byref(t), pts.data_ptr(), g.data_ptr(), 8, dpts.data_ptr(), dpar.data_ptr(),
+                           torch.cuda.current_stream().cuda_stream)
+    assert st != 0 and b"specialised for another tape" in handle.rm_last_error()
+    with pytest.raises(_lib.RmError, match="specialised"):
+        SP.spec_check(handle, st, "rm_sdf_vjp")
