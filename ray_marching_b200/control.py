@@ -91,6 +91,28 @@ class RenderLoop(nn.Module):
                                  marching_steps=marching_steps)
         return res.rgba.reshape(self.px_height, self.px_width, 4)
 
+    def supersampled(self, orientations: Tensor, translations: Tensor, mode: int = 0, factor: int = 2,
+                     degree: int = 1, marching_steps: int = 32) -> Tensor:
+        """``factor`` x ``factor`` rays per pixel, box-filtered (the reference's TODO "supersampling",
+        README.md:246).  The sub-pixel rays are the pixel centres of a sensor of the
+        same size with ``factor`` times the resolution -- the closed form of ``PinholeCamera`` at
+        ``(factor W, factor H)`` -- marched and shaded by the same fused kernel (normalising shaders take
+        their range over all sub-pixel rays), then averaged per pixel.  ``(N,H,W,3)``, no autograd."""
+        if factor < 1:
+            raise ValueError("factor must be >= 1")
+        N, H, W = self.camera.num_cameras, self.px_height, self.px_width
+        cam = ops.camera_struct(N, W * factor, H * factor, self.camera.focal_length,
+                                self.camera.sensor_width, self.camera.sensor_height)
+        m = mode % 8
+        poses = ops.pose_records(orientations, translations)
+        res = ops.render(tape_of(self.scene), cam, poses, steps=marching_steps,
+                         normals_eps=self.normals.normals_eps, mode_mask=1 << m, degree=degree,
+                         early_exit=self.early_exit,
+                         fast_math=2 if (self.fast_math and self.cull) else int(self.fast_math),
+                         cmap=self.shader.cyclic_cmap)
+        fine = res.images[m].reshape(N, H, factor, W, factor, -1)
+        return fine.mean(dim=(2, 4)).expand(-1, H, W, 3)
+
     # ---- reference signature --------------------------------------------------------------
     def forward(self, orientations: Tensor, translations: Tensor, mode: int = 0, degree: int = 1,
                 marching_steps: int = 32):

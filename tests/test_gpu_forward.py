@@ -366,3 +366,28 @@ def test_planes_to_f16_argument_errors():
     assert lib.rm_planes_to_f16(1, -1, src, dst, stream) != 0
     assert lib.rm_planes_to_f16(0, 4, src, dst, stream) == 0            # nothing requested: no launch
     assert lib.rm_planes_to_f16(1, 0, src, dst, stream) != 0            # still validates the table
+
+
+@pytest.mark.gpu
+def test_supersampled_frame_is_the_box_filter_of_the_fine_camera():
+    """RenderLoop.supersampled: factor^2 rays per pixel = the oracle's PinholeCamera at
+    factor x the resolution on the same sensor, shaded, then averaged per pixel."""
+    from oracle import sdf_oracle as O
+    from ray_marching_b200 import RenderLoop
+    from ray_marching_b200.scene.scene_registry import make_test_scene2
+    PXS, W, H, F = 3.45e-6, 40, 24, 3
+    intr = dict(num_cameras=1, focal_length=PXS * H, sensor_width=PXS * W, sensor_height=PXS * H)
+    loop = RenderLoop(make_test_scene2(), px_width=W, px_height=H, normals_eps=5e-2, **intr).cuda()
+    q = torch.nn.functional.normalize(torch.tensor([[0.99, 0.03, -0.08, 0.05]]), dim=-1)
+    t = torch.tensor([[0.05, 0.1, 1.0]])
+    orc = O.RenderLoopOracle(make_test_scene2(), px_width=W * F, px_height=H * F, normals_eps=5e-2, **intr)
+    for mode in (0, 4):
+        got = loop.supersampled(q.cuda(), t.cuda(), mode=mode, factor=F)
+        assert got.shape == (1, H, W, 3)
+        with torch.no_grad():
+            fine = orc(q, t, mode, 1, 32)                                   # (1, H F, W F, 3)
+        want = fine.reshape(1, H, F, W, F, 3).mean(dim=(2, 4))
+        assert (got.cpu() - want).abs().max().item() < 1e-3, mode
+    with torch.no_grad():                              # the fused path (autograd on takes the G-buffer route)
+        one = loop.supersampled(q.cuda(), t.cuda(), mode=0, factor=1)
+        assert torch.equal(one, loop(q.cuda(), t.cuda(), 0))
