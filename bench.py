@@ -344,6 +344,30 @@ def run_gpu(args):
                                "RenderLoop; the headline uses RenderLoop.specialise())"}
         loop.specialise(True)
 
+    # the same frame with the march loop's bit-identical fixed-point exit (a ray whose position stops
+    # changing reproduces itself; the loop ends when the whole warp is there): executed < algorithmic
+    # work, so it is reported beside the fully marched headline, without a roofline fraction
+    exit_info = None
+    if not wl["backward"] and not loop.early_exit:
+        loop.early_exit = True
+        for _ in range(3):
+            gpu_step()
+        torch.cuda.synchronize()
+        ys = []
+        for _ in range(max(3, min(args.steps, 20))):
+            flush.zero_()
+            ye0, ye1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ye0.record()
+            gpu_step()
+            ye1.record()
+            ye1.synchronize()
+            ys.append(ye0.elapsed_time(ye1))
+        loop.early_exit = False
+        y_ms = sum(ys) / len(ys)
+        exit_info = {"ms_per_step": y_ms, "value": rays / (y_ms * 1e-3) / 1e6, "unit": "Mrays/s",
+                     "note": "per-GPU, RenderLoop.early_exit = True: output bit-identical to the fully "
+                             "marched frame (tests); executed < algorithmic work, no roofline fraction"}
+
     # the same frame as ONE CUDA-graph replay (reduce init + render + finalize captured once, the way
     # ray_marching_b200.frames.FrameLoop runs a display loop): c1 is launch-latency scale
     graph_info = None
@@ -416,6 +440,8 @@ def run_gpu(args):
                 "note": "rank 0's own loop (per GPU): the e2e loop with binary16 image planes on the wire "
                         "(rm_planes_to_f16, float32 arithmetic, pixels exact to 2.4e-4); the headline "
                         "e2e keeps the reference's float32 planes"}
+        if exit_info is not None:
+            line["early_exit"] = exit_info
         if interp_info is not None:
             line["interpreter"] = interp_info
         if graph_info is not None:

@@ -200,8 +200,9 @@ def test_specialised_backward_refuses_another_tape():
     loop_a = make_loop(make_test_scene2(), 16, 16).specialise()
     handle = tape_of(loop_a.scene).spec_lib
     other = tape_of(make_loop(make_test_scene(), 16, 16).scene)
-    par = other.lowered_params("cuda")
-    t = ops._tape_struct(other.code_tensor("cuda"), par, other.n_nodes, other.max_depth)
+    with torch.no_grad():
+        par = other.lowered_params()
+    t = ops._tape_struct(other.code_tensor(), par, other.n_nodes, other.max_depth)
     pts = torch.zeros(8, 3, device="cuda")
     g = torch.ones(8, device="cuda")
     dpts, dpar = torch.empty_like(pts), torch.empty_like(par)
@@ -210,3 +211,16 @@ def test_specialised_backward_refuses_another_tape():
     assert st != 0 and b"specialised for another tape" in handle.rm_last_error()
     with pytest.raises(_lib.RmError, match="specialised"):
         SP.spec_check(handle, st, "rm_sdf_vjp")
+
+
+def test_specialised_early_exit_is_bit_identical():
+    """The specialised kernel has two march loops (with and without the fixed-point test): same planes."""
+    loop = make_loop(make_test_scene2(), 128, 72).specialise()
+    q = torch.nn.functional.normalize(torch.tensor([[0.98, 0.05, -0.1, 0.02]], device="cuda"), dim=-1)
+    t = torch.tensor([[0.0, 0.0, 1.0]], device="cuda")
+    full = loop.render_planes(q, t, gbuffer=True, modes=(0, 4, 5))
+    keep = [x.clone() for x in (full.pos, full.sdf, full.normals, full.laplacian, full.images[0], full.images[5])]
+    loop.early_exit = True
+    fast = loop.render_planes(q, t, gbuffer=True, modes=(0, 4, 5))
+    for a, b in zip(keep, (fast.pos, fast.sdf, fast.normals, fast.laplacian, fast.images[0], fast.images[5])):
+        assert torch.equal(torch.nan_to_num(a, nan=-7.0), torch.nan_to_num(b, nan=-7.0))
