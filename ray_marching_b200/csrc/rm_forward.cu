@@ -29,12 +29,16 @@
 #define RM_MINB 4
 #endif
 
+#ifndef RM_SPEC_UNROLL
+#define RM_SPEC_UNROLL 2        // march-loop unrolling of the tape-specialised kernel
+#endif
 #ifndef RM_PERSIST
 #define RM_PERSIST 0            // 1: persistent balanced tiling in render_kernel (measured slower: profiles/r01/variants.md)
 #endif
 
 namespace rm {
 
+constexpr int SPEC_UNROLL = RM_SPEC_UNROLL;
 constexpr int K = RM_K;         // rays per thread (multiple of 4: float4 plane I/O)
 constexpr int BLOCK = RM_BLOCK; // threads per block
 
@@ -213,7 +217,7 @@ __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_inst
     // fixed-point test below (12 compares, the old/new register rotation, a vote) would be ~15 % of
     // the loop even when predicated off.  Launches without early exit take this loop instead.
     if (!CULL && !early_exit) {
-#pragma unroll 2
+#pragma unroll SPEC_UNROLL
         for (int s = 0; s < steps; ++s) {
             eval_scene<K, FAST, CAP, 0>(code, n_instr, spar, px, py, pz, d);
 #pragma unroll
