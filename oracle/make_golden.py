@@ -201,6 +201,90 @@ def gen_grads(ref, out):
              for (_, p), gp in zip(params, grads2[2:])]))
 
 
+def gen_grads_c4b(ref, out):
+    """Config-4b: the same loss on synthetic-64 inside the shell (642 + 8 parameters), 32x32, through
+    the reference's unrolled autograd graph -- pins the fused backward kernel on the large tape."""
+    W = H = 32
+    intr = cases.config1_camera(W, H)
+    scene = make_synthetic_scene(64, 0, True, classes=ref)
+    loop = ref.RenderLoop(scene, normals_eps=5e-2, **intr)
+    q = torch.nn.functional.normalize(torch.tensor([[0.98, 0.05, -0.12, 0.08]]), dim=-1)
+    t = torch.tensor([[0.0, 0.0, -4.0]])
+
+    def gbuf(q, t):
+        px, frames, pos0, dirs = loop.camera(q, t)
+        pos = loop.marcher(pos0, dirs, 32)
+        normals, lap = loop.normals(pos)
+        lam = (dirs * normals).sum(-1, keepdim=True).neg().clamp(0, 1)
+        depth = (pos - px).norm(dim=-1, keepdim=True)
+        return lam, depth
+
+    params = param_list(scene)
+    saved = [p.detach().clone() for _, p in params]
+    g = torch.Generator().manual_seed(1)
+    with torch.no_grad():
+        for _, p in params:
+            p.add_(0.05 * torch.randn(p.shape, generator=g))
+        lam_t, depth_t = gbuf(q, t)
+        for (_, p), s in zip(params, saved):
+            p.copy_(s)
+    q = q.clone().requires_grad_(True)
+    t = t.clone().requires_grad_(True)
+    lam, depth = gbuf(q, t)
+    loss = ((lam - lam_t) ** 2).mean() + ((depth - depth_t) ** 2).mean()
+    grads = torch.autograd.grad(loss, [q, t] + [p for _, p in params], allow_unused=True)
+    out["grads/syn64/q"] = np32(q)
+    out["grads/syn64/t"] = np32(t)
+    out["grads/syn64/lam_target"] = np32(lam_t)
+    out["grads/syn64/depth_target"] = np32(depth_t)
+    out["grads/syn64/lam"] = np32(lam)
+    out["grads/syn64/depth"] = np32(depth)
+    out["grads/syn64/loss"] = np32(loss)
+    out["grads/syn64/dq"] = np32(grads[0])
+    out["grads/syn64/dt"] = np32(grads[1])
+    out["grads/syn64/dparams_flat"] = np32(torch.cat(
+        [(gp if gp is not None else torch.zeros_like(p)).reshape(-1)
+         for (_, p), gp in zip(params, grads[2:])]))
+
+
+def gen_api_surface(ref):
+    """Parameter names of every drop-in class's ``__init__`` / ``forward`` and the ``state_dict``
+    keys / shapes / dtypes of a reference ``RenderLoop``: the boundary, pinned."""
+    import inspect
+    import json
+    classes = {}
+    table = {name: getattr(ref, name) for name in dir(ref) if name.startswith("SDF")}
+    table.update(PinholeCamera=ref.RM.PinholeCamera, SDFMarcher=ref.RM.SDFMarcher,
+                 SDFNormals=ref.RM.SDFNormals, Shader=ref.SH.Shader,
+                 QuaternionToSO3=ref.Q.QuaternionToSO3)
+    loop1 = ref.RenderLoop(ref.SR.make_test_scene2(), 1, 8, 6, 1e-3, 2e-3, 1.5e-3, 5e-2)
+    table["RenderLoop"] = type(loop1)
+    for name, cls in sorted(table.items()):
+        classes[name] = {"init": list(inspect.signature(cls.__init__).parameters),
+                         "forward": list(inspect.signature(cls.forward).parameters),
+                         "init_defaults": {k: v.default for k, v in inspect.signature(cls.__init__).parameters.items()
+                                           if v.default is not inspect.Parameter.empty
+                                           and isinstance(v.default, (int, float, str, bool))},
+                         "forward_defaults": {k: v.default for k, v in inspect.signature(cls.forward).parameters.items()
+                                              if v.default is not inspect.Parameter.empty
+                                              and isinstance(v.default, (int, float, str, bool))}}
+    functions = {}
+    for name in ("cross_product", "multiply", "conjugate", "rotation", "to_versor"):
+        functions[f"quaternion.{name}"] = list(inspect.signature(getattr(ref.Q, name)).parameters)
+    functions["control.make_reflection_directions"] = list(
+        inspect.signature(ref.make_reflection_directions).parameters)
+    functions["scene_registry.make_test_scene"] = list(inspect.signature(ref.SR.make_test_scene).parameters)
+    functions["scene_registry.make_test_scene2"] = list(inspect.signature(ref.SR.make_test_scene2).parameters)
+    state = {}
+    for tag, loop in (("scene2_n1_8x6", loop1),
+                      ("scene1_n2_8x6", ref.RenderLoop(ref.SR.make_test_scene(), 2, 8, 6, 1e-3, 2e-3, 1.5e-3, 5e-2))):
+        state[tag] = [[k, list(v.shape), str(v.dtype)] for k, v in loop.state_dict().items()]
+    path = os.path.join(OUT, "api_surface.json")
+    with open(path, "w") as f:
+        json.dump({"classes": classes, "functions": functions, "state_dict": state}, f, indent=1, sort_keys=True)
+    print(f"{path}: {len(classes)} classes, {len(functions)} functions")
+
+
 def gen_camera_path(ref, out):
     """A scripted 24-frame path of 3 cameras through control.py:148-165 (the reference's own source)."""
     import types
@@ -233,13 +317,21 @@ def main():
     torch.set_num_threads(1)          # deterministic reduction order
     ref = ref_import.load()
     os.makedirs(OUT, exist_ok=True)
+    only = set(sys.argv[1:])          # e.g. `python -m oracle.make_golden api grads_c4b`
+    if not only or "api" in only:
+        gen_api_surface(ref)
     for name, fn in (("quaternion", gen_quaternion), ("nodes", gen_nodes), ("camera", gen_camera),
-                     ("render", gen_render), ("grads", gen_grads), ("camera_path", gen_camera_path)):
+                     ("render", gen_render), ("grads", gen_grads), ("grads_c4b", gen_grads_c4b),
+                     ("camera_path", gen_camera_path)):
+        if only and name not in only:
+            continue
         out = {}
         fn(ref, out)
         path = os.path.join(OUT, f"{name}.npz")
         np.savez_compressed(path, **out)
         print(f"{path}: {len(out)} arrays, {os.path.getsize(path)/1024:.1f} KiB")
+    if only:
+        return
     cmap = ref.shader.cyclic_cmap.contiguous().numpy().astype(np.float32)
     # the colour LUT is an *input* of the tangent/spin shaders (data/cyclic_cmap.pt, (4096,3) f64,
     # loaded at shader.py:177); kept as a float32 data asset so the GPU box has it

@@ -94,7 +94,9 @@ def lib() -> C.CDLL:
     """Loads (building first if needed) the shared library; raises if that is impossible."""
     global _lib
     if _lib is None:
-        if not os.path.exists(LIB_PATH):
+        if not os.environ.get("RM_B200_LIB"):
+            # (re)build when the library is missing or its sources changed (content digest kept
+            # beside the .so); an alternative build named by RM_B200_LIB is taken as is
             from .csrc.build import build
             build()
         handle = C.CDLL(LIB_PATH)

@@ -201,7 +201,7 @@ __global__ void camera_update_kernel(float* __restrict__ poses, const float* __r
 
 // ---- the march loop (ray_marching.py:78-84): p <- f(p) v + p --------------------------------
 // CULL: see eval_scene.  The union value of the previous step and the step length bound the union
-// value at the new position (|v| = 1, so the ray moved |f(p)|).
+// value at the new position (the ray moved |f(p)| |v|).
 template <bool FAST, int CAP, bool CULL>
 __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                            int steps, bool early_exit,
@@ -209,9 +209,13 @@ __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_inst
                                            const float (&vx)[K], const float (&vy)[K],
                                            const float (&vz)[K]) {
     float d[K];
-    float hint[CULL ? K : 1], move[CULL ? K : 1];
+    float hint[CULL ? K : 1], move[CULL ? K : 1], vlen[CULL ? K : 1];
 #pragma unroll
-    for (int k = 0; k < (CULL ? K : 1); ++k) { hint[k] = CUDART_INF_F; move[k] = 0.f; }
+    for (int k = 0; k < (CULL ? K : 1); ++k) {
+        hint[k] = CUDART_INF_F; move[k] = 0.f;
+        // the ray moves |f(p)| |v| per step: rm_march accepts directions of any length
+        vlen[k] = CULL ? sqrt_rn_inline(fmaf(vx[k], vx[k], fmaf(vy[k], vy[k], vz[k] * vz[k]))) * 1.0001f : 0.f;
+    }
 #ifdef RM_SPEC_INC
     // Tape-specialised build: the evaluation is a few dozen straight-line instructions, so the
     // fixed-point test below (12 compares, the old/new register rotation, a vote) would be ~15 % of
@@ -240,7 +244,7 @@ __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_inst
             const float nz = fmaf(d[k], vz[k], pz[k]);
             if (early_exit) moved |= (nx != px[k]) | (ny != py[k]) | (nz != pz[k]);
             px[k] = nx; py[k] = ny; pz[k] = nz;
-            if (CULL) move[CULL ? k : 0] = fabsf(d[k]) * 1.0001f;   // |v| = 1 up to rounding
+            if (CULL) move[CULL ? k : 0] = fabsf(d[k]) * vlen[CULL ? k : 0];
         }
         // A ray whose position did not change is at a fixed point of the update: all further
         // steps reproduce it bit for bit, so leaving the loop (when the whole warp is there) does
@@ -257,7 +261,8 @@ march_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n
     extern __shared__ __align__(16) unsigned char smem[];
     const float4* spar = stage_params(par, n_par, smem);
     const int64_t first = ((int64_t)blockIdx.x * BLOCK + threadIdx.x) * K;
-    if (first >= n) return;
+    // no early return for tail threads: the culling interpreter votes with a full-warp mask; lanes
+    // past the end march zero rays (load3 pads with zeros) and store nothing
     float px[K], py[K], pz[K], vx[K], vy[K], vz[K];
     load3(origin, first, n, px, py, pz);
     load3(dirs, first, n, vx, vy, vz);

@@ -41,10 +41,11 @@ class CameraPath:
     orientation)``; ``orientation = normalize(Q.multiply(orientation, Q.to_versor(orientation_input
     * rotation_sensitivity)))``).  With ``script`` -- a ``(frames, N, 6)`` tensor of
     ``(translation_input, orientation_input)`` rows -- every :meth:`advance` applies the next row of
-    the script, indexed by a device-side counter, so it can be replayed from inside a CUDA graph."""
+    the script, indexed by a device-side counter, so it can be replayed from inside a CUDA graph.
+    The sensitivities default to ``EventAggregator``'s (``control.py:30-31``: 0.1 and 0.25)."""
 
-    def __init__(self, initial_position, initial_orientation, *, translation_sensitivity: float = 0.05,
-                 rotation_sensitivity: float = 0.05, script: Optional[Tensor] = None, device="cuda"):
+    def __init__(self, initial_position, initial_orientation, *, translation_sensitivity: float = 0.1,
+                 rotation_sensitivity: float = 0.25, script: Optional[Tensor] = None, device="cuda"):
         device = torch.device(device)
         if device.type != "cuda":
             raise _lib.RmError("CameraPath integrates on the GPU; there is no CPU path")
@@ -143,7 +144,13 @@ class FrameLoop:
         else:
             with torch.no_grad():                 # the cached lowering (no autograd graph), as ops.render uses
                 par = tape_of(self.loop.scene).lowered_params(self.path.poses.device)
-            key = (par.data_ptr(), par._version, scripted, self.mode, self.degree, self.marching_steps)
+            # everything _launch bakes into the captured kernel arguments
+            loop, cam = self.loop, self.loop.camera
+            key = (par.data_ptr(), par._version, scripted, self.mode, self.degree, self.marching_steps,
+                   bool(loop.early_exit), bool(loop.fast_math), bool(loop.cull),
+                   id(getattr(tape_of(loop.scene), "spec_lib", None)), float(loop.normals.normals_eps),
+                   cam.num_cameras, cam.px_width, cam.px_height, float(cam.focal_length),
+                   float(cam.sensor_width), float(cam.sensor_height))
             if self._graph is None or key != self._key:
                 self._capture(scripted)
                 self._key, self._par = key, par        # holding `par` keeps its address from being reused

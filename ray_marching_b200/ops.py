@@ -178,6 +178,18 @@ def render(tape, cam: RmCamera, poses: Tensor, *, steps: int = 32, normals_eps: 
         n = total - ray_begin if n_rays is None else n_rays
         res = out or RenderResult()
         new = lambda *shape: torch.empty(*shape, device=dev, dtype=torch.float32)
+        if out is not None:
+            # planes reused from an earlier call must fit THIS ray range (the C ABI sees no sizes)
+            for name in ("origin", "dirs", "pos", "sdf", "normals", "laplacian", "rgba"):
+                t = getattr(res, name)
+                if t is not None and (t.shape[0] != n or t.device != dev):
+                    setattr(res, name, None)
+            for m in range(8):
+                t = res.images[m]
+                if t is not None and (t.shape[0] != n or t.device != dev):
+                    res.images[m] = None
+            if res.reduce is not None and res.reduce.device != dev:
+                res.reduce = None
         if gbuffer:
             res.origin = res.origin if res.origin is not None else new(n, 3)
             res.dirs = res.dirs if res.dirs is not None else new(n, 3)

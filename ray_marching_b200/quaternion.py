@@ -68,6 +68,11 @@ class QuaternionToSO3(nn.Module):
 
     Differs from :func:`rotation_matrix` for non-unit q (diagonal uses ``ww+xx-yy-zz``)."""
 
+    def __init__(self):
+        super().__init__()
+        # the reference's index buffer (quaternion.py:107-112); kept so state_dict keys match
+        self.register_buffer("pairs", torch.tensor([(i, j) for i in range(4) for j in range(i, 4)]))
+
     def forward(self, q: Tensor) -> Tensor:
         w, x, y, z = q.unbind(-1)
         m = torch.stack([

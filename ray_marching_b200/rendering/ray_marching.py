@@ -35,12 +35,64 @@ class PinholeCamera(nn.Module):
         self.sensor_height = sensor_height
         self.size = (num_cameras, 1, px_height, px_width)
         self.px_width, self.px_height = px_width, px_height
+        # the reference's small buffers (ray_marching.py:26-39,51-54), same names / shapes (stored
+        # contiguous: the reference's expanded views cannot be written by load_state_dict for N > 1)
+        self.register_buffer("focus", torch.tensor([[[[0., 0., -focal_length]]]]).expand(num_cameras, 1, 1, 3).clone())
+        self.register_buffer("theta", torch.tensor([[[sensor_width / 2, 0., 0.],
+                                                     [0., -sensor_height / 2, 0.]]]).expand(num_cameras, 2, 3).clone())
+        self.register_buffer("pixel_frames",
+                             torch.eye(3)[None, None, None, [0, 1], :].expand(num_cameras, 1, 1, 2, 3).clone())
         self.quaternion_to_so3 = Q.QuaternionToSO3()
         self._base = None
+        # `ray_positions` / `ray_directions` (ray_marching.py:40-50) are 24 B/ray of state the kernels
+        # never read (rays come from the pixel index): they are not held as buffers, but state_dict()
+        # carries them (materialised on demand) and load_state_dict() accepts them, so checkpoints
+        # move between the reference and this module with strict=True in both directions.
+        self._register_state_dict_hook(PinholeCamera._emit_ray_buffers)
+        self._register_load_state_dict_pre_hook(self._accept_ray_buffers)
 
     def struct(self):
         return ops.camera_struct(self.num_cameras, self.px_width, self.px_height,
                                  self.focal_length, self.sensor_width, self.sensor_height)
+
+    def closed_form_rays(self, device=None):
+        """The reference's ``ray_positions`` / ``ray_directions`` buffers from their closed form
+        (SURVEY.md 8(a) C1), in plain torch on any device: pixel (row i, col j) ->
+        ``(sw/2 ((2j+1)/W - 1), -sh/2 ((2i+1)/H - 1), 0)``, ``dir = normalize(pos - focus)``."""
+        N, H, W = self.num_cameras, self.px_height, self.px_width
+        device = device if device is not None else self.focus.device
+        gx = (2 * torch.arange(W, device=device, dtype=torch.float32) + 1) / W - 1
+        gy = (2 * torch.arange(H, device=device, dtype=torch.float32) + 1) / H - 1
+        x = (self.sensor_width / 2 * gx)[None, :].expand(H, W)
+        y = (-self.sensor_height / 2 * gy)[:, None].expand(H, W)
+        pos = torch.stack([x, y, torch.zeros_like(x)], dim=-1)[None].expand(N, H, W, 3).contiguous()
+        rel = pos - self.focus.to(device)
+        return pos, rel / rel.norm(dim=-1, keepdim=True)
+
+    @staticmethod
+    def _emit_ray_buffers(module, state_dict, prefix, local_metadata):
+        pos, dirs = module.closed_form_rays()
+        # keep the reference's key order: focus, theta, ray_positions, ray_directions, pixel_frames, ...
+        items = list(state_dict.items())
+        state_dict.clear()
+        for k, v in items:
+            if k == prefix + "pixel_frames":
+                state_dict[prefix + "ray_positions"] = pos
+                state_dict[prefix + "ray_directions"] = dirs
+            state_dict[k] = v
+        return state_dict
+
+    def _accept_ray_buffers(self, state_dict, prefix, local_metadata, strict, missing_keys,
+                            unexpected_keys, error_msgs):
+        shape = (self.num_cameras, self.px_height, self.px_width, 3)
+        for name in ("ray_positions", "ray_directions"):
+            t = state_dict.pop(prefix + name, None)
+            if t is None:
+                if strict:
+                    missing_keys.append(prefix + name)
+            elif tuple(t.shape) != shape:
+                error_msgs.append(f"size mismatch for {prefix + name}: copying a param with shape "
+                                  f"{tuple(t.shape)} from checkpoint, the shape in current model is {shape}.")
 
     def base_rays(self, device):
         """Camera-frame rays (the reference's ``ray_positions`` / ``ray_directions`` buffers),

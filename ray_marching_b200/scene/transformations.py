@@ -7,8 +7,17 @@ carry over.  Evaluation goes through the lowered tape, see :class:`SDFNode`.
 from __future__ import annotations
 
 import torch.nn as nn
+from torch import Tensor
 
 from ._node import SDFNode
+
+
+class _CoordsNode(SDFNode):
+    """The four value combinators name their ``forward`` argument ``query_coords`` in the reference
+    (``transformations.py:67,90,117,131``); keyword callers must keep working."""
+
+    def forward(self, query_coords: Tensor) -> Tensor:     # noqa: D102 - see SDFNode.forward
+        return SDFNode.forward(self, query_coords)
 
 
 class SDFAffineTransformation(SDFNode):
@@ -26,7 +35,7 @@ class SDFAffineTransformation(SDFNode):
         self._param(tuple(orientation), "orientation")
 
 
-class SDFSmoothUnion(SDFNode):
+class SDFSmoothUnion(_CoordsNode):
     """``-(1/k) logsumexp_i(-k f_i)`` over the children (``transformations.py:45-71``)."""
     kind = "SDFSmoothUnion"
 
@@ -36,7 +45,7 @@ class SDFSmoothUnion(SDFNode):
         self._param(blend_k, "blend_k")
 
 
-class SDFUnion(SDFNode):
+class SDFUnion(_CoordsNode):
     """``min_i f_i`` over the children (``transformations.py:74-94``)."""
     kind = "SDFUnion"
 
@@ -45,7 +54,7 @@ class SDFUnion(SDFNode):
         self.sdfs = nn.ModuleList(sdfs)
 
 
-class SDFRounding(SDFNode):
+class SDFRounding(_CoordsNode):
     """``child(p) - rounding`` (``transformations.py:97-118``)."""
     kind = "SDFRounding"
 
@@ -55,7 +64,7 @@ class SDFRounding(SDFNode):
         self._param(rounding, "rounding")
 
 
-class SDFOnion(SDFNode):
+class SDFOnion(_CoordsNode):
     """``|child(p)| - radius`` (``transformations.py:121-132``)."""
     kind = "SDFOnion"
 

@@ -233,24 +233,29 @@ _loaded = {}
 # entry points a specialised library exports besides rm_abi_version / rm_last_error
 SPEC_EXPORTS = ("rm_render", "rm_render_bwd", "rm_march_bwd", "rm_sdf_vjp", "rm_bwd_scratch_floats")
 
-# Libraries selected by RenderLoop.specialise(), keyed by the tape's code bytes: the autograd ops
-# (ops.py: render_gbuffer / render_bwd) receive the code tensor, not the Tape object.
+# Libraries selected by RenderLoop.specialise(), per TAPE OBJECT: the autograd ops (ops.py:
+# render_gbuffer / render_bwd) receive the tape's host code tensor, not the Tape, so the key is that
+# tensor's address (owned by the tape for its whole life; the entry dies with the tape).  Two
+# RenderLoops over scenes of the same structure hold different tapes and choose independently.
 _selected = {}
 
 
 def select(tape, handle: Optional[C.CDLL]) -> None:
-    key = np.ascontiguousarray(tape.code, dtype=np.int32).tobytes()
+    import weakref
+    key = tape.code_tensor().data_ptr()
     if handle is None:
         _selected.pop(key, None)
-    else:
-        _selected[key] = handle
+        return
+    if key not in _selected:
+        weakref.finalize(tape, _selected.pop, key, None)
+    _selected[key] = handle
 
 
 def selected_for(code) -> Optional[C.CDLL]:
-    """The specialised library selected for this code block (a host int32 tensor), or None."""
+    """The specialised library selected for the tape this code block (a host int32 tensor) belongs to."""
     if not _selected:
         return None
-    return _selected.get(code.numpy().tobytes())
+    return _selected.get(code.data_ptr())
 
 
 def spec_check(handle: C.CDLL, status: int, what: str) -> None:

@@ -413,16 +413,25 @@ class Tape:
             union = torch.stack([smin_all, lmax, theta.new_tensor(math.log2(max(self._cull_n, 1)))])
             return [rec, union]
 
+    def invalidate(self) -> None:
+        """Drops the cached lowering.  Needed only after writes autograd cannot see -- in-place
+        writes through ``p.data`` (``p.data.fill_(..)``, ``p.data.clamp_(..)``) share the storage but
+        not the version counter.  Optimiser steps, ``load_state_dict``, ``p.copy_()`` under
+        ``no_grad`` and ``p.data = x`` are detected without this."""
+        self._par_cache = None
+
     def lowered_params(self, device=None) -> torch.Tensor:
         """Current ``par`` on the parameters' device (``device`` only matters for a scene
         without parameters).  Cached while no parameter changes and autograd is off (a static
-        scene under a moving camera costs nothing per frame)."""
+        scene under a moving camera costs nothing per frame).  The cache key is every parameter's
+        version counter AND storage address; see :meth:`invalidate` for the one kind of write it
+        cannot see."""
         if self.params and device is not None and torch.device(device) != self.device:
             raise RuntimeError(f"scene parameters live on {self.device} but the query is on "
                                f"{device}; move the scene with .to(device)")
         track = torch.is_grad_enabled() and any(p.requires_grad for p in self.params)
         if not track:
-            key = tuple(p._version for p in self.params) + (str(device or self.device),)
+            key = (tuple((p._version, p.data_ptr()) for p in self.params), str(device or self.device))
             if self._par_cache is not None and self._par_cache[0] == key:
                 return self._par_cache[1]
             with torch.no_grad():

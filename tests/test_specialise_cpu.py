@@ -57,3 +57,22 @@ def test_specialised_translation_unit_compiles(tmp_path, monkeypatch):
         assert f" {name}\n" in out, name
     assert " rm_march\n" not in out and " rm_sdf_eval" not in out          # no stand-alone forward ops
     assert SP.build(tape_of(nested_scene())) == lib                          # cached
+
+
+def test_selection_is_per_tape_not_per_structure():
+    """two scenes of the same structure choose their kernels independently, and the
+    entry dies with the tape."""
+    import gc
+    a, b = make_test_scene2(), make_test_scene2()
+    ta, tb = tape_of(a), tape_of(b)
+    handle = object()
+    SP.select(ta, handle)
+    assert SP.selected_for(ta.code_tensor()) is handle
+    assert SP.selected_for(tb.code_tensor()) is None          # same code bytes, other tape
+    SP.select(ta, None)
+    assert SP.selected_for(ta.code_tensor()) is None
+    SP.select(tb, handle)
+    n = len(SP._selected)
+    del b, tb
+    gc.collect()
+    assert len(SP._selected) == n - 1

@@ -99,3 +99,24 @@ def test_lowered_params_cache_tracks_parameter_updates():
         b = tape.lowered_params()
     assert b is not a and not torch.equal(a, b)
     assert tape.lowered_params().requires_grad      # autograd on: fresh, connected to parameters
+
+
+def test_lowered_params_cache_sees_parameter_writes():
+    """the no-grad cache must not serve a stale block.  Version-bumping writes and a
+    replaced ``.data`` are detected; in-place writes THROUGH ``.data`` need ``Tape.invalidate()``."""
+    scene = S.make_test_scene()
+    tape = T.tape_of(scene)
+    k = scene.blend_k
+    with torch.no_grad():
+        a = tape.lowered_params()
+        assert tape.lowered_params() is a                         # cached
+        k.mul_(2.0)                                               # bumps the version counter
+        b = tape.lowered_params()
+        assert b is not a and not torch.equal(a, b)
+        k.data = torch.tensor(5.0)                                # new storage, same version
+        c = tape.lowered_params()
+        assert c is not b and float(-c[tape._perm.tolist().index(1 + tape.n_theta + tape._slot(k))]) == 5.0
+        k.data.fill_(7.0)                                         # invisible to autograd's counters
+        tape.invalidate()
+        d = tape.lowered_params()
+        assert d is not c and float(-d[tape._perm.tolist().index(1 + tape.n_theta + tape._slot(k))]) == 7.0
