@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define RM_B200_ABI_VERSION 5
+#define RM_B200_ABI_VERSION 6
 
 typedef enum RmStatus {
     RM_OK = 0,
@@ -108,6 +108,12 @@ typedef struct RmRenderArgs {
                                their softmax term < 2^-30 of the largest one (march steps only)      */
     const float* cmap;      /* [4096][3] cyclic colour LUT for modes 6,7 (may be NULL otherwise) */
     float   bwd_converge_tol; /* rm_render_bwd only: see rm_march_bwd (0 = reverse every step) */
+    /* Interleaved shard ("row-interleaved tiles"): with strip_rays > 0 the shard's LOCAL
+     * ray l is the global ray  ray_begin + (l / strip_rays) * strip_stride + l % strip_rays,  i.e. strips
+     * of strip_rays consecutive rays taken every strip_stride rays (rank g of G: ray_begin = g * strip,
+     * strip_stride = G * strip).  strip_rays must be a multiple of 4; 0 = one contiguous range. */
+    int64_t strip_rays;
+    int64_t strip_stride;
 } RmRenderArgs;
 
 int rm_abi_version(void);
@@ -208,6 +214,30 @@ int64_t rm_bwd_scratch_floats(int64_t n_rays, int32_t steps);
 int rm_render_bwd(const RmTape* tape, const RmCamera* cam, const float* poses,
                   const RmRenderArgs* args, const RmRenderGrads* grads, float* traj_scratch,
                   float* dpar, float* dposes, void* stream);
+
+/* Targets and weights of the fused inverse-rendering loss (rm_render_loss_bwd), indexed by the LOCAL
+ * ray index like RmRenderOut.  Either target may be NULL (its term is skipped). */
+typedef struct RmLossArgs {
+    const float* target_lambertian; /* [n] target of LambertianShader (shader.py:16-20)            */
+    const float* target_depth;      /* [n] target of the raw depth |pos - origin|                  */
+    float weight_lambertian;        /* weight of sum_r (lambertian_r - target_r)^2, e.g. 1/n for a mean */
+    float weight_depth;             /* weight of sum_r (depth_r - target_r)^2                       */
+    float* loss_out;                /* DEVICE [2], overwritten: the two weighted sums over this shard */
+} RmLossArgs;
+
+/* Forward AND backward of the inverse-rendering loss of SURVEY.md 8(d) (config 4),
+ *     loss = w_l sum_r (clamp(-v.n, 0, 1)_r - lam*_r)^2 + w_d sum_r (|p_S - o|_r - depth*_r)^2,
+ * over the pipeline of RenderLoop.forward (control.py:239-245) + LambertianShader (shader.py:16-20), in
+ * ONE kernel: rays from the pixel index, march replay, stencil, shading, residuals and adjoint seeds in
+ * registers, reverse march, camera-pose contraction.  What torch.autograd does through the reference's
+ * unrolled graph plus its loss algebra; no G-buffer or gradient plane touches memory.
+ * Writes loss->loss_out[2], d loss / d par [tape->n_par] and d loss / d poses [n_views][RM_POSE_STRIDE]
+ * (overwritten; gradients of the SUM of both terms with unit upstream).  dpar == dposes == NULL evaluates
+ * the loss only.  Uses args->ray_begin, n_rays, steps, normals_eps, bwd_converge_tol (bounces must be 0);
+ * a sharded job sums loss_out / dpar / dposes over shards (one all-reduce). */
+int rm_render_loss_bwd(const RmTape* tape, const RmCamera* cam, const float* poses,
+                       const RmRenderArgs* args, const RmLossArgs* loss, float* traj_scratch,
+                       float* dpar, float* dposes, void* stream);
 
 /* Measurement aid for the FP32 roofline denominator (bench.py): blocks x 256 threads, each issuing
  * iters*128 independent FFMA (256 flop).  Not part of the render path. */

@@ -17,7 +17,7 @@ LIB_PATH = os.environ.get("RM_B200_LIB") or os.path.join(_HERE, "csrc", "librm_b
 
 POSE_STRIDE = 8
 REDUCE_FLOATS = 8
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 
 class RmTape(C.Structure):
@@ -42,12 +42,18 @@ class RmRenderArgs(C.Structure):
                 ("bounces", C.c_int32), ("normals_eps", C.c_float), ("hit_tau", C.c_float),
                 ("lift_delta", C.c_float), ("mode_mask", C.c_uint32),
                 ("display_mode", C.c_int32), ("degree", C.c_int32), ("early_exit", C.c_int32),
-                ("fast_math", C.c_int32), ("cmap", C.c_void_p), ("bwd_converge_tol", C.c_float)]
+                ("fast_math", C.c_int32), ("cmap", C.c_void_p), ("bwd_converge_tol", C.c_float),
+                ("strip_rays", C.c_int64), ("strip_stride", C.c_int64)]
 
 
 class RmRenderGrads(C.Structure):
     _fields_ = [("origin", C.c_void_p), ("dirs", C.c_void_p), ("pos", C.c_void_p),
                 ("sdf", C.c_void_p), ("normals", C.c_void_p), ("laplacian", C.c_void_p)]
+
+
+class RmLossArgs(C.Structure):
+    _fields_ = [("target_lambertian", C.c_void_p), ("target_depth", C.c_void_p),
+                ("weight_lambertian", C.c_float), ("weight_depth", C.c_float), ("loss_out", C.c_void_p)]
 
 
 _SIGNATURES = {
@@ -78,6 +84,9 @@ _SIGNATURES = {
     "rm_render_bwd": (C.c_int, [C.POINTER(RmTape), C.POINTER(RmCamera), C.c_void_p,
                                 C.POINTER(RmRenderArgs), C.POINTER(RmRenderGrads), C.c_void_p,
                                 C.c_void_p, C.c_void_p, C.c_void_p]),
+    "rm_render_loss_bwd": (C.c_int, [C.POINTER(RmTape), C.POINTER(RmCamera), C.c_void_p,
+                                     C.POINTER(RmRenderArgs), C.POINTER(RmLossArgs), C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_void_p]),
     "rm_probe_ffma": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "rm_probe_math": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
 }

@@ -65,8 +65,8 @@ class RenderLoop(nn.Module):
                       gbuffer: bool = False, display_mode: int = -1, degree: int = 1,
                       marching_steps: int = 32, bounces: int = 0, hit_tau: float = 1e-3,
                       lift_delta: Optional[float] = None, ray_begin: int = 0,
-                      n_rays: Optional[int] = None, finalize: bool = True,
-                      out: Optional[ops.RenderResult] = None) -> ops.RenderResult:
+                      n_rays: Optional[int] = None, strip_rays: int = 0, strip_stride: int = 0,
+                      finalize: bool = True, out: Optional[ops.RenderResult] = None) -> ops.RenderResult:
         """One launch for several shader modes and/or the G-buffer (planes are flat, ray-major)."""
         _lib.require_cuda(orientations, translations)
         mask = 0
@@ -79,7 +79,8 @@ class RenderLoop(nn.Module):
                           hit_tau=hit_tau, lift_delta=lift_delta, early_exit=self.early_exit,
                           fast_math=2 if (self.fast_math and self.cull) else int(self.fast_math),
                           cmap=self.shader.cyclic_cmap,
-                          ray_begin=ray_begin, n_rays=n_rays, finalize=finalize, out=out)
+                          ray_begin=ray_begin, n_rays=n_rays, strip_rays=strip_rays,
+                          strip_stride=strip_stride, finalize=finalize, out=out)
 
     def display_frame(self, orientations: Tensor, translations: Tensor, mode: int = 0,
                       degree: int = 1, marching_steps: int = 32) -> Tensor:
@@ -130,6 +131,27 @@ class RenderLoop(nn.Module):
         image = self.shader(gb["origin"], orientations, pixel_frames, gb["dirs"], gb["pos"], gb["normals"],
                             gb["laplacian"], gb["sdf"], mode=mode, degree=degree)
         return image.expand(-1, H, W, 3)
+
+    def inverse_loss(self, orientations: Tensor, translations: Tensor, target_lambertian: Optional[Tensor],
+                     target_depth: Optional[Tensor], *, marching_steps: int = 32,
+                     weight_lambertian: Optional[float] = None, weight_depth: Optional[float] = None,
+                     ray_begin: int = 0, n_rays: Optional[int] = None, strip_rays: int = 0,
+                     strip_stride: int = 0, return_terms: bool = False):
+        """The inverse-rendering loss of BASELINE config 4,
+        ``mean((lambertian - target_lambertian)^2) + mean((depth - target_depth)^2)`` with
+        ``depth = |marched position - ray origin|``, evaluated AND differentiated by one fused kernel
+        (``rm_render_loss_bwd``): the forward replay, the shading, the residuals, the adjoint seeds, the
+        reverse march and the camera-pose contraction never leave registers.  Equivalent to composing
+        :meth:`gbuffer` with the reference's shader algebra (``shader.py:16-20``) and ``.mean()`` -- and
+        tested against it -- at a third of the GPU time.  ``ray_begin`` / ``n_rays`` select a shard of the
+        batch (targets are indexed by the local ray); weights default to ``1 / total rays``."""
+        loss, terms = ops.render_loss(tape_of(self.scene), self.camera.struct(), orientations, translations,
+                                      target_lambertian=target_lambertian, target_depth=target_depth,
+                                      weight_lambertian=weight_lambertian, weight_depth=weight_depth,
+                                      steps=marching_steps, normals_eps=self.normals.normals_eps,
+                                      ray_begin=ray_begin, n_rays=n_rays, strip_rays=strip_rays,
+                                      strip_stride=strip_stride)
+        return (loss, terms) if return_terms else loss
 
     def gbuffer(self, orientations: Tensor, translations: Tensor, marching_steps: int = 32):
         """Differentiable G-buffer of control.py:239-245 as ``(N,H,W,c)`` tensors: ``origin`` (= pixel

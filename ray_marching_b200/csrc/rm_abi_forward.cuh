@@ -154,8 +154,8 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
     if (a == nullptr || out == nullptr || poses == nullptr)
         return fail(RM_ERR_INVALID, "rm_render: null argument block");
     const int64_t total = (int64_t)P.cam.n_views * P.cam.width * P.cam.height;
-    if (a->ray_begin < 0 || a->n_rays < 0 || a->ray_begin + a->n_rays > total)
-        return fail(RM_ERR_INVALID, "rm_render: ray range outside the camera batch");
+    if (const char* why = check_shard(a->ray_begin, a->n_rays, a->strip_rays, a->strip_stride, total))
+        return fail(RM_ERR_INVALID, "rm_render: %s", why);
     if (a->steps < 0 || a->bounces < 0 || !(a->normals_eps > 0.f))
         return fail(RM_ERR_INVALID, "rm_render: negative steps/bounces or eps <= 0");
     if (a->display_mode > 7) return fail(RM_ERR_INVALID, "rm_render: display_mode must be -1..7");
@@ -172,6 +172,7 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
     if (a->n_rays == 0) return RM_OK;
     make_stencil(a->normals_eps, &P.st);
     P.ray_begin = a->ray_begin; P.n_rays = a->n_rays; P.steps = a->steps; P.bounces = a->bounces;
+    P.strip_rays = a->strip_rays; P.strip_stride = a->strip_stride;
     P.hit_tau = a->hit_tau; P.lift_delta = a->lift_delta; P.mode_mask = a->mode_mask;
     P.display_mode = a->display_mode; P.degree = a->degree; P.early_exit = a->early_exit;
     P.cmap = a->cmap; P.out = *out;

@@ -376,13 +376,20 @@ struct RenderBwdParams {
     int iters;
     CamParams cam;
     Stencil st;
-    int64_t ray_begin, n_rays;
+    int64_t ray_begin, n_rays, strip_rays, strip_stride;
     int steps;
     float tol;
     RmRenderGrads g;
     float* traj;
     float* dpar;
     float* dposes;
+    // LOSS instantiation (rm_render_loss_bwd): the upstream gradients are not read from planes but
+    // derived in registers from the residuals of the shaded pixel against the target planes
+    const float* target_lam;
+    const float* target_depth;
+    float w_lam, w_depth;
+    float* loss_out;        // [2]: weighted sums of squared residuals (lambertian, depth)
+    int want_grad;          // 0: loss only (no reverse pass)
 };
 
 // Adjoint of w = R(q) b w.r.t. q for an upstream adjoint l of w (R = rotation polynomial):
@@ -420,21 +427,31 @@ __device__ __forceinline__ void flush_pose_grad(float* dposes, int view, const f
     }
 }
 
-template <int CAP, int MODE>
-__global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
-render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
-                  const float* __restrict__ poses, const __grid_constant__ RenderBwdParams P) {
+// LOSS = false: rm_render_bwd (upstream gradients of the G-buffer planes come from memory).
+// LOSS = true : rm_render_loss_bwd -- forward AND backward of the inverse-rendering loss of SURVEY.md
+// 8(d) in one kernel: after the replay the thread holds p_S, the stencil vector u and the ray, so it
+// shades the pixel (LambertianShader, shader.py:16-20; raw depth |p_S - origin|), forms the residuals
+// against the target planes, adds their weighted squares to the loss and seeds the reverse pass with
+//     g_lam = 2 w_lam r_lam [0 <= -v.n <= 1],   g_depth = 2 w_depth r_depth
+//     d/dn = -g_lam v,  d/dv = -g_lam n,  d/dp_S = g_depth e/|e|,  d/do = -g_depth e/|e|   (e = p_S - o)
+// (clamp passes its gradient on the closed interval, the norm has sub-gradient 0 at 0: torch's
+// conventions).  No G-buffer plane, no gradient plane and no elementwise kernel exists on this route.
+template <int CAP, int MODE, bool LOSS>
+__device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const float* par, int n_instr, int n_par,
+                                                const float* __restrict__ poses, const RenderBwdParams& P) {
     extern __shared__ __align__(16) unsigned char smem[];
     const GradAcc<MODE> sacc = stage_accumulators<MODE>(smem, n_par, P.acc_shared);
     const float4* spar = stage_params(par, n_par, smem);
     const int64_t n = P.n_rays;
-    const bool need_stencil = P.g.normals != nullptr || P.g.laplacian != nullptr;
+    const bool need_stencil = LOSS ? (P.target_lam != nullptr)
+                                   : (P.g.normals != nullptr || P.g.laplacian != nullptr);
     const int64_t per_view = (int64_t)P.cam.width * P.cam.height;
 
     float cam_acc[7];                       // dq[4], dt[3] of `acc_view`, summed over this thread's rays
 #pragma unroll
     for (int i = 0; i < 7; ++i) cam_acc[i] = 0.f;
     int acc_view = -1;
+    float loss_l = 0.f, loss_d = 0.f;       // LOSS: this thread's sums of squared residuals
 
     const int iters = P.iters;
     for (int it = 0; it < iters; ++it) {                    // block-uniform trip count (see backward_grid)
@@ -447,7 +464,7 @@ render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, 
 #pragma unroll
         for (int k = 0; k < KB; ++k) {
             float ob[3], vb[3], ow[3], vw[3];
-            world_ray(P.cam, poses, P.ray_begin + first + k, pose, cur_view, ob, vb, ow, vw);
+            world_ray(P.cam, poses, shard_ray(P.ray_begin, P.strip_rays, P.strip_stride, first + k), pose, cur_view, ob, vb, ow, vw);
             px[k] = ow[0]; py[k] = ow[1]; pz[k] = ow[2];
             vx[k] = vw[0]; vy[k] = vw[1]; vz[k] = vw[2];
         }
@@ -457,13 +474,54 @@ render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, 
         forward_pass<CAP>(code, n_instr, spar, P.steps, P.tol, need_stencil ? &P.st : nullptr, P.traj,
                           px, py, pz, vx, vy, vz, conv, ux, uy, uz);
 
-        // ---- adjoints of the stencil outputs (SDFNormals.forward, ray_marching.py:115-125) and of
-        //      f(p_S) (control.py:244) ----
-        float lx[KB], ly[KB], lz[KB];
-        load3k(P.g.pos, first, n, lx, ly, lz);
+        // ---- adjoints of the stencil outputs (SDFNormals.forward, ray_marching.py:115-125), of
+        //      f(p_S) (control.py:244), of p_S, the direction and the origin ----
+        float lx[KB], ly[KB], lz[KB], dvx[KB], dvy[KB], dvz[KB], gox[KB], goy[KB], goz[KB];
         StencilAdjoint sa;
-        load1k(P.g.sdf, first, n, sa.gs);
-        {
+        if constexpr (LOSS) {
+#pragma unroll
+            for (int k = 0; k < KB; ++k) {
+                const int64_t r = shard_ray(P.ray_begin, P.strip_rays, P.strip_stride, first + k);
+                const bool valid = first + k < n;
+                float ob[3], vb[3], ow[3], vw[3];
+                world_ray(P.cam, poses, r, pose, cur_view, ob, vb, ow, vw);      // origin, regenerated
+                const float len = sqrt_rn_inline(ux[k] * ux[k] + uy[k] * uy[k] + uz[k] * uz[k]);
+                const float il = div_rn_inline(1.f, len);
+                const float nx = ux[k] * il, ny = uy[k] * il, nz = uz[k] * il;
+                float g_lam = 0.f, g_dep = 0.f;
+                if (P.target_lam != nullptr && valid) {
+                    const float nv = -(vx[k] * nx + vy[k] * ny + vz[k] * nz);
+                    const float res = clamp_nan(nv, 0.f, 1.f) - __ldg(P.target_lam + first + k);
+                    loss_l = fmaf(res, res, loss_l);
+                    // clamp passes the gradient on [0, 1] inclusive; a NaN pixel poisons the gradient
+                    // exactly as it poisons the reference's (NaN * 0 = NaN there, too)
+                    g_lam = (!(nv < 0.f) && !(nv > 1.f)) ? 2.f * P.w_lam * res : 0.f;
+                }
+                const float ex = px[k] - ow[0], ey = py[k] - ow[1], ez = pz[k] - ow[2];
+                float hx = 0.f, hy = 0.f, hz = 0.f;
+                if (P.target_depth != nullptr && valid) {
+                    const float depth = sqrt_rn_inline(ex * ex + ey * ey + ez * ez);
+                    const float res = depth - __ldg(P.target_depth + first + k);
+                    loss_d = fmaf(res, res, loss_d);
+                    g_dep = 2.f * P.w_depth * res;
+                    const float id = rcp_or_zero(depth);
+                    hx = g_dep * ex * id; hy = g_dep * ey * id; hz = g_dep * ez * id;
+                }
+                lx[k] = hx; ly[k] = hy; lz[k] = hz;
+                gox[k] = -hx; goy[k] = -hy; goz[k] = -hz;
+                dvx[k] = -g_lam * nx; dvy[k] = -g_lam * ny; dvz[k] = -g_lam * nz;
+                // d nrm / d u = (I - nrm nrm^T) / |u| applied to g_n = -g_lam v
+                const float gnx = -g_lam * vx[k], gny = -g_lam * vy[k], gnz = -g_lam * vz[k];
+                const float gn = gnx * nx + gny * ny + gnz * nz;
+                const bool has_n = P.target_lam != nullptr;
+                sa.gux[k] = has_n ? (gnx - gn * nx) * il : 0.f;
+                sa.guy[k] = has_n ? (gny - gn * ny) * il : 0.f;
+                sa.guz[k] = has_n ? (gnz - gn * nz) * il : 0.f;
+                sa.gm[k] = 0.f; sa.gs[k] = 0.f;
+            }
+        } else {
+            load3k(P.g.pos, first, n, lx, ly, lz);
+            load1k(P.g.sdf, first, n, sa.gs);
             float gnx[KB], gny[KB], gnz[KB], glap[KB];
             load3k(P.g.normals, first, n, gnx, gny, gnz);
             load1k(P.g.laplacian, first, n, glap);
@@ -480,21 +538,20 @@ render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, 
                 sa.guz[k] = has_n ? (gnz[k] - gn * nz) * il : 0.f;
                 sa.gm[k] = glap[k] * P.st.lap_scale;
             }
+            load3k(P.g.dirs, first, n, dvx, dvy, dvz);
+            load3k(P.g.origin, first, n, gox, goy, goz);
         }
+        if (LOSS && !P.want_grad) continue;                 // loss evaluation only
 
         // ---- reverse pass: stencil samples, converged tail, exact steps ----
-        float dvx[KB], dvy[KB], dvz[KB];
-        load3k(P.g.dirs, first, n, dvx, dvy, dvz);
         reverse_pass<CAP, MODE>(code, n_instr, spar, P.steps, &P.st,
-                          (need_stencil || P.g.sdf != nullptr) ? &sa : nullptr, P.traj, sacc, conv,
+                          (need_stencil || (!LOSS && P.g.sdf != nullptr)) ? &sa : nullptr, P.traj, sacc, conv,
                           px, py, pz, vx, vy, vz, lx, ly, lz, dvx, dvy, dvz);
-        float gox[KB], goy[KB], goz[KB];
-        load3k(P.g.origin, first, n, gox, goy, goz);
 
         // ---- camera pose: origin = R(q) o_b + t, dir = R(q) v_b ----
 #pragma unroll
         for (int k = 0; k < KB; ++k) {
-            const int64_t r = P.ray_begin + first + k;
+            const int64_t r = shard_ray(P.ray_begin, P.strip_rays, P.strip_stride, first + k);
             const bool valid = first + k < n;
             const int view = valid ? (int)(r / per_view) : acc_view;
             if (view != acc_view) {                           // rare: view boundary inside a thread's stream
@@ -522,8 +579,29 @@ render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, 
             }
         }
     }
+    if constexpr (LOSS) {
+        const float sl = warp_sum(loss_l) * P.w_lam, sd = warp_sum(loss_d) * P.w_depth;
+        if ((threadIdx.x & 31) == 0) {
+            if (P.target_lam != nullptr) atomicAdd(P.loss_out + 0, sl);
+            if (P.target_depth != nullptr) atomicAdd(P.loss_out + 1, sd);
+        }
+        if (!P.want_grad) return;
+    }
     flush_pose_grad(P.dposes, acc_view, cam_acc);
     flush_accumulators(sacc, P.dpar, n_par);
+}
+
+template <int CAP, int MODE>
+__global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
+render_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
+                  const float* __restrict__ poses, const __grid_constant__ RenderBwdParams P) {
+    render_bwd_body<CAP, MODE, false>(code, par, n_instr, n_par, poses, P);
+}
+template <int CAP, int MODE>
+__global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
+render_loss_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
+                       const float* __restrict__ poses, const __grid_constant__ RenderBwdParams P) {
+    render_bwd_body<CAP, MODE, true>(code, par, n_instr, n_par, poses, P);
 }
 
 inline int check_backward_tape(const RmTape* t) {
@@ -641,36 +719,75 @@ extern "C" int rm_march_bwd(const RmTape* tape, const float* origin, const float
     return RM_OK;
 }
 
+// Argument checks and kernel constants shared by rm_render_bwd and rm_render_loss_bwd.
+static int prepare_render_bwd(const char* who, const RmTape* tape, const RmCamera* cam, const float* poses,
+                              const RmRenderArgs* a, float* traj_scratch, float* dpar, float* dposes,
+                              bool want_grad, void* stream, RenderBwdParams* P) {
+    if (int s = check_backward_tape(tape)) return s;
+    if (int s = make_cam(cam, &P->cam)) return s;
+    if (a == nullptr || poses == nullptr || (want_grad && (dposes == nullptr || (dpar == nullptr && tape->n_par > 0))))
+        return fail(RM_ERR_INVALID, "%s: null argument", who);
+    const int64_t total = (int64_t)cam->n_views * cam->width * cam->height;
+    if (const char* why = check_shard(a->ray_begin, a->n_rays, a->strip_rays, a->strip_stride, total))
+        return fail(RM_ERR_INVALID, "%s: %s", who, why);
+    if (a->steps < 0 || !(a->normals_eps > 0.f) || !(a->bwd_converge_tol >= 0.f))
+        return fail(RM_ERR_INVALID, "%s: negative steps, eps <= 0 or negative tolerance", who);
+    if (a->bounces != 0)
+        return fail(RM_ERR_UNSUPPORTED, "%s: reflected segments are not differentiable here", who);
+    if (a->n_rays > 0 && a->steps > 0 && traj_scratch == nullptr)
+        return fail(RM_ERR_INVALID, "%s: trajectory scratch is null", who);
+    if (want_grad) {
+        if (tape->n_par > 0)
+            RM_CUDA(cudaMemsetAsync(dpar, 0, (size_t)tape->n_par * sizeof(float), (cudaStream_t)stream));
+        RM_CUDA(cudaMemsetAsync(dposes, 0, (size_t)cam->n_views * RM_POSE_STRIDE * sizeof(float), (cudaStream_t)stream));
+    }
+    make_stencil(a->normals_eps, &P->st);
+    P->ray_begin = a->ray_begin; P->n_rays = a->n_rays; P->steps = a->steps;
+    P->strip_rays = a->strip_rays; P->strip_stride = a->strip_stride;
+    P->acc_shared = backward_acc_shared(tape);
+    P->iters = backward_iters(a->n_rays);
+    P->tol = a->bwd_converge_tol;
+    P->g = RmRenderGrads{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    P->traj = traj_scratch; P->dpar = dpar; P->dposes = dposes;
+    P->target_lam = P->target_depth = nullptr; P->w_lam = P->w_depth = 0.f; P->loss_out = nullptr;
+    P->want_grad = want_grad ? 1 : 0;
+    return RM_OK;
+}
+
 extern "C" int rm_render_bwd(const RmTape* tape, const RmCamera* cam, const float* poses,
                              const RmRenderArgs* a, const RmRenderGrads* grads, float* traj_scratch,
                              float* dpar, float* dposes, void* stream) {
-    if (int s = check_backward_tape(tape)) return s;
     RenderBwdParams P;
-    if (int s = make_cam(cam, &P.cam)) return s;
-    if (a == nullptr || grads == nullptr || poses == nullptr || dposes == nullptr ||
-        (dpar == nullptr && tape->n_par > 0))
-        return fail(RM_ERR_INVALID, "rm_render_bwd: null argument");
-    const int64_t total = (int64_t)cam->n_views * cam->width * cam->height;
-    if (a->ray_begin < 0 || a->n_rays < 0 || a->ray_begin + a->n_rays > total)
-        return fail(RM_ERR_INVALID, "rm_render_bwd: ray range outside the camera batch");
-    if (a->steps < 0 || !(a->normals_eps > 0.f) || !(a->bwd_converge_tol >= 0.f))
-        return fail(RM_ERR_INVALID, "rm_render_bwd: negative steps, eps <= 0 or negative tolerance");
-    if (a->bounces != 0)
-        return fail(RM_ERR_UNSUPPORTED, "rm_render_bwd: reflected segments are not differentiable here");
-    if (a->n_rays > 0 && a->steps > 0 && traj_scratch == nullptr)
-        return fail(RM_ERR_INVALID, "rm_render_bwd: trajectory scratch is null");
-    if (tape->n_par > 0)
-        RM_CUDA(cudaMemsetAsync(dpar, 0, (size_t)tape->n_par * sizeof(float), (cudaStream_t)stream));
-    RM_CUDA(cudaMemsetAsync(dposes, 0, (size_t)cam->n_views * RM_POSE_STRIDE * sizeof(float), (cudaStream_t)stream));
+    if (grads == nullptr) return fail(RM_ERR_INVALID, "rm_render_bwd: null argument");
+    if (int s = prepare_render_bwd("rm_render_bwd", tape, cam, poses, a, traj_scratch, dpar, dposes, true, stream, &P))
+        return s;
     if (a->n_rays == 0) return RM_OK;
-    make_stencil(a->normals_eps, &P.st);
-    P.ray_begin = a->ray_begin; P.n_rays = a->n_rays; P.steps = a->steps;
-    P.acc_shared = backward_acc_shared(tape);
-    P.iters = backward_iters(a->n_rays);
-    P.tol = a->bwd_converge_tol;
-    P.g = *grads; P.traj = traj_scratch; P.dpar = dpar; P.dposes = dposes;
+    P.g = *grads;
     const size_t sm = backward_smem(tape);
     RM_BWD_LAUNCH(tape, render_bwd_kernel, backward_grid(a->n_rays), sm, stream, tape->par, tape->n_instr,
+                  tape->n_par, poses, P);
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+}
+
+extern "C" int rm_render_loss_bwd(const RmTape* tape, const RmCamera* cam, const float* poses,
+                                  const RmRenderArgs* a, const RmLossArgs* loss, float* traj_scratch,
+                                  float* dpar, float* dposes, void* stream) {
+    RenderBwdParams P;
+    if (loss == nullptr || loss->loss_out == nullptr)
+        return fail(RM_ERR_INVALID, "rm_render_loss_bwd: null loss block or loss_out");
+    if (a != nullptr && a->n_rays > 0 && loss->target_lambertian == nullptr && loss->target_depth == nullptr)
+        return fail(RM_ERR_INVALID, "rm_render_loss_bwd: no target plane given");
+    const bool want_grad = dpar != nullptr || dposes != nullptr;
+    if (int s = prepare_render_bwd("rm_render_loss_bwd", tape, cam, poses, a, traj_scratch, dpar, dposes,
+                                   want_grad, stream, &P))
+        return s;
+    RM_CUDA(cudaMemsetAsync(loss->loss_out, 0, 2 * sizeof(float), (cudaStream_t)stream));
+    if (a->n_rays == 0) return RM_OK;
+    P.target_lam = loss->target_lambertian; P.target_depth = loss->target_depth;
+    P.w_lam = loss->weight_lambertian; P.w_depth = loss->weight_depth; P.loss_out = loss->loss_out;
+    const size_t sm = backward_smem(tape);
+    RM_BWD_LAUNCH(tape, render_loss_bwd_kernel, backward_grid(a->n_rays), sm, stream, tape->par, tape->n_instr,
                   tape->n_par, poses, P);
     RM_CUDA(cudaGetLastError());
     return RM_OK;

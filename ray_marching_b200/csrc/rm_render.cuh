@@ -9,7 +9,7 @@ namespace rm {
 struct RenderParams {
     CamParams cam;
     Stencil st;
-    int64_t ray_begin, n_rays;
+    int64_t ray_begin, n_rays, strip_rays, strip_stride;
     int steps, bounces;
     float hit_tau, lift_delta;
     unsigned mode_mask;
@@ -110,9 +110,10 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
         (void)warp; (void)t0; (void)t1; (void)rot;
 #endif
         const int64_t first = ((int64_t)t * 32 + lane) * K;
+        const int64_t ray0 = shard_ray(P.ray_begin, P.strip_rays, P.strip_stride, first);   // global index
         float ox[K], oy[K], oz[K], vx[K], vy[K], vz[K];
         float px[K], py[K], pz[K], f[K], nx[K], ny[K], nz[K], lap[K];
-        make_rays(P.cam, poses, P.ray_begin + first, ox, oy, oz, vx, vy, vz);
+        make_rays(P.cam, poses, ray0, ox, oy, oz, vx, vy, vz);
         store3(P.out.origin, first, n, ox, oy, oz);
 #pragma unroll
         for (int k = 0; k < K; ++k) { px[k] = ox[k]; py[k] = oy[k]; pz[k] = oz[k]; }
@@ -179,7 +180,7 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
         }
         if (mask & (RM_MODE_VIGNETTE | RM_MODE_TANGENT | RM_MODE_SPIN)) {
             // the camera pose of each ray's view (one divide per thread, as in make_rays)
-            PixelCursor cur = pixel_cursor(P.cam, P.ray_begin + first);
+            PixelCursor cur = pixel_cursor(P.cam, ray0);
             int pose_view = cur.view;
             Pose pose = load_pose(poses, cur.view);
 #pragma unroll
@@ -201,7 +202,7 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
             if (P.mode_mask & RM_MODE_VIGNETTE) store1(P.out.image[3], first, n, img);
             if (P.mode_mask & RM_MODE_TANGENT) store3(P.out.image[6], first, n, rgb0, rgb1, rgb2);
             if (mask & RM_MODE_SPIN) {
-                cur = pixel_cursor(P.cam, P.ray_begin + first);
+                cur = pixel_cursor(P.cam, ray0);
                 pose_view = cur.view;
                 pose = load_pose(poses, cur.view);
 #pragma unroll

@@ -82,6 +82,29 @@ __device__ __forceinline__ PixelCursor pixel_cursor(const CamParams& cam, int64_
     }
     return c;
 }
+// Global ray index of local ray `local` of a shard (RmRenderArgs: ray_begin, strip_rays, strip_stride).
+// One divide per thread (32-bit when it fits); the K rays of a thread lie in one strip (strip % 4 == 0).
+__device__ __forceinline__ int64_t shard_ray(int64_t begin, int64_t strip, int64_t stride, int64_t local) {
+    if (strip <= 0) return begin + local;
+    if ((local | strip) <= 0x7fffffffLL) {
+        const unsigned s = (unsigned)local / (unsigned)strip;
+        return begin + (int64_t)s * stride + (int64_t)((unsigned)local - s * (unsigned)strip);
+    }
+    const int64_t s = local / strip;
+    return begin + s * stride + (local - s * strip);
+}
+// Host: validates a shard description against the batch size.
+inline const char* check_shard(int64_t begin, int64_t n, int64_t strip, int64_t stride, int64_t total) {
+    if (begin < 0 || n < 0) return "negative ray range";
+    if (strip < 0 || stride < 0) return "negative strip";
+    if (strip == 0) return begin + n > total ? "ray range outside the camera batch" : nullptr;
+    if (strip % 4 != 0) return "strip_rays must be a multiple of 4";
+    if (stride < strip) return "strip_stride smaller than strip_rays";
+    if (n == 0) return nullptr;
+    const int64_t last = begin + ((n - 1) / strip) * stride + (n - 1) % strip;
+    return last >= total ? "interleaved ray range outside the camera batch" : nullptr;
+}
+
 __device__ __forceinline__ void pixel_next(const CamParams& cam, PixelCursor& c) {
     if (++c.col == cam.width) {
         c.col = 0;

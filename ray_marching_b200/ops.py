@@ -15,7 +15,7 @@ import torch
 from torch import Tensor
 
 from . import _lib, specialise as _spec
-from ._lib import (RmCamera, RmRenderArgs, RmRenderGrads, RmRenderOut, RmTape, check, lib, ptr,
+from ._lib import (RmCamera, RmLossArgs, RmRenderArgs, RmRenderGrads, RmRenderOut, RmTape, check, lib, ptr,
                    stream_ptr)
 
 # Backward kernels: step-length tolerance (relative to 1 + |p|_inf) below which a ray counts as
@@ -163,18 +163,23 @@ def render(tape, cam: RmCamera, poses: Tensor, *, steps: int = 32, normals_eps: 
            mode_mask: int = 0, gbuffer: bool = False, display_mode: int = -1, degree: int = 1,
            bounces: int = 0, hit_tau: float = 1e-3, lift_delta: Optional[float] = None,
            early_exit: bool = False, fast_math: int = 1, cmap: Optional[Tensor] = None,
-           ray_begin: int = 0, n_rays: Optional[int] = None, finalize: bool = True,
-           reduce: Optional[Tensor] = None, out: Optional[RenderResult] = None) -> RenderResult:
+           ray_begin: int = 0, n_rays: Optional[int] = None, strip_rays: int = 0, strip_stride: int = 0,
+           finalize: bool = True, reduce: Optional[Tensor] = None,
+           out: Optional[RenderResult] = None) -> RenderResult:
     """One launch of the fused camera->march->stencil->shade kernel (no autograd).
 
     ``fast_math``: 0 IEEE everywhere, 1 approximate sqrt/exp inside march steps, 2 additionally
     bounding-sphere culling of smooth-union children inside march steps.
+    ``strip_rays`` / ``strip_stride``: interleaved shard (``parallel.shard_strips``; ``n_rays`` is then
+    required): local ray l = global ray ``ray_begin + (l // strip_rays) * strip_stride + l % strip_rays``.
     ``finalize=False`` leaves modes 1/2/5 un-normalised (so a sharded job can all-reduce
     ``result.reduce`` first and then call :func:`shade_finalize`)."""
     dev = _lib.require_cuda(poses)
     with torch.no_grad():
         par = tape.lowered_params(dev)
         total = cam.n_views * cam.width * cam.height
+        if strip_rays and n_rays is None:
+            raise _lib.RmError("render: an interleaved shard needs n_rays (parallel.shard_strips)")
         n = total - ray_begin if n_rays is None else n_rays
         res = out or RenderResult()
         new = lambda *shape: torch.empty(*shape, device=dev, dtype=torch.float32)
@@ -220,7 +225,7 @@ def render(tape, cam: RmCamera, poses: Tensor, *, steps: int = 32, normals_eps: 
         a = RmRenderArgs(ray_begin, n, int(steps), int(bounces), float(normals_eps), float(hit_tau),
                          float(2 * normals_eps if lift_delta is None else lift_delta),
                          int(mode_mask), int(display_mode), int(degree), int(early_exit),
-                         int(fast_math), ptr(cmap), 0.0)
+                         int(fast_math), ptr(cmap), 0.0, int(strip_rays), int(strip_stride))
         t = _tape_struct(tape.code_tensor(dev), par, tape.n_nodes, tape.max_depth)
         # a tape-specialised library (specialise.py) exports rm_render with the same ABI
         spec = getattr(tape, "spec_lib", None) if fast_math < 2 else None
@@ -458,6 +463,87 @@ def render_gbuffer(tape, cam: RmCamera, orientations: Tensor, translations: Tens
     return _render_gbuffer(tape.code_tensor(dev), tape.lowered_params(dev), poses, cam.n_views, cam.width,
                            cam.height, cam.focal_length, cam.sensor_width, cam.sensor_height, int(steps),
                            float(normals_eps), tape.n_nodes, tape.max_depth)
+
+
+# ------------------------------------------------------------------------------ fused loss + backward
+@torch.library.custom_op("rm_b200::render_loss", mutates_args=())
+def _render_loss(code: Tensor, par: Tensor, poses: Tensor, n_views: int, width: int, height: int,
+                 focal: float, sensor_w: float, sensor_h: float, steps: int, eps: float,
+                 target_lam: Optional[Tensor], target_depth: Optional[Tensor], w_lam: float, w_depth: float,
+                 ray_begin: int, n_rays: int, n_nodes: int, max_depth: int, tol: float,
+                 want_grad: bool, strip_rays: int = 0, strip_stride: int = 0) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """One kernel: ``(loss, terms[2], d loss/d par, d loss/d poses)`` of the config-4 loss."""
+    dev = _lib.require_cuda(par, poses, target_lam, target_depth)
+    cont = lambda x: None if x is None else x.reshape(-1).contiguous()
+    tl, td = cont(target_lam), cont(target_depth)
+    for x in (tl, td):
+        if x is not None and x.numel() != n_rays:
+            raise _lib.RmError(f"render_loss: a target plane has {x.numel()} elements for {n_rays} rays")
+    spec = _spec.selected_for(code)
+    traj = torch.empty(max(int((spec or lib()).rm_bwd_scratch_floats(n_rays, steps)), 1), device=dev,
+                       dtype=torch.float32)
+    terms = torch.empty(2, device=dev, dtype=torch.float32)
+    poses = poses.contiguous()
+    dpar = torch.empty_like(par) if want_grad else torch.zeros_like(par)
+    dposes = torch.empty_like(poses) if want_grad else torch.zeros_like(poses)
+    a = RmRenderArgs(int(ray_begin), int(n_rays), int(steps), 0, float(eps), 0.0, 0.0, 0, -1, 1, 0, 0, 0, float(tol),
+                     int(strip_rays), int(strip_stride))
+    la = RmLossArgs(ptr(tl), ptr(td), float(w_lam), float(w_depth), ptr(terms))
+    cam = camera_struct(n_views, width, height, focal, sensor_w, sensor_h)
+    t = _tape_struct(code, par, n_nodes, max_depth)
+    args = (C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(la), ptr(traj),
+            ptr(dpar) if want_grad else None, ptr(dposes) if want_grad else None, stream_ptr(dev))
+    if spec is not None:
+        _spec.spec_check(spec, spec.rm_render_loss_bwd(*args), "rm_render_loss_bwd")
+    else:
+        check(lib().rm_render_loss_bwd(*args), "rm_render_loss_bwd")
+    return terms.sum(), terms, dpar, dposes
+
+
+@_render_loss.register_fake
+def _(code, par, poses, n_views, width, height, focal, sensor_w, sensor_h, steps, eps, target_lam, target_depth,
+      w_lam, w_depth, ray_begin, n_rays, n_nodes, max_depth, tol, want_grad, strip_rays=0, strip_stride=0):
+    return par.new_empty(()), par.new_empty(2), torch.empty_like(par), torch.empty_like(poses)
+
+
+def _render_loss_setup(ctx, inputs, output):
+    loss, terms, dpar, dposes = output
+    ctx.mark_non_differentiable(terms, dpar, dposes)
+    if not inputs[20]:
+        raise _lib.RmError("render_loss was evaluated with want_grad=False but autograd is recording")
+    ctx.save_for_backward(dpar, dposes)
+
+
+def _render_loss_backward(ctx, g_loss, g_terms, g_dpar, g_dposes):
+    dpar, dposes = ctx.saved_tensors
+    return (None, g_loss * dpar, g_loss * dposes) + (None,) * 20
+
+
+_render_loss.register_autograd(_render_loss_backward, setup_context=_render_loss_setup)
+
+
+def render_loss(tape, cam: RmCamera, orientations: Tensor, translations: Tensor, *, target_lambertian=None,
+                target_depth=None, weight_lambertian: Optional[float] = None,
+                weight_depth: Optional[float] = None, steps: int = 32, normals_eps: float = 5e-2,
+                ray_begin: int = 0, n_rays: Optional[int] = None, strip_rays: int = 0, strip_stride: int = 0):
+    """``(loss, terms)``: the inverse-rendering loss of SURVEY.md 8(d) -- ``w_l sum (lambertian - target)^2 +
+    w_d sum (depth - target)^2`` over rays ``[ray_begin, ray_begin + n_rays)`` -- through ONE kernel that
+    also produces its gradients (``rm_render_loss_bwd``); ``loss.backward()`` only scales them.  Weights
+    default to ``1 / n_rays_total`` (the ``.mean()`` of the reference formulation)."""
+    dev = _lib.require_cuda(orientations, translations)
+    total = cam.n_views * cam.width * cam.height
+    n = total - ray_begin if n_rays is None else int(n_rays)
+    wl = 1.0 / total if weight_lambertian is None else float(weight_lambertian)
+    wd = 1.0 / total if weight_depth is None else float(weight_depth)
+    poses = pose_records(orientations, translations)
+    par = tape.lowered_params(dev)
+    want = torch.is_grad_enabled() and (par.requires_grad or poses.requires_grad)
+    loss, terms, _, _ = _render_loss(tape.code_tensor(dev), par, poses, cam.n_views, cam.width, cam.height,
+                                     cam.focal_length, cam.sensor_width, cam.sensor_height, int(steps),
+                                     float(normals_eps), target_lambertian, target_depth, wl, wd, int(ray_begin),
+                                     n, tape.n_nodes, tape.max_depth, BWD_CONVERGE_TOL, bool(want),
+                                     int(strip_rays), int(strip_stride))
+    return loss, terms
 
 
 BACKWARD_READY = True

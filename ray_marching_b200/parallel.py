@@ -36,6 +36,34 @@ def shard_range(total: int, rank: int, world_size: int, align: int = 4) -> Tuple
     return min(begin_u * align, total), min(end_u * align, total)
 
 
+def shard_strips(total: int, rank: int, world_size: int, strip_rays: int) -> dict:
+    """Interleaved shard of ``total`` rays (row-interleaved tiles): strips of
+    ``strip_rays`` consecutive rays dealt round-robin, rank g taking strips g, g+G, ...  Returns the
+    keyword arguments of ``RenderLoop.render_planes`` / ``inverse_loss``:
+    ``ray_begin, n_rays, strip_rays, strip_stride`` (``n_rays`` = this rank's local ray count; the last
+    strip of the batch may be short).  Uneven per-ray cost (culling, early exit, open scenes) then
+    averages out over the image instead of loading the rank that owns the busy region."""
+    if not 0 <= rank < world_size:
+        raise ValueError(f"rank {rank} outside world of {world_size}")
+    if strip_rays <= 0 or strip_rays % 4:
+        raise ValueError("strip_rays must be a positive multiple of 4 (128-bit plane stores)")
+    n_strips = (total + strip_rays - 1) // strip_rays
+    mine = len(range(rank, n_strips, world_size))
+    n = mine * strip_rays
+    if mine and (rank + (mine - 1) * world_size) == n_strips - 1:          # I own the (possibly short) last strip
+        n -= n_strips * strip_rays - total
+    return dict(ray_begin=rank * strip_rays, n_rays=n, strip_rays=strip_rays,
+                strip_stride=world_size * strip_rays)
+
+
+def strip_ray_index(shard: dict, device=None) -> torch.Tensor:
+    """Global ray index of every local ray of an interleaved shard (int64 ``(n_rays,)``): scatter a
+    local plane into the full image with ``full[strip_ray_index(shard)] = plane``."""
+    l = torch.arange(shard["n_rays"], dtype=torch.int64, device=device)
+    s = shard["strip_rays"]
+    return shard["ray_begin"] + (l // s) * shard["strip_stride"] + l % s
+
+
 def shard_views(n_views: int, rank: int, world_size: int) -> List[int]:
     """Round-robin view assignment: rank g renders views g, g+G, ...."""
     return list(range(rank, n_views, world_size))

@@ -426,7 +426,7 @@ class Tape:
         scene under a moving camera costs nothing per frame).  The cache key is every parameter's
         version counter AND storage address; see :meth:`invalidate` for the one kind of write it
         cannot see."""
-        if self.params and device is not None and torch.device(device) != self.device:
+        if self.params and device is not None and not _same_device(device, self.device):
             raise RuntimeError(f"scene parameters live on {self.device} but the query is on "
                                f"{device}; move the scene with .to(device)")
         track = torch.is_grad_enabled() and any(p.requires_grad for p in self.params)
@@ -444,6 +444,17 @@ class Tape:
         return (f"Tape(instr={self.n_instr}, par={self.n_par} floats, leaves={self.n_leaves}, "
                 f"unions={self.n_nodes}, depth={self.max_depth}, theta={self.n_theta}, "
                 f"flops/eval={self.flops_per_eval})")
+
+
+def _same_device(a, b) -> bool:
+    """``cuda`` (no index) names the current device."""
+    a, b = torch.device(a), torch.device(b)
+    if a.type != b.type:
+        return False
+    if a.type != "cuda":
+        return True
+    cur = torch.cuda.current_device() if (a.index is None or b.index is None) else 0
+    return (cur if a.index is None else a.index) == (cur if b.index is None else b.index)
 
 
 def tape_of(module: nn.Module) -> Tape:

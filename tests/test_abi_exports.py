@@ -28,7 +28,8 @@ def test_struct_layout_matches_header():
     assert ctypes.sizeof(_lib.RmTape) == 32
     assert ctypes.sizeof(_lib.RmCamera) == 24
     assert ctypes.sizeof(_lib.RmRenderOut) == 16 * 8
-    assert ctypes.sizeof(_lib.RmRenderArgs) == 72
+    assert ctypes.sizeof(_lib.RmRenderArgs) == 88
+    assert ctypes.sizeof(_lib.RmLossArgs) == 32
     assert ctypes.sizeof(_lib.RmRenderGrads) == 48
 
 
@@ -37,6 +38,35 @@ def test_argument_errors_do_not_need_a_gpu():
     tape = _lib.RmTape(0, 0, 0, 0, 0, 0)
     assert handle.rm_sdf_eval(ctypes.byref(tape), 0, 4, 0, 0) == -1
     assert b"tape" in handle.rm_last_error()
+
+
+def test_shard_arguments_are_validated_on_the_host():
+    """rm_render / rm_render_loss_bwd check the (possibly interleaved) ray range before any CUDA call."""
+    import numpy as np
+    handle = _lib.lib()
+    code = np.array([[1, 0]], dtype=np.int32)                        # one world-space sphere
+    tape = _lib.RmTape(code.ctypes.data, 8, 1, 4, 0, 0)              # fake device pointer: never dereferenced
+    cam = _lib.RmCamera(1, 16, 8, 1e-3, 2e-3, 1e-3)
+    out = _lib.RmRenderOut()
+
+    def render(begin, n, strip, stride):
+        a = _lib.RmRenderArgs(begin, n, 4, 0, 5e-2, 1e-3, 0.1, 0, -1, 1, 0, 1, 0, 0.0, strip, stride)
+        st = handle.rm_render(ctypes.byref(tape), ctypes.byref(cam), 8, ctypes.byref(a), ctypes.byref(out), 0)
+        return st, handle.rm_last_error()
+    assert render(0, 129, 0, 0)[0] == -1                             # contiguous range past the batch (128 rays)
+    st, msg = render(0, 64, 6, 12)
+    assert st == -1 and b"multiple of 4" in msg
+    st, msg = render(0, 64, 8, 4)
+    assert st == -1 and b"strip_stride" in msg
+    st, msg = render(8, 72, 8, 16)                                   # local ray 71 = global 8 + 8*16 + 7 = 143 >= 128
+    assert st == -1 and b"interleaved" in msg
+    assert render(-1, 4, 0, 0)[0] == -1
+    assert render(0, 0, 8, 16)[0] == 0                               # an empty shard is legal (no launch)
+    loss = _lib.RmLossArgs(8, 8, 1.0, 1.0, 0)
+    a = _lib.RmRenderArgs(0, 4, 4, 0, 5e-2, 0.0, 0.0, 0, -1, 1, 0, 0, 0, 0.0, 0, 0)
+    assert handle.rm_render_loss_bwd(ctypes.byref(tape), ctypes.byref(cam), 8, ctypes.byref(a),
+                                     ctypes.byref(loss), 8, 8, 8, 0) == -1
+    assert b"loss_out" in handle.rm_last_error()
 
 
 def test_cpu_tensors_are_rejected_loudly():

@@ -267,3 +267,99 @@ def test_backward_exact_and_settled_ray_modes_agree_with_reference(golden, tol):
             assert rel_err(flat_grads(list(scene.parameters())), g[f"grads/{tag}/dparams_flat"]) < 1e-3, (tag, tol)
     finally:
         ops.set_backward_converge_tol(old)
+
+
+# ---- fused loss + backward (rm_render_loss_bwd) ---------------------------------------------------
+@pytest.mark.parametrize("specialise", [False, True])
+@pytest.mark.parametrize("tag,build", [("scene2", S.make_test_scene2),
+                                       ("syn8", lambda: S.make_synthetic_scene(8, 0, True))])
+def test_loss_fused_kernel_matches_reference_fixture(golden, tag, build, specialise):
+    """RenderLoop.inverse_loss: the config-4 loss AND its gradients from ONE kernel (no G-buffer, no
+    gradient planes, no loss algebra in torch) vs the reference's autograd (fixture), 1e-3."""
+    g = golden("grads")
+    scene = build()
+    loop = RenderLoop(scene, normals_eps=5e-2, **cases.config1_camera(16, 16)).to(DEV)
+    if specialise:
+        loop.specialise(True)
+    q = t32(g[f"grads/{tag}/q"]).to(DEV).requires_grad_(True)
+    t = t32(g[f"grads/{tag}/t"]).to(DEV).requires_grad_(True)
+    lam_t, depth_t = t32(g[f"grads/{tag}/lam_target"]).to(DEV), t32(g[f"grads/{tag}/depth_target"]).to(DEV)
+    loss, terms = loop.inverse_loss(q, t, lam_t, depth_t, marching_steps=32, return_terms=True)
+    ref = float(g[f"grads/{tag}/loss"])
+    assert loss.shape == () and abs(loss.item() - ref) < 1e-4 * max(1.0, ref)
+    assert abs(terms.sum().item() - loss.item()) < 1e-7 and (terms >= 0).all()
+    loss.backward()
+    assert rel_err(q.grad, g[f"grads/{tag}/dq"]) < 1e-3
+    assert rel_err(t.grad, g[f"grads/{tag}/dt"]) < 1e-3
+    assert rel_err(flat_grads(list(scene.parameters())), g[f"grads/{tag}/dparams_flat"]) < 1e-3
+
+
+def test_loss_fused_kernel_equals_the_composed_route_and_shards_sum():
+    """Same loss through (a) gbuffer + torch shader algebra + autograd and (b) the fused kernel: equal to
+    float32 rounding.  Ray-range shards of (b) sum to the whole (what a tile-sharded job all-reduces);
+    odd image size (tail lanes), two views, scaled upstream gradient, single-term losses, loss-only mode."""
+    from ray_marching_b200 import ops
+    from ray_marching_b200.tape import tape_of
+    intr = dict(cases.config1_camera(23, 9))
+    intr["num_cameras"] = 2
+    q0 = torch.nn.functional.normalize(torch.tensor([[0.99, 0.03, -0.08, 0.05], [0.97, -0.1, 0.12, 0.02]]), dim=-1)
+    t0 = torch.tensor([[0.05, 0.1, 1.0], [-0.1, 0.0, 0.9]])
+    gen = torch.Generator().manual_seed(5)
+    lam_t = torch.rand(2, 9, 23, 1, generator=gen).to(DEV)
+    depth_t = (0.25 + 0.1 * torch.rand(2, 9, 23, 1, generator=gen)).to(DEV)
+
+    def run(fused, which="both", scale=1.0):
+        scene = S.make_test_scene2()
+        loop = RenderLoop(scene, normals_eps=5e-2, **intr).to(DEV)
+        q, t = q0.to(DEV).requires_grad_(True), t0.to(DEV).requires_grad_(True)
+        lt = lam_t if which in ("both", "lam") else None
+        dt = depth_t if which in ("both", "depth") else None
+        if fused:
+            loss = loop.inverse_loss(q, t, lt, dt)
+        else:
+            gb = loop.gbuffer(q, t, 32)
+            loss = 0.0
+            if lt is not None:
+                loss = loss + (((-(gb["dirs"] * gb["normals"]).sum(-1, keepdim=True)).clamp(0, 1) - lt) ** 2).mean()
+            if dt is not None:
+                loss = loss + (((gb["pos"] - gb["origin"]).norm(dim=-1, keepdim=True) - dt) ** 2).mean()
+        (loss * scale).backward()
+        return loss.item(), q.grad.clone(), t.grad.clone(), flat_grads(list(scene.parameters())), loop, scene
+
+    for which, scale in (("both", 1.0), ("lam", 1.0), ("depth", 1.0), ("both", -2.5)):
+        la, qa, ta, pa, _, _ = run(False, which, scale)
+        lb, qb, tb, pb, loop, scene = run(True, which, scale)
+        assert abs(la - lb) < 1e-6 * max(1.0, abs(la)), which
+        assert rel_err(qb, qa) < 1e-4 and rel_err(tb, ta) < 1e-4 and rel_err(pb, pa) < 1e-4, (which, scale)
+
+    # shards: three ray ranges (not multiples of 4) of the fused kernel sum to the whole batch
+    total = 2 * 9 * 23
+    tape, cam = tape_of(scene), loop.camera.struct()
+    par = tape.lowered_params(torch.device(DEV)).detach()
+    poses = ops.pose_records(q0.to(DEV), t0.to(DEV))
+    def shard(a, b):
+        return torch.ops.rm_b200.render_loss(tape.code_tensor(), par, poses, cam.n_views, cam.width, cam.height,
+                                             cam.focal_length, cam.sensor_width, cam.sensor_height, 32, 5e-2,
+                                             lam_t.reshape(-1)[a:b], depth_t.reshape(-1)[a:b], 1.0 / total,
+                                             1.0 / total, a, b - a, tape.n_nodes, tape.max_depth, 1e-7, True)
+    whole = shard(0, total)
+    cuts = [0, 101, 300, total]
+    parts = [shard(a, b) for a, b in zip(cuts[:-1], cuts[1:])]
+    for i in range(4):
+        s = sum(p[i] for p in parts)
+        assert rel_err(s, whole[i]) < 1e-5, i
+    assert abs(whole[0].item() - lb) < 1e-6
+    # loss-only evaluation: no gradient buffers are touched, same loss
+    with torch.no_grad():
+        only = loop.inverse_loss(q0.to(DEV), t0.to(DEV), lam_t, depth_t)
+    assert abs(only.item() - lb) < 1e-7
+    # an empty shard is legal
+    empty = torch.ops.rm_b200.render_loss(tape.code_tensor(), par, poses, cam.n_views, cam.width, cam.height,
+                                          cam.focal_length, cam.sensor_width, cam.sensor_height, 32, 5e-2,
+                                          lam_t.reshape(-1)[:0], depth_t.reshape(-1)[:0], 1.0, 1.0, 7, 0,
+                                          tape.n_nodes, tape.max_depth, 1e-7, True)
+    assert empty[0].item() == 0.0 and not empty[2].any() and not empty[3].any()
+    with pytest.raises(Exception):
+        loop.inverse_loss(q0.to(DEV), t0.to(DEV), lam_t.reshape(-1)[:5], depth_t)        # wrong plane size
+    with pytest.raises(Exception):
+        loop.inverse_loss(q0.to(DEV), t0.to(DEV), None, None)                            # no target at all

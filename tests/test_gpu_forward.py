@@ -391,3 +391,40 @@ def test_supersampled_frame_is_the_box_filter_of_the_fine_camera():
     with torch.no_grad():                              # the fused path (autograd on takes the G-buffer route)
         one = loop.supersampled(q.cuda(), t.cuda(), mode=0, factor=1)
         assert torch.equal(one, loop(q.cuda(), t.cuda(), 0))
+
+
+@pytest.mark.gpu
+def test_interleaved_strip_shards_equal_the_full_frame():
+    """parallel.shard_strips (SURVEY 8(e) "row-interleaved tiles"): G interleaved shards of one frame,
+    scattered back by strip_ray_index, are bit-identical to the one-shot render (rays are independent);
+    two views, a short last strip, a normalising shader whose reduce scratch the shards share."""
+    from ray_marching_b200 import parallel
+    scene = S.make_synthetic_scene(8, 0, True)
+    loop = _loop(scene, 40, 30, n=2)
+    q = torch.nn.functional.normalize(torch.tensor([[1.0, 0, 0, 0], [0.9, 0.1, -0.3, 0.05]], device=DEV), dim=-1)
+    t = torch.tensor([[0.0, 0, -4.0], [0.5, 0.2, -3.5]], device=DEV)
+    full = loop.render_planes(q, t, gbuffer=True, modes=(0, 1, 4))
+    total = 2 * 30 * 40
+    for G, strip in ((3, 160), (4, 4 * 40), (2, 1000)):
+        pos = torch.empty_like(full.pos)
+        lam = torch.empty_like(full.images[0])
+        nrm = torch.empty_like(full.images[4])
+        dist = torch.empty_like(full.images[1])
+        reduce = torch.empty(8, device=DEV)
+        from ray_marching_b200 import ops
+        ops.check(ops.lib().rm_reduce_init(reduce.data_ptr(), torch.cuda.current_stream().cuda_stream), "init")
+        parts = []
+        for g_ in range(G):
+            sh = parallel.shard_strips(total, g_, G, strip)
+            part = loop.render_planes(q, t, gbuffer=True, modes=(0, 1, 4), finalize=False, **sh)
+            assert part.pos.shape[0] == sh["n_rays"]
+            # shared scratch: combine like the MAX all-reduce would
+            reduce = torch.maximum(reduce, part.reduce)
+            parts.append((sh, part))
+        for sh, part in parts:
+            part.reduce = reduce
+            ops.shade_finalize(part, 1 << 1)
+            idx = parallel.strip_ray_index(sh, device=DEV)
+            pos[idx], lam[idx], nrm[idx], dist[idx] = part.pos, part.images[0], part.images[4], part.images[1]
+        assert torch.equal(pos, full.pos) and torch.equal(lam, full.images[0]) and torch.equal(nrm, full.images[4])
+        assert torch.equal(dist, full.images[1])

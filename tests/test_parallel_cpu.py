@@ -28,6 +28,23 @@ def test_shard_range_partitions_exactly():
     assert sum(len(parallel.shard_views(10, r, 4)) for r in range(4)) == 10
 
 
+def test_shard_strips_partitions_exactly():
+    """Interleaved strips: every ray belongs to exactly one rank; ranks differ by at most one strip."""
+    for total, strip in ((3840 * 2160, 8 * 3840), (1000, 64), (1000, 1000), (1000, 8), (7, 4), (0, 4), (64, 64)):
+        for ws in (1, 2, 3, 8):
+            shards = [parallel.shard_strips(total, r, ws, strip) for r in range(ws)]
+            idx = torch.cat([parallel.strip_ray_index(s) for s in shards])
+            assert idx.numel() == total and torch.equal(idx.sort().values, torch.arange(total))
+            sizes = [s["n_rays"] for s in shards]
+            assert max(sizes) - min(sizes) <= strip
+            for r, s in enumerate(shards):
+                assert s["ray_begin"] == r * strip and s["strip_stride"] == ws * strip
+    with pytest.raises(ValueError):
+        parallel.shard_strips(100, 0, 2, 6)
+    with pytest.raises(ValueError):
+        parallel.shard_strips(100, 2, 2, 8)
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
