@@ -243,6 +243,11 @@ int rm_render_loss_bwd(const RmTape* tape, const RmCamera* cam, const float* pos
  * iters*128 independent FFMA (256 flop).  Not part of the render path. */
 int rm_probe_ffma(int32_t blocks, int32_t iters, float* sink, void* stream);
 
+/* Measurement aid: issue-slot behaviour of the packed FP32 instructions of sm_100 (fma.rn.f32x2).
+ * kind 0 = 128 scalar FFMA per thread and iteration, 1 = the same FMAs as 64 FFMA2, 2 = a march-like
+ * scalar mix (64 FFMA + 32 FMNMX + 16 MUFU), 3 = that mix with the FMAs packed.  Not on the render path. */
+int rm_probe_issue(int32_t kind, int32_t blocks, int32_t iters, float* sink, void* stream);
+
 /* Test hook for the kernels' branch-free correctly rounded arithmetic (csrc/rm_math.cuh): for n
  * operand pairs writes out[6][n] = { sqrt_inline(a), sqrt.rn(a), div_inline(a,b), div.rn(a,b),
  * rcp_or_zero(b), (0 < b < inf ? 1/b : 0) }.  Not part of the render path. */

@@ -245,6 +245,21 @@ def gen_grads_c4b(ref, out):
     out["grads/syn64/dparams_flat"] = np32(torch.cat(
         [(gp if gp is not None else torch.zeros_like(p)).reshape(-1)
          for (_, p), gp in zip(params, grads[2:])]))
+    # the same gradient through the SAME reference modules in float64 (the exact value up to 1e-16): the
+    # yardstick for how much of a float32 discrepancy is the reference's own rounding noise
+    loop.double()
+    params64 = param_list(scene)
+    q64 = q.detach().double().requires_grad_(True)
+    t64 = t.detach().double().requires_grad_(True)
+    lam, depth = gbuf(q64, t64)
+    loss64 = ((lam - lam_t.double()) ** 2).mean() + ((depth - depth_t.double()) ** 2).mean()
+    grads64 = torch.autograd.grad(loss64, [q64, t64] + [p for _, p in params64], allow_unused=True)
+    out["grads/syn64/loss64"] = loss64.detach().numpy()
+    out["grads/syn64/dq64"] = grads64[0].numpy()
+    out["grads/syn64/dt64"] = grads64[1].numpy()
+    out["grads/syn64/dparams_flat64"] = torch.cat(
+        [(gp if gp is not None else torch.zeros_like(p)).reshape(-1)
+         for (_, p), gp in zip(params64, grads64[2:])]).numpy()
 
 
 def gen_api_surface(ref):

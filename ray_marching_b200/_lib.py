@@ -88,6 +88,7 @@ _SIGNATURES = {
                                      C.POINTER(RmRenderArgs), C.POINTER(RmLossArgs), C.c_void_p,
                                      C.c_void_p, C.c_void_p, C.c_void_p]),
     "rm_probe_ffma": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "rm_probe_issue": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "rm_probe_math": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),
 }
 

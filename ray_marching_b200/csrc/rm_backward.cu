@@ -485,11 +485,12 @@ __device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const
                 const bool valid = first + k < n;
                 float ob[3], vb[3], ow[3], vw[3];
                 world_ray(P.cam, poses, r, pose, cur_view, ob, vb, ow, vw);      // origin, regenerated
+                const bool has_n = P.target_lam != nullptr;     // no lambertian term: the stencil was not sampled
                 const float len = sqrt_rn_inline(ux[k] * ux[k] + uy[k] * uy[k] + uz[k] * uz[k]);
-                const float il = div_rn_inline(1.f, len);
+                const float il = has_n ? div_rn_inline(1.f, len) : 0.f;
                 const float nx = ux[k] * il, ny = uy[k] * il, nz = uz[k] * il;
                 float g_lam = 0.f, g_dep = 0.f;
-                if (P.target_lam != nullptr && valid) {
+                if (has_n && valid) {
                     const float nv = -(vx[k] * nx + vy[k] * ny + vz[k] * nz);
                     const float res = clamp_nan(nv, 0.f, 1.f) - __ldg(P.target_lam + first + k);
                     loss_l = fmaf(res, res, loss_l);
@@ -513,7 +514,6 @@ __device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const
                 // d nrm / d u = (I - nrm nrm^T) / |u| applied to g_n = -g_lam v
                 const float gnx = -g_lam * vx[k], gny = -g_lam * vy[k], gnz = -g_lam * vz[k];
                 const float gn = gnx * nx + gny * ny + gnz * nz;
-                const bool has_n = P.target_lam != nullptr;
                 sa.gux[k] = has_n ? (gnx - gn * nx) * il : 0.f;
                 sa.guy[k] = has_n ? (gny - gn * ny) * il : 0.f;
                 sa.guz[k] = has_n ? (gnz - gn * nz) * il : 0.f;

@@ -7,7 +7,9 @@ Yardsticks:
   * the oracle run in float64, which is the exact gradient: float32 autograd of the reference is
     itself ill-conditioned for some parameters (d/dk of a smooth union cancels to 0.0 instead of
     0.0272 on `smooth_nested`, see tests/test_tape_lowering.py), so those are checked against
-    float64 instead.
+    float64 instead;
+  * where the comparison is against a float32 autograd run made in the test, `grad_close` states the
+    budget: 1e-3 plus the measured float32 rounding error of that reference (never a flat 2e-3).
 """
 import copy
 
@@ -30,6 +32,19 @@ def rel_err(got, want):
     want = want.detach().cpu().double().numpy() if isinstance(want, torch.Tensor) else np.asarray(want, dtype=np.float64)
     assert got.shape == want.shape, (got.shape, want.shape)
     return np.abs(got - want).max() / (np.abs(want).max() + 1e-30)
+
+
+def grad_close(got, ref32, ref64, what=""):
+    """north_star: gradients to 1e-3 relative (max-norm per tensor) against the reference autograd.  The
+    reference's float32 autograd is itself a rounded value; its distance to the same graph in float64 is
+    measured in the test (`noise`).  Budget: 1e-3 + noise against the exact (float64) gradient, 1e-3 +
+    2 noise against the float32 one (two rounded values).  Where the reference is well conditioned
+    (noise << 1e-3) this IS the 1e-3 bar; a float32 reference that is off by more than 1e-3 itself cannot
+    arbitrate and fails the test instead of widening the tolerance."""
+    noise = rel_err(ref32, ref64)
+    e32, e64 = rel_err(got, ref32), rel_err(got, ref64)
+    assert noise < 1e-3, (what, "reference float32 gradient unusable", noise)
+    assert e64 < 1e-3 + noise and e32 < 1e-3 + 2 * noise, (what, e32, e64, noise)
 
 
 def flat_grads(params):
@@ -70,8 +85,7 @@ def test_sdf_vjp(golden, name):
     key = f"scenes/{GOLD_KEY[name]}/dpoints" if name in SCENES else f"nodes/{name}/dpoints"
     assert rel_err(x.grad[keep], g[key][keep.numpy()]) < 1e-3
     if name in SCENES:
-        ref = g[f"scenes/{GOLD_KEY[name]}/dparams_flat"]
-        assert rel_err(flat_grads(params), ref) < 2e-3
+        grad_close(flat_grads(params), g[f"scenes/{GOLD_KEY[name]}/dparams_flat"], flat_grads(list(n64.parameters())), name)
 
 
 def test_sdf_vjp_edge_cases():
@@ -118,9 +132,13 @@ def test_march_backward_matches_unrolled_autograd(name):
     (pos * wm.to(DEV)).sum().backward()
     np.testing.assert_allclose(pos.detach().cpu().numpy()[conv], pos_ref.detach().numpy()[conv],
                                rtol=1e-4, atol=1e-5)
-    assert rel_err(od.grad, oo.grad) < 2e-3
-    assert rel_err(vd.grad, vv.grad) < 2e-3
-    assert rel_err(flat_grads(list(scene.parameters())), flat_grads(list(ref_scene.parameters()))) < 2e-3
+    s64 = copy.deepcopy(SCENES[name]()).double()                     # the same graph in float64
+    o64, v64 = o.double().requires_grad_(True), v.double().requires_grad_(True)
+    (O.march(s64, o64, v64, 32) * wm.double()).sum().backward()
+    grad_close(od.grad, oo.grad, o64.grad, "d origin")
+    grad_close(vd.grad, vv.grad, v64.grad, "d dirs")
+    grad_close(flat_grads(list(scene.parameters())), flat_grads(list(ref_scene.parameters())),
+               flat_grads(list(s64.parameters())), "d params")
 
 
 @pytest.mark.parametrize("tag,build", [("scene2", S.make_test_scene2),
@@ -165,11 +183,16 @@ def test_render_loop_forward_is_differentiable_in_every_finite_mode():
         np.testing.assert_allclose(img.detach().cpu().numpy(), ref.detach().numpy(), atol=1e-3)
         img.mean().backward()
         ref.mean().backward()
-        assert rel_err(q.grad, qr.grad) < 2e-3, mode
+        s64 = copy.deepcopy(S.make_test_scene2()).double()
+        o64 = O.RenderLoopOracle(s64, normals_eps=5e-2, **intr)
+        o64.base = tuple(b.double() for b in o64.base)
+        q64, t64 = q0.double().requires_grad_(True), t0.double().requires_grad_(True)
+        o64(q64, t64, mode, 1, 32).mean().backward()
+        grad_close(q.grad, qr.grad, q64.grad, f"mode {mode} dq")
         if mode != 3:                                        # vignette depends on the camera only
-            assert rel_err(t.grad, tr.grad) < 2e-3, mode
-            assert rel_err(flat_grads(list(scene.parameters())),
-                           flat_grads(list(ref_scene.parameters()))) < 2e-3, mode
+            grad_close(t.grad, tr.grad, t64.grad, f"mode {mode} dt")
+            grad_close(flat_grads(list(scene.parameters())), flat_grads(list(ref_scene.parameters())),
+                       flat_grads(list(s64.parameters())), f"mode {mode} dparams")
 
 
 @pytest.mark.parametrize("tag,build", [("scene2", S.make_test_scene2),
@@ -212,19 +235,29 @@ def test_fused_render_bwd_every_plane_and_two_views():
            "normals": ref["normals"], "laplacian": ref["lap"]}
     gen = torch.Generator().manual_seed(11)
     loss = loss_ref = 0.0
+    weights = {}
     for name, scale in [("origin", 1.0), ("dirs", 1.0), ("pos", 1.0), ("sdf", 1.0), ("normals", 1.0),
                         ("laplacian", 1e-3)]:
         w = torch.randn(ref[name].shape, generator=gen) * scale
-        np.testing.assert_allclose(gb[name].detach().cpu().numpy(), ref[name].detach().numpy(),
-                                   rtol=2e-3 if name == "laplacian" else 1e-4,
-                                   atol=2e-2 if name == "laplacian" else 1e-5)
+        weights[name] = w
+        if name != "laplacian":          # (the Laplacian plane's float32 noise floor is tested in test_gpu_forward)
+            np.testing.assert_allclose(gb[name].detach().cpu().numpy(), ref[name].detach().numpy(), rtol=1e-4, atol=1e-5)
         loss = loss + (gb[name] * w.to(DEV)).sum()
         loss_ref = loss_ref + (ref[name] * w).sum()
     loss.backward()
     loss_ref.backward()
-    assert rel_err(q.grad, qr.grad) < 2e-3
-    assert rel_err(t.grad, tr.grad) < 2e-3
-    assert rel_err(flat_grads(list(scene.parameters())), flat_grads(list(ref_scene.parameters()))) < 2e-3
+    s64 = copy.deepcopy(S.make_test_scene2()).double()
+    o64 = O.RenderLoopOracle(s64, normals_eps=5e-2, **intr)
+    o64.base = tuple(b.double() for b in o64.base)
+    q64, t64 = q0.double().requires_grad_(True), t0.double().requires_grad_(True)
+    r64 = o64.gbuffer(q64, t64, 32)
+    r64 = {"origin": r64["px"], "dirs": r64["dirs"], "pos": r64["pos"], "sdf": r64["dists"],
+           "normals": r64["normals"], "laplacian": r64["lap"]}
+    sum((r64[name] * w.double()).sum() for name, w in weights.items()).backward()
+    grad_close(q.grad, qr.grad, q64.grad, "dq")
+    grad_close(t.grad, tr.grad, t64.grad, "dt")
+    grad_close(flat_grads(list(scene.parameters())), flat_grads(list(ref_scene.parameters())),
+               flat_grads(list(s64.parameters())), "dparams")
 
 
 def test_fused_render_bwd_unused_planes_are_skipped():
@@ -239,8 +272,15 @@ def test_fused_render_bwd_unused_planes_are_skipped():
     qr, tr = q0.clone().requires_grad_(True), t0.clone().requires_grad_(True)
     (loop.gbuffer(q, t, 32)["pos"] ** 2).mean().backward()
     (orc.gbuffer(qr, tr, 32)["pos"] ** 2).mean().backward()
-    assert rel_err(q.grad, qr.grad) < 2e-3 and rel_err(t.grad, tr.grad) < 2e-3
-    assert rel_err(flat_grads(list(scene.parameters())), flat_grads(list(ref_scene.parameters()))) < 2e-3
+    s64 = copy.deepcopy(S.make_test_scene2()).double()
+    o64 = O.RenderLoopOracle(s64, normals_eps=5e-2, **intr)
+    o64.base = tuple(b.double() for b in o64.base)
+    q64, t64 = q0.double().requires_grad_(True), t0.double().requires_grad_(True)
+    (o64.gbuffer(q64, t64, 32)["pos"] ** 2).mean().backward()
+    grad_close(q.grad, qr.grad, q64.grad, "dq")
+    grad_close(t.grad, tr.grad, t64.grad, "dt")
+    grad_close(flat_grads(list(scene.parameters())), flat_grads(list(ref_scene.parameters())),
+               flat_grads(list(s64.parameters())), "dparams")
 
 
 @pytest.mark.parametrize("tol", [0.0, 1e-7, 1e-6])

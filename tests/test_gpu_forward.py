@@ -21,6 +21,28 @@ C = _default_classes()
 DEV = "cuda"
 
 
+def lap_close(lap_gpu, lap32, scene_fn, pos32, what=""):
+    """Laplacian = (f(p) - mean_4 f(p + off)) * 6/eps^2: differences of O(1e-2) float32 values scaled by
+    2400, i.e. an ABSOLUTE rounding noise of a few 1e-3 in the reference itself.  Yardstick: the float64
+    oracle at the reference's hit points is the exact value; the CUDA result must be as close to it as the
+    reference's own float32 evaluation is, within a factor 2 (floor 1e-3)."""
+    import copy
+    s64 = copy.deepcopy(scene_fn()).double()
+    with torch.no_grad():
+        _, lap64 = O.normals_laplacian(s64, torch.as_tensor(pos32).double(), 5e-2)
+    lap64 = lap64.reshape(-1).numpy()
+    lap_gpu = lap_gpu.detach().cpu().double().numpy().reshape(-1) if isinstance(lap_gpu, torch.Tensor) else np.asarray(lap_gpu, dtype=np.float64).reshape(-1)
+    e_ref = np.abs(np.asarray(lap32, dtype=np.float64).reshape(-1) - lap64).max()
+    e_gpu = np.abs(lap_gpu - lap64).max()
+    # Floor: ONE float32 rounding of a coordinate of size |p| moves f by up to ulp(|p|) and the Laplacian by
+    # 6/eps^2 ulp(|p|) (= 1.1e-3 at |p| = 5, 1.4e-4 at |p| = 0.75); the frame transform and the five samples
+    # contribute a handful of such roundings, in a different order than the reference's quaternion form
+    # (its own error `e_ref` is a max over mostly flat hits and can be lucky): 4 of them.  This replaces the
+    # flat 2e-2 of round 1.  (The GPU evaluates at ITS hit points; |grad L| x 1e-6 is below this floor.)
+    floor = 4.0 * (6.0 / 5e-2 ** 2) * float(np.spacing(np.float32(np.abs(np.asarray(pos32)).max())))
+    assert e_gpu <= max(2.0 * e_ref, floor), (what, e_gpu, e_ref, floor)
+
+
 def close(a, b, rtol, atol, what=""):
     a = a.detach().cpu().numpy() if isinstance(a, torch.Tensor) else np.asarray(a)
     b = b.detach().cpu().numpy() if isinstance(b, torch.Tensor) else np.asarray(b)
@@ -108,7 +130,7 @@ def test_gbuffer_matches_reference_fixture(golden, tag, build, fast):
     n_got, n_ref = res.normals.cpu().numpy()[hit], ref["normals"][hit]
     assert np.isfinite(n_got).all()
     np.testing.assert_allclose(n_got, n_ref, atol=1e-3)
-    np.testing.assert_allclose(res.laplacian.cpu().numpy()[hit], ref["lap"][hit, 0], rtol=2e-3, atol=2e-2)
+    lap_close(res.laplacian[torch.from_numpy(hit).to(DEV)], ref["lap"][hit, 0], build, ref["pos"][hit], tag)
     if tag == "scene2":                                  # closed scene: every ray hits
         assert hit.all()
 
@@ -174,7 +196,7 @@ def test_marcher_and_normals_modules(golden):
     assert pos.shape == pos0.shape and n.shape == pos0.shape and lap.shape == (1, 24, 32, 1)
     close(pos, g["render/scene2/pos"], 1e-4, 1e-5, "march")
     close(n, g["render/scene2/normals"], 0, 1e-3, "normals")
-    close(lap, g["render/scene2/lap"], 2e-3, 2e-2, "laplacian")
+    lap_close(lap, g["render/scene2/lap"], S.make_test_scene2, g["render/scene2/pos"].reshape(-1, 3), "laplacian")
     ref7 = O.march(S.make_test_scene2(), pos0.cpu(), dirs.cpu(), 7)
     close(pos7, ref7.detach(), 1e-4, 1e-5, "march 7 steps")
     assert SDFMarcher(scene)(pos0, dirs, 0).equal(pos0)
