@@ -188,6 +188,11 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
         if (tiles > 0x7fffffff) return fail(RM_ERR_INVALID, "rm_render: ray range too large for one launch");
         P.tile_base = (int)(tiles / grid); P.tile_rem = (int)(tiles % grid);     // persistent tiling only
     }
+    // Approximate-math stencil samples (stencil_eval<.., SFAST>): only when no output of this frame needs correctly
+    // rounded samples -- no Laplacian, no reported f(p) (sdf plane, proximity shader), no G-buffer plane.
+    const bool any_gbuffer = out->origin || out->dirs || out->pos || out->sdf || out->normals || out->laplacian;
+    const bool sfast = a->fast_math >= 1 && !any_gbuffer &&
+                       !(mask & (RM_MODE_LAPLACIAN | RM_MODE_PROXIMITY)) && RM_SFAST;
 #ifdef RM_SPEC_INC
     // specialised library: one code capacity, no culling variant; refuses any other tape
     if (tape->n_instr > CODE_CAP_SMALL || tape_code_hash(tape) != RM_SPEC_HASH)
@@ -197,7 +202,11 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
         constexpr int CAP = CODE_CAP_SMALL;
         TapeCode<CAP> code;
         expand_code(tape->code_host, tape->n_instr, code, false);
-        if (a->fast_math) {
+        if (sfast) {
+            if (int s = prepare_smem(render_kernel<true, CAP, false, true>, sm)) return s;
+            render_kernel<true, CAP, false, true><<<grid, threads, sm, (cudaStream_t)stream>>>(
+                code, tape->par, tape->n_instr, tape->n_par, poses, P);
+        } else if (a->fast_math) {
             if (int s = prepare_smem(render_kernel<true, CAP, false>, sm)) return s;
             render_kernel<true, CAP, false><<<grid, threads, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);
@@ -209,7 +218,15 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
     }
 #else
     RM_WITH_CODE_EX(tape, a->fast_math >= 2, {
-        if (a->fast_math >= 2) {
+        if (sfast && a->fast_math >= 2) {
+            if (int s = prepare_smem(render_kernel<true, CAP, true, true>, sm)) return s;
+            render_kernel<true, CAP, true, true><<<grid, threads, sm, (cudaStream_t)stream>>>(
+                code, tape->par, tape->n_instr, tape->n_par, poses, P);
+        } else if (sfast) {
+            if (int s = prepare_smem(render_kernel<true, CAP, false, true>, sm)) return s;
+            render_kernel<true, CAP, false, true><<<grid, threads, sm, (cudaStream_t)stream>>>(
+                code, tape->par, tape->n_instr, tape->n_par, poses, P);
+        } else if (a->fast_math >= 2) {
             if (int s = prepare_smem(render_kernel<true, CAP, true>, sm)) return s;
             render_kernel<true, CAP, true><<<grid, threads, sm, (cudaStream_t)stream>>>(
                 code, tape->par, tape->n_instr, tape->n_par, poses, P);

@@ -40,6 +40,9 @@ namespace rm {
 #ifndef RM_KB
 #define RM_KB 1
 #endif
+#ifndef RM_LOSS_FAST_REPLAY
+#define RM_LOSS_FAST_REPLAY 1     // rm_render_loss_bwd replays the march with approximate sqrt / exp (see forward_pass)
+#endif
 constexpr int KB = RM_KB;        // samples per thread in the backward kernels (1, 2 or 4)
 constexpr int BLOCK_B = 128;
 
@@ -158,7 +161,11 @@ struct StencilAdjoint {          // per-sample inputs of the stencil's reverse t
 // conv[k] = first step from which every step length stayed within tol * (1 + |p|_inf) (= steps when
 // the ray never settles, or when tol == 0): the tail [conv, steps) is a stationary point of the
 // iteration to first order in tol.
-template <int CAP>
+// FASTM: approximate sqrt / exp in the replay.  rm_render_loss_bwd replays with it -- the kernel IS the
+// forward of its loss, so there is no separately computed trajectory to reproduce, and a 2^-22 relative
+// change of the evaluation points moves the gradient by ~1e-6 of its size.  rm_render_bwd / rm_march_bwd keep
+// the IEEE replay (it mirrors the IEEE forward kernel that produced the planes).
+template <int CAP, bool FASTM = false>
 __device__ __forceinline__ void forward_pass(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                              int steps, float tol, const Stencil* st, float* traj,
                                              float (&px)[KB], float (&py)[KB], float (&pz)[KB],
@@ -178,7 +185,9 @@ __device__ __forceinline__ void forward_pass(const TapeCode<CAP>& code, int n_in
         else traj_store(traj, task, px, py, pz);
 #pragma unroll
         for (int k = 0; k < KB; ++k) { x[k] = px[k] + dx; y[k] = py[k] + dy; z[k] = pz[k] + dz; }
-        eval_scene<KB, false, CAP>(code, n_instr, spar, x, y, z, d);
+        // ONE call site for steps and samples (a second, correctly rounded one for the samples costs c4b
+        // 32.9 -> 35.3 ms in instruction-cache misses and changes no gradient digit: profiles/r02/variants.md)
+        eval_scene<KB, FASTM, CAP>(code, n_instr, spar, x, y, z, d);
         if (marching) {
             bool at_rest = true;
 #pragma unroll
@@ -471,8 +480,8 @@ __device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const
         // ---- forward pass: replay the march, sample the stencil offsets ----
         int conv[KB];
         float ux[KB], uy[KB], uz[KB];
-        forward_pass<CAP>(code, n_instr, spar, P.steps, P.tol, need_stencil ? &P.st : nullptr, P.traj,
-                          px, py, pz, vx, vy, vz, conv, ux, uy, uz);
+        forward_pass<CAP, LOSS && RM_LOSS_FAST_REPLAY>(code, n_instr, spar, P.steps, P.tol, need_stencil ? &P.st : nullptr,
+                                                       P.traj, px, py, pz, vx, vy, vz, conv, ux, uy, uz);
 
         // ---- adjoints of the stencil outputs (SDFNormals.forward, ray_marching.py:115-125), of
         //      f(p_S) (control.py:244), of p_S, the direction and the origin ----

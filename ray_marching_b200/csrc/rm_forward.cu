@@ -32,6 +32,12 @@
 #ifndef RM_SPEC_UNROLL
 #define RM_SPEC_UNROLL 2        // march-loop unrolling of the tape-specialised kernel
 #endif
+#ifndef RM_SFAST
+#define RM_SFAST 1              // 1: frames without Laplacian / reported f / G-buffer take march_stencil_fast
+#endif
+#ifndef RM_STEP_SYNC
+#define RM_STEP_SYNC 0          // 1: block barrier before every march step (see march_rays)
+#endif
 #ifndef RM_PERSIST
 #define RM_PERSIST 0            // 1: persistent balanced tiling in render_kernel (measured slower: profiles/r01/variants.md)
 #endif
@@ -235,6 +241,11 @@ __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_inst
     }
 #endif
     for (int s = 0; s < steps; ++s) {                 // one interpreter instance (instruction cache)
+#if RM_STEP_SYNC
+        // keep the block's warps in phase: they then walk the interpreter's code together and share its
+        // instruction-cache lines (block-uniform trip count: legal whenever early_exit is off)
+        if (!early_exit) __syncthreads();
+#endif
         eval_scene<K, FAST, CAP, CULL ? 2 : 0>(code, n_instr, spar, px, py, pz, d, hint, move);
         bool moved = false;
 #pragma unroll
@@ -274,7 +285,14 @@ march_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n
 // One call site of the interpreter; the samples are folded into the normal / Laplacian on the fly
 // (o_0, the running sum, and Ainv (o_j - o_0) accumulated column by column, in the reference's
 // summation order) so that no per-sample storage and no sample-dependent branch is needed.
-template <int CAP, bool CULLFLAGS = false>
+// SFAST: the samples use the march's approximate sqrt / exp.  For frames whose outputs do not amplify
+// rounding -- no Laplacian (x 6/eps^2 = 2400), no reported f(p), no G-buffer plane: just shaded pixels from
+// the normal -- a 2^-22 relative error on f moves the normal by ~1e-5, a hundred times inside the 1e-3 pixel
+// tolerance, and the five samples cost what march steps cost instead of ~1.8x (IEEE expf, rounded sqrt).
+// (Folding the samples into the march loop, so that ONE interpreter instance serves both, was measured
+// slower: the stencil accumulators stay live across the march and spill at 64 registers --
+// profiles/r02/variants.md.)
+template <int CAP, bool CULLFLAGS = false, bool SFAST = false>
 __device__ __forceinline__ void stencil_eval(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                              const Stencil& st, bool need_offsets,
                                              const float (&px)[K], const float (&py)[K],
@@ -289,7 +307,7 @@ __device__ __forceinline__ void stencil_eval(const TapeCode<CAP>& code, int n_in
         const float dx = st.off[j][0], dy = st.off[j][1], dz = st.off[j][2];
 #pragma unroll
         for (int k = 0; k < K; ++k) { x[k] = px[k] + dx; y[k] = py[k] + dy; z[k] = pz[k] + dz; }
-        eval_scene<K, false, CAP, CULLFLAGS ? 1 : 0>(code, n_instr, spar, x, y, z, d);
+        eval_scene<K, SFAST, CAP, CULLFLAGS ? 1 : 0>(code, n_instr, spar, x, y, z, d);
         const float wx = st.w[j][0], wy = st.w[j][1], wz = st.w[j][2];
         const float first = st.first[j], in_sum = st.in_sum[j];
 #pragma unroll

@@ -66,7 +66,9 @@ __device__ __forceinline__ void block_minmax(MinMax m, float* gmin, float* gmax,
     }
 }
 
-template <bool FAST, int CAP, bool CULL>
+// SFAST: the stencil samples use the march's approximate math (stencil_eval, rm_forward.cu); chosen by
+// rm_render when nothing the frame outputs needs correctly rounded samples.
+template <bool FAST, int CAP, bool CULL, bool SFAST = false>
 __global__ void __launch_bounds__(BLOCK, RM_MINB)
 render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
               const float* __restrict__ poses, const __grid_constant__ RenderParams P) {
@@ -120,7 +122,7 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
 
         for (int b = 0;; ++b) {
             march_rays<FAST, CAP, CULL>(code, n_instr, spar, P.steps, P.early_exit != 0, px, py, pz, vx, vy, vz);
-            stencil_eval<CAP, CULL>(code, n_instr, spar, P.st, need_stencil, px, py, pz, f, nx, ny, nz, lap);
+            stencil_eval<CAP, CULL, SFAST>(code, n_instr, spar, P.st, need_stencil, px, py, pz, f, nx, ny, nz, lap);
             if (b >= P.bounces) break;
             // reflected-ray branch (reflect = control.py:179-194)
 #pragma unroll

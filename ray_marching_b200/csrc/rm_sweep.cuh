@@ -135,6 +135,7 @@ struct GradAcc {
 // Softmax weights below this are treated as zero (smooth-union children far behind the surface);
 // a 512-child union then loses at most 512e-9 of the gradient, far inside the 1e-3 tolerance.
 constexpr float CULL_EPS = 1e-9f;
+constexpr float LOG_CULL_EPS = -20.723266f;        // ln(1e-9)
 
 // The reverse sweep.  Outputs g{x,y,z}[k] = abar[k] * grad_p f(p_k) and adds d f / d par into
 // `acc`.  All 32 lanes of the warp must call this together (warp votes skip leaves whose adjoint
@@ -194,6 +195,24 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
             continue;
         }
         // ---- leaf ------------------------------------------------------------------------
+        // cheap pre-test FIRST (most leaves of a large smooth union are dead: nothing is loaded for them):
+        // is any lane's adjoint of this child non-zero?
+        bool live = false;
+        if (fold == FOLD_MIN) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) live |= (cur.win[k] == ordinal) && cur.a[k] != 0.f;
+        } else if (fold == FOLD_SMOOTH) {
+            // softmax weight exp(c (y - d_U)) >= CULL_EPS  <=>  c (y - d_U) >= ln CULL_EPS, from the child's
+            // value recorded by pass 1 (no re-evaluation, no exp)
+#pragma unroll
+            for (int k = 0; k < K; ++k)
+                live |= cur.a[k] != 0.f && cur.c * (rec.y[pc][k] - cur.d[k]) >= LOG_CULL_EPS;
+        } else {
+#pragma unroll
+            for (int k = 0; k < K; ++k) live |= abar[k] != 0.f;
+        }
+        if (!__any_sync(0xffffffffu, live)) continue;
+
         const bool has_frame = (head & HEAD_FRAME) != 0;
         const int prim_rec = off + (has_frame ? 3 : 0);
         const int post_rec = prim_rec + prim_f4(op);
@@ -202,24 +221,6 @@ __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_in
         if (has_frame) { r0 = spar[off]; r1 = spar[off + 1]; r2 = spar[off + 2]; }
         const float4 pp = np ? spar[post_rec] : make_float4(0.f, 0.f, 0.f, 0.f);
         const float pv[3] = {pp.x, pp.y, pp.z};
-
-        // cheap pre-test: is any lane's adjoint of this child non-zero?
-        bool live = false;
-        if (fold == FOLD_MIN) {
-#pragma unroll
-            for (int k = 0; k < K; ++k) live |= (cur.win[k] == ordinal) && cur.a[k] != 0.f;
-        } else if (fold == FOLD_SMOOTH) {
-            // softmax weight from the child's value recorded by pass 1 (no re-evaluation)
-#pragma unroll
-            for (int k = 0; k < K; ++k) {
-                const float w = expf(cur.c * (rec.y[pc][k] - cur.d[k]));
-                live |= cur.a[k] != 0.f && w >= CULL_EPS;
-            }
-        } else {
-#pragma unroll
-            for (int k = 0; k < K; ++k) live |= abar[k] != 0.f;
-        }
-        if (!__any_sync(0xffffffffu, live)) continue;
 
         // value + local gradients, one sample at a time (keeps the 15 local partials of a sample
         // short-lived); per-thread sums over the K samples of every parameter partial

@@ -370,7 +370,10 @@ def test_loss_fused_kernel_equals_the_composed_route_and_shards_sum():
         la, qa, ta, pa, _, _ = run(False, which, scale)
         lb, qb, tb, pb, loop, scene = run(True, which, scale)
         assert abs(la - lb) < 1e-6 * max(1.0, abs(la)), which
-        assert rel_err(qb, qa) < 1e-4 and rel_err(tb, ta) < 1e-4 and rel_err(pb, pa) < 1e-4, (which, scale)
+        # the routes differ in the math policy of the replayed march (the fused kernel replays with the
+        # approximate sqrt, the composed route with the rounded one): agreement to a fraction of the 1e-3
+        # budget each of them has against the reference (fixture tests above)
+        assert rel_err(qb, qa) < 3e-4 and rel_err(tb, ta) < 3e-4 and rel_err(pb, pa) < 3e-4, (which, scale)
 
     # shards: three ray ranges (not multiples of 4) of the fused kernel sum to the whole batch
     total = 2 * 9 * 23

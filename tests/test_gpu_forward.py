@@ -450,3 +450,46 @@ def test_interleaved_strip_shards_equal_the_full_frame():
             pos[idx], lam[idx], nrm[idx], dist[idx] = part.pos, part.images[0], part.images[4], part.images[1]
         assert torch.equal(pos, full.pos) and torch.equal(lam, full.images[0]) and torch.equal(nrm, full.images[4])
         assert torch.equal(dist, full.images[1])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("tag,build,t0,bounces,cull", [
+    ("scene2", S.make_test_scene2, (0.0, 0.0, 1.0), 0, False),
+    ("syn8", lambda: S.make_synthetic_scene(8, 0, True), (0.3, -0.2, -4.0), 0, False),
+    ("syn64", lambda: S.make_synthetic_scene(64, 0, True), (0.0, 0.0, -4.0), 0, True),
+    ("syn64", lambda: S.make_synthetic_scene(64, 0, True), (0.0, 0.0, -4.0), 2, False),
+])
+def test_fast_stencil_path_matches_the_rounded_one(tag, build, t0, bounces, cull):
+    """rm_render picks march_stencil_fast (one approximate-math interpreter instance for the march AND the
+    stencil samples) when the frame outputs neither a Laplacian, nor f(p), nor a G-buffer plane.  Its pixels
+    must equal those of the correctly rounded stencil (requested here through gbuffer=True) far inside the
+    1e-3 pixel tolerance: the approximate sqrt / exp move f by 2^-22 relative, the normal by ~1e-5."""
+    loop = _loop(build(), 96, 64)
+    loop.cull = cull
+    q = torch.nn.functional.normalize(torch.tensor([[0.99, 0.03, -0.08, 0.05]], device=DEV), dim=-1)
+    t = torch.tensor([list(t0)], device=DEV)
+    modes = (0, 3, 4, 6, 7)
+    ieee = loop.render_planes(q, t, gbuffer=True, modes=modes, bounces=bounces, degree=2)
+    fast = loop.render_planes(q, t, modes=modes, bounces=bounces, degree=2)
+    assert fast.pos is None and fast.normals is None
+    if bounces == 0:
+        ok = torch.ones(96 * 64, dtype=torch.bool, device=DEV)
+    else:
+        # multi-bounce rays are chaotic (tests/test_gpu_fullsize.py): compare where the math policy of the
+        # MARCH does not move the end point (IEEE march vs approximate march, both with the rounded stencil)
+        loop.fast_math = False
+        exact = loop.render_planes(q, t, gbuffer=True, modes=modes, bounces=bounces, degree=2)
+        loop.fast_math = True
+        ok = (exact.pos - ieee.pos).norm(dim=-1) < 1e-5
+        assert ok.float().mean().item() > 0.5
+    for m in (0, 3, 4):
+        d = (fast.images[m] - ieee.images[m]).abs()[ok]
+        assert torch.equal(torch.isnan(fast.images[m]), torch.isnan(ieee.images[m]))
+        frac = (d <= 1e-4).float().mean().item()
+        assert frac >= (1.0 if bounces == 0 else 0.97) and (bounces or d.max().item() <= 1e-4), (m, frac, d.max().item())
+    for m in (6, 7):                                     # colour wheel: a LUT entry off on < 1 % of pixels
+        d = (fast.images[m] - ieee.images[m]).abs()[ok]
+        assert (d > 1e-3).float().mean().item() < 0.01
+    # the display buffer takes the same path
+    rgba = loop.display_frame(q, t, mode=0)
+    assert (rgba[..., 0].reshape(-1) - fast.images[0].reshape(-1)).abs().max().item() == 0.0 or bounces
