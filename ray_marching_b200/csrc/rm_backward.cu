@@ -229,7 +229,7 @@ __device__ __forceinline__ void forward_pass(const TapeCode<CAP>& code, int n_in
 //          with a_0 (S_n - 1), S_n = sum_{j<n} c^j, n = S - conv: the implicit-surface adjoint of the
 //          hit point truncated to the n steps the reference unrolls; O(tol) from the step-by-step sum.
 //   7..    exact steps s = max_warp(conv) - 1 .. 0 of the unrolled graph.
-template <int CAP, int MODE>
+template <int CAP, int MODE, bool FASTM = false>
 __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                              int steps, const Stencil* st, const StencilAdjoint* sa,
                                              float* traj, const GradAcc<MODE> sacc, const int (&conv)[KB],
@@ -282,7 +282,7 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
                 a[k] = s < conv[k] ? lx[k] * vx[k] + ly[k] * vy[k] + lz[k] * vz[k] : 0.f;
         }
         NodeRecords<KB, CAP> rec;
-        eval_record<KB, CAP>(code, n_instr, spar, x, y, z, rec, f);
+        eval_record<KB, CAP, FASTM>(code, n_instr, spar, x, y, z, rec, f);
         sweep_vjp<KB, CAP, MODE>(code, n_instr, spar, x, y, z, a, rec, sacc, gx, gy, gz);
         if (task < 5) {
 #pragma unroll
@@ -553,7 +553,7 @@ __device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const
         if (LOSS && !P.want_grad) continue;                 // loss evaluation only
 
         // ---- reverse pass: stencil samples, converged tail, exact steps ----
-        reverse_pass<CAP, MODE>(code, n_instr, spar, P.steps, &P.st,
+        reverse_pass<CAP, MODE, LOSS && RM_LOSS_FAST_REPLAY>(code, n_instr, spar, P.steps, &P.st,
                           (need_stencil || (!LOSS && P.g.sdf != nullptr)) ? &sa : nullptr, P.traj, sacc, conv,
                           px, py, pz, vx, vy, vz, lx, ly, lz, dvx, dvy, dvz);
 

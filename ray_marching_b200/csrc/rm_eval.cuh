@@ -194,7 +194,7 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
                 } else {
                     const float4 u = P[0];           // (-k, s_min, L_max, log2 n)
                     c = M::exp_scale(u.x);
-                    if (RECORD) rec->c[word_node(ins.y)] = c;
+                    if (RECORD) rec->c[word_node(ins.y)] = u.x;      // natural -k (c is base-2 scaled under FAST)
 #pragma unroll
                     for (int k = 0; k < K; ++k) { a0[k] = -CUDART_INF_F; a1[k] = 0.f; }
                     if (CULL && (disp_raw & DISP_CULL) && u.w > 0.f) {

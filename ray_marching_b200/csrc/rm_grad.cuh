@@ -116,14 +116,15 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
-// Pass 1 of the scene VJP: forward evaluation (IEEE math) that fills the node records -- the
+// Pass 1 of the scene VJP: forward evaluation (IEEE math; approximate with FASTM, see forward_pass in
+// rm_backward.cu) that fills the node records -- the
 // interpreter of rm_eval.cuh in RECORD mode.  Returns f(p_k).
-template <int K, int CAP>
+template <int K, int CAP, bool FASTM = false>
 __device__ __forceinline__ void eval_record(const TapeCode<CAP>& C, const int n_instr,
                                             const float4* __restrict__ spar, const float (&px)[K],
                                             const float (&py)[K], const float (&pz)[K],
                                             NodeRecords<K, CAP>& rec, float (&out)[K]) {
-    eval_scene<K, false, CAP, 0, true>(C, n_instr, spar, px, py, pz, out, nullptr, nullptr, &rec);
+    eval_scene<K, FASTM, CAP, 0, true>(C, n_instr, spar, px, py, pz, out, nullptr, nullptr, &rec);
 }
 
 }  // namespace rm
