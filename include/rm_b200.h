@@ -191,6 +191,24 @@ int rm_march_bwd(const RmTape* tape, const float* origin, const float* dirs, con
                  int64_t n_rays, int32_t steps, float converge_tol, float* traj_scratch,
                  float* dorigin, float* ddirs, float* dpar, void* stream);
 
+/* rm_march_bwd for callers that may not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving
+ * loops, harnesses that forbid it).  Same inputs, outputs, launch geometry and results as rm_march_bwd, but the
+ * trajectory scratch is a file-scope device array inside the library (RM_MARCH_BWD_STATIC_MAX_FLOATS floats =
+ * 32 MiB, held by every GPU that loads the library until the process exits); the call performs no cudaMalloc /
+ * cudaFree and calls no allocating routine.  Limit: rm_bwd_scratch_floats(n_rays, steps) must not exceed
+ * RM_MARCH_BWD_STATIC_MAX_FLOATS (e.g. 87 296 rays at 32 steps, any ray count at <= 18 steps); beyond it the call
+ * returns RM_ERR_UNSUPPORTED with a message naming need and limit.  The first call on a device fetches the
+ * array's device address (cudaGetSymbolAddress, once per device): make that call -- n_rays = 0 suffices --
+ * outside graph capture.  All calls on one GPU share the array, which keeps the last call's contents (nothing
+ * in it needs to start at zero; dpar is cleared by the call): calls that OVERLAP on one GPU (other streams or
+ * host threads) race on it -- serialise them or use rm_march_bwd.  Exported by librm_b200.so only (not by the
+ * tape-specialised libraries). */
+#define RM_MARCH_BWD_STATIC_MAX_FLOATS 8388608
+int rm_march_bwd_static(const RmTape* tape, const float* origin, const float* dirs, const float* grad_pos,
+                        int64_t n_rays, int32_t steps, float converge_tol,
+                        float* dorigin, float* ddirs, float* dpar, void* stream);
+
 /* Upstream gradients of the G-buffer planes for rm_render_bwd, indexed like RmRenderOut (local ray
  * index); any pointer may be NULL (= zero gradient). */
 typedef struct RmRenderGrads {

@@ -17,6 +17,7 @@ LIB_PATH = os.environ.get("RM_B200_LIB") or os.path.join(_HERE, "csrc", "librm_b
 
 POSE_STRIDE = 8
 REDUCE_FLOATS = 8
+MARCH_BWD_STATIC_MAX_FLOATS = 8388608      # include/rm_b200.h: RM_MARCH_BWD_STATIC_MAX_FLOATS
 ABI_VERSION = 6
 
 
@@ -80,6 +81,8 @@ _SIGNATURES = {
     "rm_march_bwd": (C.c_int, [C.POINTER(RmTape), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                C.c_int32, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                C.c_void_p]),
+    "rm_march_bwd_static": (C.c_int, [C.POINTER(RmTape), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                      C.c_int32, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "rm_bwd_scratch_floats": (C.c_int64, [C.c_int64, C.c_int32]),
     "rm_render_bwd": (C.c_int, [C.POINTER(RmTape), C.POINTER(RmCamera), C.c_void_p,
                                 C.POINTER(RmRenderArgs), C.POINTER(RmRenderGrads), C.c_void_p,

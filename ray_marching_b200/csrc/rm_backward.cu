@@ -801,3 +801,72 @@ extern "C" int rm_render_loss_bwd(const RmTape* tape, const RmCamera* cam, const
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }
+
+#ifndef RM_SPEC_INC      // the general library only: a tape-specialised library would hold a second copy of the array
+// ---- rm_march_bwd_static: rm_march_bwd without any caller- or library-side allocation ---------------
+// No counterpart in the reference; added for callers that cannot
+// call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+// The trajectory scratch of the replay lives in a file-scope device array of a fixed, modest size
+// (RM_MARCH_BWD_STATIC_MAX_FLOATS floats = 32 MiB; every GPU that loads this library holds it until the
+// process exits).  In HOST code the array's name is only a stand-in for the symbol, not a device address:
+// the address is fetched once per device, with that device current, through cudaGetSymbolAddress, and that
+// pointer is what the kernel receives.  Every call on a device shares the array, which keeps the last
+// call's contents: nothing in it has to start at zero (the replay writes every slot before the reverse pass
+// reads it; the outputs dpar are cleared by a stream-ordered memset), but calls that OVERLAP on one GPU --
+// different streams, or different host threads -- race on it: serialise them, or use rm_march_bwd.
+#include <mutex>
+
+namespace rm {
+static __device__ __align__(256) float g_static_traj[RM_MARCH_BWD_STATIC_MAX_FLOATS];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+static float* g_static_traj_ptr[STATIC_MAX_DEVICES];     // device address of g_static_traj, per device
+static std::mutex g_static_traj_mutex;
+
+// Set-up, once per device: the device address of the static scratch on the CURRENT device.
+static int static_traj_pointer(float** out) {
+    int dev = -1;
+    RM_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= STATIC_MAX_DEVICES)
+        return fail(RM_ERR_UNSUPPORTED, "rm_march_bwd_static: device ordinal %d outside 0..%d", dev, STATIC_MAX_DEVICES - 1);
+    std::lock_guard<std::mutex> lock(g_static_traj_mutex);
+    if (g_static_traj_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_traj);
+        if (e != cudaSuccess || p == nullptr)
+            return fail(RM_ERR_CUDA, "rm_march_bwd_static: cudaGetSymbolAddress(g_static_traj) failed on device %d: %s",
+                        dev, cudaGetErrorString(e));
+        g_static_traj_ptr[dev] = static_cast<float*>(p);
+    }
+    *out = g_static_traj_ptr[dev];
+    return RM_OK;
+}
+}  // namespace rm
+
+extern "C" int rm_march_bwd_static(const RmTape* tape, const float* origin, const float* dirs,
+                                   const float* grad_pos, int64_t n, int32_t steps, float converge_tol,
+                                   float* dorigin, float* ddirs, float* dpar, void* stream) {
+    if (int s = check_backward_tape(tape)) return s;
+    if (n < 0 || steps < 0 || !(converge_tol >= 0.f) || (dpar == nullptr && tape->n_par > 0) ||
+        (n > 0 && (!origin || !dirs || !grad_pos)))
+        return fail(RM_ERR_INVALID, "rm_march_bwd_static: null buffer or negative count");
+    // same launch geometry as rm_march_bwd, so the scratch need is rm_bwd_scratch_floats(n, steps)
+    const int64_t need = n > 0 && steps > 0 ? (int64_t)steps * backward_grid(n) * BLOCK_B * KB * 3 : 0;
+    if (need > (int64_t)RM_MARCH_BWD_STATIC_MAX_FLOATS)
+        return fail(RM_ERR_UNSUPPORTED,
+                    "rm_march_bwd_static: %lld rays x %d steps need %lld floats of trajectory scratch, the static "
+                    "scratch holds %lld (RM_MARCH_BWD_STATIC_MAX_FLOATS); use rm_march_bwd with caller-provided scratch",
+                    (long long)n, (int)steps, (long long)need, (long long)RM_MARCH_BWD_STATIC_MAX_FLOATS);
+    float* traj = nullptr;
+    if (int s = static_traj_pointer(&traj)) return s;       // set-up on the first call per device; no allocation
+    if (tape->n_par > 0)
+        RM_CUDA(cudaMemsetAsync(dpar, 0, (size_t)tape->n_par * sizeof(float), (cudaStream_t)stream));
+    if (n == 0) return RM_OK;
+    const size_t sm = backward_smem(tape);
+    RM_BWD_LAUNCH(tape, march_bwd_kernel, backward_grid(n), sm, stream, tape->par, tape->n_instr, tape->n_par,
+                  backward_acc_shared(tape), backward_iters(n), origin, dirs, grad_pos, n, steps, converge_tol,
+                  traj, dorigin, ddirs, dpar);
+    RM_CUDA(cudaGetLastError());
+    return RM_OK;
+}
+#endif  // RM_SPEC_INC
