@@ -182,12 +182,30 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
 #else
     const unsigned threads = render_threads(a->n_rays, sm);
 #endif
-    const unsigned grid = render_grid(a->n_rays, threads);
+    unsigned grid = render_grid(a->n_rays, threads);
     {
         const int64_t tiles = (a->n_rays + 32 * K - 1) / (32 * K);
         if (tiles > 0x7fffffff) return fail(RM_ERR_INVALID, "rm_render: ray range too large for one launch");
         P.tile_base = (int)(tiles / grid); P.tile_rem = (int)(tiles % grid);     // persistent tiling only
     }
+    // Culled kernel: 2-D warp tiles (render_kernel) when the range is whole rows of a width that 64-pixel patch
+    // columns divide; any other shape keeps the linear tiles.
+    P.patch_cols = 0; P.patch_rows = 0;
+#if !RM_PERSIST && !defined(RM_SPEC_INC)
+    {
+        const int64_t Wd = P.cam.width;
+        if (a->fast_math >= 2 && K == 4 && Wd % 64 == 0 && a->ray_begin % Wd == 0 && a->n_rays % Wd == 0 &&
+            (a->strip_rays == 0 || a->strip_rays % Wd == 0)) {
+            const int64_t rows = a->n_rays / Wd;
+            const int64_t tiles = (Wd / 64) * ((rows + 15) / 16) * 8;
+            if (tiles * 32 * K <= 0x7fffffff && rows <= 0x7fffffff) {
+                P.patch_cols = (int)(Wd / 64);
+                P.patch_rows = (int)rows;
+                grid = (unsigned)((tiles + threads / 32 - 1) / (threads / 32));
+            }
+        }
+    }
+#endif
     // Approximate-math stencil samples (stencil_eval<.., SFAST>): only when no output of this frame needs correctly
     // rounded samples -- no Laplacian, no reported f(p) (sdf plane, proximity shader), no G-buffer plane.
     const bool any_gbuffer = out->origin || out->dirs || out->pos || out->sdf || out->normals || out->laplacian;

@@ -31,14 +31,30 @@ __device__ __forceinline__ float prim_eval(int op, const float4* P, float x, flo
 // Decode per instruction: one 16-byte constant load (prefetched one instruction ahead), one add
 // for the record address, a switch on the dispatch id, a switch on the tail selector.
 //
-// CULL (march steps only): the children of one designated smooth union carry a
-// bounding sphere (world centre c, radius R with f_i(p) >= s_min (|p - c| - R) outside it).  A child
-// is skipped when, for every ray of the warp, its term is below 2^-30 of a LOWER bound of the
-// union's largest term: thr = max(running max, c_k (h + L m) - log2 n), where h is the union's value
-// at the previous march position, m the distance moved since and L the Lipschitz bound of the scene
-// (max term >= logsumexp - log n, and f_U(p') <= f_U(p) + L |p' - p|).  `hint` carries h in and
-// the union's value at this point out; `move` is m (+inf disables the seed).
-constexpr float CULL_LOG2 = -30.0f;
+// CULL: the children of one designated smooth union carry a bounding sphere (world
+// centre c_i, radius R_i with f_i(p) >= s_min (|p - c_i| - R_i) outside it).  A child is skipped when, for
+// EVERY ray of the warp, its term x_i = c_k f_i (base-2 scaled, c_k < 0) lies 30 below a LOWER bound of the
+// union's largest term.  That bound comes from the previous evaluation: `hint` carries the running maximum
+// a0 = max_i x_i of the culled union at the previous point in, and at this point out; every term is
+// Lipschitz, |x_i(p') - x_i(p)| <= |c_k| L |p' - p|, so max_i x_i(p') >= hint + c_k L m with m = `move`, the
+// distance moved since (hint = -inf: no information, nothing is skipped).
+// The test is WARP-PARALLEL: the 32 lanes test 32 consecutive instructions at once, each against the warp's
+// bounding sphere (centre = one lane's point, radius R_w = the farthest ray of the warp from it):
+// |p - c_i| >= |c_w - c_i| - R_w for every ray, so one ballot yields a skip mask for 32 children and the
+// interpreter jumps over masked runs.  A skipped child costs 1/32 of a dozen instructions instead of half a
+// leaf, which is what makes culling pay on 512-primitive scenes (profiles/r02/variants.md).
+// Cut-off: a skipped term is below 2^-24 = 6e-8 of the largest one (SURVEY 8(f)-1 proposes 1e-7): the sum of n
+// children changes by at most n 2^-24 relative (512 children: 3e-5, i.e. 4.4e-5 in the base-2 logarithm, i.e.
+// 1.4e-6 distance units at k = 22 -- seventy times inside the 1e-4 relative depth tolerance at depth 4).
+constexpr float CULL_LOG2 = -24.0f;
+#ifdef RM_CULL_STATS
+// counters for tools/cull_stats.py (a -DRM_CULL_STATS build only): [0] evals, [1] evals with a usable bound, [2] whole-union skips, [3] leaves evaluated inside the
+// culled union, [4] leaves skipped by the mask (per warp)
+__device__ unsigned long long g_cull_stats[8];
+#define RM_STAT(i, n) do { if ((threadIdx.x & 31) == 0) atomicAdd(&g_cull_stats[i], (unsigned long long)(n)); } while (0)
+#else
+#define RM_STAT(i, n) do { } while (0)
+#endif
 
 // RECORD (backward kernels): per union node, its raw value (before post-ops) and -- hard unions --
 // the winning child ordinal (first index on ties, as torch.min(dim)), kept in local memory and
@@ -82,6 +98,23 @@ __device__ __forceinline__ int4 tape_ins(const TapeCode<CAP>& C, int pc) { retur
 
 // CULLMODE: 0 = the code carries no culling flags; 1 = flags present (a culling launch) but this
 // instance evaluates every child (IEEE stencil samples); 2 = cull.
+//
+// Culling (one smooth union per tape, tape.py: the largest one).  A child whose term 2^(c f_i) is below
+// 2^CULL_LOG2 of the union's largest term cannot change a float32 logsumexp by more than 2^CULL_LOG2 relative,
+// and is skipped.  Everything is decided per WARP, so that the instruction stream stays warp-uniform:
+//   * at OPEN the warp bounds its 32 K points by a sphere (centre c_w, radius r_w) and the union's largest term
+//     from below by seed_min = max(carried bound, geometric bound): `hint` is the largest term at the previous
+//     evaluation of each ray and decays by c L |move| (every child is L-Lipschitz); the geometric bound needs
+//     no history -- some child's surface lies inside its sphere, so its value is <= L (|c_w - c_j| + R_j + r_w);
+//   * the union's sphere table (one float4 per body instruction, shared memory) is tested 32 instructions at a
+//     time, one per lane: child j is at least t_j = |c_w - c_j| - R_j - r_w outside its sphere, its term is
+//     <= c s_min t_j, and it is masked when that is 2^CULL_LOG2 below seed_min.  The mask is OR-reduced into
+//     a uniform register and the interpreter jumps over runs of masked instructions;
+//   * when the union is a plain child of a hard union, the same table gives f_U >= (c s_min t_min + log2 n)/c;
+//     if that exceeds the parent's running minimum for every ray of the warp, the whole union is skipped --
+//     exactly (min(parent, f_U) = parent).
+// render_kernel gives a culling warp a 16 x 8 pixel patch instead of 128 pixels of one row: r_w is what
+// decides how many children survive.
 template <int K, bool FAST, int CAP, int CULLMODE = 0, bool RECORD = false>
 __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_instr,
                                            const float4* __restrict__ spar, const float (&px)[K],
@@ -97,12 +130,14 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
 #endif
     using M = Math<FAST>;
     constexpr bool CULL = CULLMODE == 2;
-    float seed[CULL ? K : 1];                        // lower bound of the culled union's largest term
-    float cs = 0.f;                                  // c * s_min of the culled union (<= 0)
-    if (CULL) {
-#pragma unroll
-        for (int k = 0; k < (CULL ? K : 1); ++k) seed[k] = -CUDART_INF_F;
-    }
+    // culling state, all warp-uniform: skip mask of the 32 instructions from mask_base on
+    unsigned skip_mask = 0u;
+    int mask_base = -0x40000000;
+    bool cull_on = false;                            // inside the culled union, with a usable bound
+    float cs = 0.f, seed_min = 0.f;                  // c * s_min of the culled union (<= 0); min over the warp of the seed
+    float cwx = 0.f, cwy = 0.f, cwz = 0.f, rw = 0.f; // the warp's bounding sphere
+    const float4* tbl = spar;                        // sphere table of the culled union, for pcs [tbl_pc0, tbl_pc1)
+    int tbl_pc0 = 0, tbl_pc1 = 0;
     float a0[K], a1[K], d[K];
     float c = 0.f;                                   // scale of the innermost open smooth union
     float stk[MAX_DEPTH * (2 * K + 1)];              // spilled accumulators of enclosing unions
@@ -122,24 +157,40 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
     int4 nxt = tape_ins(C, pc0);
     RM_TAPE_LOOP
     for (int pc = pc0; pc < pc1; ++pc) {
+        if (CULL && cull_on) {
+            int off = pc - mask_base;
+            if (off >= 32) {
+                // lane L tests instruction pc + L against the union's sphere table (one float4 per instruction of
+                // the body, consecutive in shared memory; radius = 3e38 for an instruction without a sphere)
+                const int q = pc + (int)(threadIdx.x & 31);
+                bool sk = false;
+                if (q < tbl_pc1) {
+                    const float4 cr = tbl[q - tbl_pc0];
+                    const float dx = cwx - cr.x, dy = cwy - cr.y, dz = cwz - cr.z;
+                    const float t = M::sqrt(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) - cr.w - rw;
+                    sk = t > 0.f && (cs * t - seed_min < CULL_LOG2);                      // false for NaN
+                }
+                // REDUX (not VOTE): the result lands in a uniform register, so pc and every branch of the
+                // interpreter stay on the uniform datapath
+                skip_mask = __reduce_or_sync(0xffffffffu, sk ? (1u << (threadIdx.x & 31)) : 0u);
+                mask_base = pc;
+                off = 0;
+            }
+            const unsigned m = skip_mask >> off;
+            if (m & 1u) {                                              // jump over the whole masked run
+                const int run = (~m) != 0u ? __ffs((int)~m) - 1 : 32;  // consecutive masked instructions from pc
+                RM_STAT(4, run);
+                pc += run - 1;                                         // (the loop adds the last one)
+                nxt = tape_ins(C, pc + 1);
+                continue;
+            }
+        }
+        if (CULL && pc >= tbl_pc0 && pc < tbl_pc1) RM_STAT(3, 1);
         const int4 ins = nxt;
         nxt = tape_ins(C, pc + 1);                    // prefetch (pad entry after the last instruction)
         const float4* P = reinterpret_cast<const float4*>(sbytes + ins.z);
         const int disp_raw = ins_disp(ins.w);
         const int disp = CULLMODE ? (disp_raw & ~DISP_CULL) : disp_raw;  // flags are only set for culling launches
-        if (CULL) {
-            if ((disp_raw & DISP_CULL) && disp < DISP_OPEN_MIN) {
-                const float4 cr = P[-1];             // bounding sphere of this leaf
-                bool skip = true;
-#pragma unroll
-                for (int k = 0; k < K; ++k) {
-                    const float dx = px[k] - cr.x, dy = py[k] - cr.y, dz = pz[k] - cr.z;
-                    const float t = M::sqrt(fmaf(dx, dx, fmaf(dy, dy, dz * dz))) - cr.w;
-                    skip = skip && t > 0.f && (cs * t - fmaxf(a0[k], seed[k]) < CULL_LOG2);
-                }
-                if (__all_sync(0xffffffffu, skip)) continue;
-            }
-        }
 
 #define RM_LEAF_FRAME(EXPR)                                                                     \
     {                                                                                           \
@@ -181,6 +232,12 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
             case OP_PLANE | DISP_FRAME: RM_LEAF_FRAME(x)
             case DISP_OPEN_MIN:
             case DISP_OPEN_SMOOTH: {
+                float s_parent[CULL ? K : 1], s_parent1[CULL ? K : 1];      // the parent's accumulators (culling)
+                const float c_parent = c;
+                if (CULL) {
+#pragma unroll
+                    for (int k = 0; k < (CULL ? K : 1); ++k) { s_parent[k] = a0[k]; s_parent1[k] = a1[k]; }
+                }
                 if (!(ins.x & HEAD_ROOT)) {
                     float* s = stk + sp * (2 * K + 1);
 #pragma unroll
@@ -199,9 +256,92 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
                     for (int k = 0; k < K; ++k) { a0[k] = -CUDART_INF_F; a1[k] = 0.f; }
                     if (CULL && (disp_raw & DISP_CULL) && u.w > 0.f) {
                         cs = c * u.y;
+                        // lower bound of this union's largest term at these points, minimum over the warp
+                        float sm = CUDART_INF_F;
 #pragma unroll
-                        for (int k = 0; k < (CULL ? K : 1); ++k)
-                            seed[k] = fmaf(c, fmaf(u.z, move[k], hint[k]), -u.w);
+                        for (int k = 0; k < (CULL ? K : 1); ++k) sm = fminf(sm, fmaf(c * u.z, move[k], hint[k]));
+                        // the warp's bounding sphere: centre = lane 16's first point
+                        cwx = __shfl_sync(0xffffffffu, px[0], 16);
+                        cwy = __shfl_sync(0xffffffffu, py[0], 16);
+                        cwz = __shfl_sync(0xffffffffu, pz[0], 16);
+                        float r2 = 0.f;
+#pragma unroll
+                        for (int k = 0; k < K; ++k) {
+                            const float dx = px[k] - cwx, dy = py[k] - cwy, dz = pz[k] - cwz;
+                            const float q2 = fmaf(dx, dx, fmaf(dy, dy, dz * dz));
+                            r2 = q2 > r2 ? q2 : (q2 == q2 ? r2 : CUDART_INF_F);      // NaN point: no culling
+                        }
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) {
+                            sm = fminf(sm, __shfl_xor_sync(0xffffffffu, sm, o));
+                            r2 = fmaxf(r2, __shfl_xor_sync(0xffffffffu, r2, o));
+                        }
+                        rw = sqrt_rn_inline(r2) * 1.0001f;
+                        RM_STAT(0, 1);
+                        const int close_pc = ins_post_off(ins.w) & 0xFFFF;        // pc of this union's CLOSE
+                        const bool plain_min_child = (ins.w & (1 << 16)) != 0;     // ... of a hard union, no post-op
+                        tbl = spar + head_ordinal(ins.x);                          // (ordinal field of OPEN = table offset)
+                        tbl_pc0 = pc + 1;
+                        tbl_pc1 = close_pc;
+                        // One lane-parallel pass over the sphere table: t_min = the least distance from the warp's
+                        // sphere to a child's sphere (every child's value >= smin t_i), u_min = the least distance
+                        // to the FAR side of a child's sphere (that child's value <= L (u_i + rw): its surface has a
+                        // point inside its sphere and its value is L-Lipschitz).
+                        float tmin = CUDART_INF_F, umin = CUDART_INF_F;
+                        for (int base = pc + 1; base < close_pc; base += 32) {
+                            const int q = base + (int)(threadIdx.x & 31);
+                            if (q < close_pc) {
+                                const float4 cr = tbl[q - tbl_pc0];
+                                const float dx = cwx - cr.x, dy = cwy - cr.y, dz = cwz - cr.z;
+                                const float dist = M::sqrt(fmaf(dx, dx, fmaf(dy, dy, dz * dz)));
+                                const float t = dist - cr.w - rw;
+                                tmin = t < tmin ? t : (t == t ? tmin : -CUDART_INF_F);   // no sphere: t = -3e38
+                                umin = fminf(umin, dist + fabsf(cr.w));                  // no sphere: 3e38, ignored
+                            }
+                        }
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) {
+                            tmin = fminf(tmin, __shfl_xor_sync(0xffffffffu, tmin, o));
+                            umin = fminf(umin, __shfl_xor_sync(0xffffffffu, umin, o));
+                        }
+                        // the largest term is >= c L (u_min + rw) (c < 0) whatever the history; a bound carried from
+                        // the previous evaluation is usually tighter.  Moved down 1e-5 relative for rounding.
+                        const float geo0 = (c * u.z) * (umin + rw);
+                        const float geo = geo0 - 1e-5f * fabsf(geo0);
+                        if (!(sm >= geo)) sm = geo;                            // (sm NaN: take geo)
+                        seed_min = sm;
+                        // Skip the WHOLE union when it cannot win its parent's min: every child is outside its
+                        // sphere by t_i >= t_min > 0, so every term <= cs t_min, logsumexp <= cs t_min + log2 n
+                        // and f_U >= (cs t_min + log2 n) / c.  If that exceeds the parent's running minimum
+                        // (still in a0 here) for every ray of the warp, min(parent, f_U) = parent: exact.
+                        if (plain_min_child) {                          // warp-uniform (rw = inf makes lb = -inf below)
+                            // lower bound of the union's value (u.w = log2 n), moved DOWN by 1e-6 relative for rounding
+                            const float lb0 = M::div(fmaf(cs, tmin, u.w), c);
+                            const float lb = tmin > 0.f ? lb0 - 1e-6f * fabsf(lb0) : -CUDART_INF_F;
+                            bool lose = true;
+#pragma unroll
+                            for (int k = 0; k < K; ++k) lose = lose && lb > s_parent[k];
+                            if (__reduce_and_sync(0xffffffffu, lose ? 1u : 0u) != 0u) {
+                                // leave the parent's accumulators as they are and continue after the CLOSE
+#pragma unroll
+                                for (int k = 0; k < K; ++k) { a0[k] = s_parent[k]; a1[k] = s_parent1[k]; }
+                                const float c_union = c;
+                                c = c_parent;
+                                // nothing was evaluated here: the bound survives, decayed by the distance moved
+                                // (every term is Lipschitz), so the next evaluation can still cull
+#pragma unroll
+                                for (int k = 0; k < (CULL ? K : 1); ++k) hint[k] = fmaf(c_union * u.z, move[k], hint[k]);
+                                if (!(ins.x & HEAD_ROOT)) --sp;
+                                cull_on = false;
+                                RM_STAT(2, 1);
+                                pc = close_pc;
+                                nxt = tape_ins(C, pc + 1);
+                                continue;
+                            }
+                        }
+                        cull_on = __reduce_and_sync(0xffffffffu, (sm > -CUDART_INF_F && rw < CUDART_INF_F) ? 1u : 0u) != 0u;
+                        mask_base = -0x40000000;                               // first child: compute a mask
+                        if (cull_on) RM_STAT(1, 1);
                     }
                 }
                 continue;
@@ -218,8 +358,8 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
                     for (int k = 0; k < K; ++k) d[k] = M::div(a0[k] + M::log(a1[k]), c);
                     if (CULL && (disp_raw & DISP_CULL)) {
 #pragma unroll
-                        for (int k = 0; k < (CULL ? K : 1); ++k) hint[k] = d[k];
-                        cs = 0.f;
+                        for (int k = 0; k < (CULL ? K : 1); ++k) hint[k] = a0[k];    // largest term at this point
+                        cull_on = false;
                     }
                 }
                 if (RECORD) {

@@ -206,22 +206,29 @@ __global__ void camera_update_kernel(float* __restrict__ poses, const float* __r
 }
 
 // ---- the march loop (ray_marching.py:78-84): p <- f(p) v + p --------------------------------
-// CULL: see eval_scene.  The union value of the previous step and the step length bound the union
-// value at the new position (the ray moved |f(p)| |v|).
+// CULL: see eval_scene.  `hint` (largest term of the culled union at the last evaluated point; -inf = none)
+// and `move` (distance from that point to the current one) are the caller's: a following stencil can go on
+// culling from where the march stopped.  The ray moves |f(p)| |v| per step.
+template <int N>
+struct CullState {
+    float hint[N], move[N];
+    __device__ __forceinline__ void reset() {
+#pragma unroll
+        for (int k = 0; k < N; ++k) { hint[k] = -CUDART_INF_F; move[k] = 0.f; }
+    }
+};
+
 template <bool FAST, int CAP, bool CULL>
 __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                            int steps, bool early_exit,
                                            float (&px)[K], float (&py)[K], float (&pz)[K],
                                            const float (&vx)[K], const float (&vy)[K],
-                                           const float (&vz)[K]) {
+                                           const float (&vz)[K], CullState<CULL ? K : 1>& cs) {
     float d[K];
-    float hint[CULL ? K : 1], move[CULL ? K : 1], vlen[CULL ? K : 1];
+    float vlen[CULL ? K : 1];
 #pragma unroll
-    for (int k = 0; k < (CULL ? K : 1); ++k) {
-        hint[k] = CUDART_INF_F; move[k] = 0.f;
-        // the ray moves |f(p)| |v| per step: rm_march accepts directions of any length
+    for (int k = 0; k < (CULL ? K : 1); ++k)
         vlen[k] = CULL ? sqrt_rn_inline(fmaf(vx[k], vx[k], fmaf(vy[k], vy[k], vz[k] * vz[k]))) * 1.0001f : 0.f;
-    }
 #ifdef RM_SPEC_INC
     // Tape-specialised build: the evaluation is a few dozen straight-line instructions, so the
     // fixed-point test below (12 compares, the old/new register rotation, a vote) would be ~15 % of
@@ -246,7 +253,7 @@ __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_inst
         // instruction-cache lines (block-uniform trip count: legal whenever early_exit is off)
         if (!early_exit) __syncthreads();
 #endif
-        eval_scene<K, FAST, CAP, CULL ? 2 : 0>(code, n_instr, spar, px, py, pz, d, hint, move);
+        eval_scene<K, FAST, CAP, CULL ? 2 : 0>(code, n_instr, spar, px, py, pz, d, cs.hint, cs.move);
         bool moved = false;
 #pragma unroll
         for (int k = 0; k < K; ++k) {
@@ -255,7 +262,7 @@ __device__ __forceinline__ void march_rays(const TapeCode<CAP>& code, int n_inst
             const float nz = fmaf(d[k], vz[k], pz[k]);
             if (early_exit) moved |= (nx != px[k]) | (ny != py[k]) | (nz != pz[k]);
             px[k] = nx; py[k] = ny; pz[k] = nz;
-            if (CULL) move[CULL ? k : 0] = fabsf(d[k]) * vlen[CULL ? k : 0];
+            if (CULL) cs.move[CULL ? k : 0] = fabsf(d[k]) * vlen[CULL ? k : 0];
         }
         // A ray whose position did not change is at a fixed point of the update: all further
         // steps reproduce it bit for bit, so leaving the loop (when the whole warp is there) does
@@ -277,7 +284,9 @@ march_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n
     float px[K], py[K], pz[K], vx[K], vy[K], vz[K];
     load3(origin, first, n, px, py, pz);
     load3(dirs, first, n, vx, vy, vz);
-    march_rays<FAST, CAP, CULL>(code, n_instr, spar, steps, false, px, py, pz, vx, vy, vz);
+    CullState<CULL ? K : 1> cull;
+    cull.reset();
+    march_rays<FAST, CAP, CULL>(code, n_instr, spar, steps, false, px, py, pz, vx, vy, vz, cull);
     store3(out, first, n, px, py, pz);
 }
 
@@ -292,13 +301,21 @@ march_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n
 // (Folding the samples into the march loop, so that ONE interpreter instance serves both, was measured
 // slower: the stencil accumulators stay live across the march and spill at 64 registers --
 // profiles/r02/variants.md.)
+// With SFAST and a culling launch the samples are culled too, with the same rigorous bound as the steps:
+// `cull` arrives from the march (last evaluated point p_{S-1}, move = |p_S - p_{S-1}|); the first sample is at
+// most eps further, consecutive samples at most 2 eps apart.  The rounded samples (SFAST off) evaluate
+// every child.
 template <int CAP, bool CULLFLAGS = false, bool SFAST = false>
 __device__ __forceinline__ void stencil_eval(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                              const Stencil& st, bool need_offsets,
                                              const float (&px)[K], const float (&py)[K],
                                              const float (&pz)[K], float (&f)[K],
                                              float (&nx)[K], float (&ny)[K], float (&nz)[K],
-                                             float (&lap)[K]) {
+                                             float (&lap)[K],
+                                             CullState<(CULLFLAGS && SFAST) ? K : 1>* cull = nullptr) {
+    constexpr bool SCULL = CULLFLAGS && SFAST;
+    const float eps1 = SCULL ? 1.0001f * sqrt_rn_inline(st.off[0][0] * st.off[0][0] + st.off[0][1] * st.off[0][1] +
+                                                        st.off[0][2] * st.off[0][2]) : 0.f;
     float o0[K], sum[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) { o0[k] = sum[k] = nx[k] = ny[k] = nz[k] = f[k] = 0.f; }
@@ -307,7 +324,13 @@ __device__ __forceinline__ void stencil_eval(const TapeCode<CAP>& code, int n_in
         const float dx = st.off[j][0], dy = st.off[j][1], dz = st.off[j][2];
 #pragma unroll
         for (int k = 0; k < K; ++k) { x[k] = px[k] + dx; y[k] = py[k] + dy; z[k] = pz[k] + dz; }
-        eval_scene<K, SFAST, CAP, CULLFLAGS ? 1 : 0>(code, n_instr, spar, x, y, z, d);
+        if constexpr (SCULL) {
+#pragma unroll
+            for (int k = 0; k < K; ++k) cull->move[k] = (j == (need_offsets ? 0 : 4) ? cull->move[k] + eps1 : 2.f * eps1);
+            eval_scene<K, true, CAP, 2>(code, n_instr, spar, x, y, z, d, cull->hint, cull->move);
+        } else {
+            eval_scene<K, SFAST, CAP, CULLFLAGS ? 1 : 0>(code, n_instr, spar, x, y, z, d);
+        }
         const float wx = st.w[j][0], wy = st.w[j][1], wz = st.w[j][2];
         const float first = st.first[j], in_sum = st.in_sum[j];
 #pragma unroll
@@ -352,3 +375,12 @@ normals_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int
 
 #include "rm_render.cuh"
 #include "rm_abi_forward.cuh"
+
+#ifdef RM_CULL_STATS
+extern "C" int rm_debug_cull_stats(unsigned long long* out8, int reset) {
+    cudaDeviceSynchronize();
+    if (out8) cudaMemcpyFromSymbol(out8, rm::g_cull_stats, sizeof(unsigned long long) * 8);
+    if (reset) { unsigned long long z[8] = {0}; cudaMemcpyToSymbol(rm::g_cull_stats, z, sizeof(z)); }
+    return 0;
+}
+#endif

@@ -15,6 +15,7 @@ struct RenderParams {
     unsigned mode_mask;
     int display_mode, degree, early_exit;
     int tile_base, tile_rem;           // persistent tiling: see render_kernel
+    int patch_cols, patch_rows;        // culled kernel: 64-pixel columns of 2-D patches (0 = linear tiles), image rows
     const float* cmap;
     RmRenderOut out;
 };
@@ -111,8 +112,21 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
         const int t = (int)blockIdx.x * WARPS + (int)(threadIdx.x >> 5);
         (void)warp; (void)t0; (void)t1; (void)rot;
 #endif
-        const int64_t first = ((int64_t)t * 32 + lane) * K;
-        const int64_t ray0 = shard_ray(P.ray_begin, P.strip_rays, P.strip_stride, first);   // global index
+        int64_t first = ((int64_t)t * 32 + lane) * K;
+        int64_t first_ray = first;                     // the local index the marched rays are made from
+        if (CULL && P.patch_cols > 0) {
+            // 2-D tiles for the culled kernel: a warp owns a 16 x 8 pixel patch (lane = 4 pixels of one row) and
+            // eight consecutive tiles make a 64 x 16 patch, so that the warp's bounding sphere is ~8x smaller
+            // than that of 128 pixels in a row and the warps of a block see similar scenery (a block's slot is
+            // held until its slowest warp ends).  Rows past the end march the last row again and store nothing.
+            const unsigned s8 = (unsigned)t >> 3, w8 = (unsigned)t & 7u;
+            const unsigned sy = s8 / (unsigned)P.patch_cols, sx = s8 - sy * (unsigned)P.patch_cols;
+            const int row = (int)(sy * 2u + (w8 >> 2)) * 8 + (lane >> 2);
+            const int col = (int)((sx * 4u + (w8 & 3u)) * 16u) + (lane & 3) * K;
+            first_ray = (int64_t)min(row, P.patch_rows - 1) * P.cam.width + col;
+            first = row < P.patch_rows ? first_ray : n;
+        }
+        const int64_t ray0 = shard_ray(P.ray_begin, P.strip_rays, P.strip_stride, first_ray);   // global index
         float ox[K], oy[K], oz[K], vx[K], vy[K], vz[K];
         float px[K], py[K], pz[K], f[K], nx[K], ny[K], nz[K], lap[K];
         make_rays(P.cam, poses, ray0, ox, oy, oz, vx, vy, vz);
@@ -121,8 +135,13 @@ render_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int 
         for (int k = 0; k < K; ++k) { px[k] = ox[k]; py[k] = oy[k]; pz[k] = oz[k]; }
 
         for (int b = 0;; ++b) {
-            march_rays<FAST, CAP, CULL>(code, n_instr, spar, P.steps, P.early_exit != 0, px, py, pz, vx, vy, vz);
-            stencil_eval<CAP, CULL, SFAST>(code, n_instr, spar, P.st, need_stencil, px, py, pz, f, nx, ny, nz, lap);
+            CullState<CULL ? K : 1> cull;              // a reflected segment starts without a bound
+            cull.reset();
+            march_rays<FAST, CAP, CULL>(code, n_instr, spar, P.steps, P.early_exit != 0, px, py, pz, vx, vy, vz, cull);
+            if constexpr (CULL && SFAST)
+                stencil_eval<CAP, CULL, SFAST>(code, n_instr, spar, P.st, need_stencil, px, py, pz, f, nx, ny, nz, lap, &cull);
+            else
+                stencil_eval<CAP, CULL, SFAST>(code, n_instr, spar, P.st, need_stencil, px, py, pz, f, nx, ny, nz, lap);
             if (b >= P.bounces) break;
             // reflected-ray branch (reflect = control.py:179-194)
 #pragma unroll

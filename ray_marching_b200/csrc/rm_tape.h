@@ -91,9 +91,29 @@ __host__ __device__ __forceinline__ int4 expand_one(int head, int w1, bool with_
 }
 
 // Host: [n][2] words -> expanded instructions.
+// Culling launches: the OPEN of the culled smooth union additionally carries, in the (otherwise unused)
+// post-op offset field of its w word, the pc of its CLOSE [0:16] and a flag [16] saying that the union is a
+// plain child of a HARD union (its CLOSE folds with min, no post-op, not the root): then the whole union may be
+// skipped, exactly, whenever a lower bound of its value exceeds the parent's running minimum (rm_eval.cuh).
+// (The ordinal field of that OPEN holds the float4 offset of the union's sphere table: tape.py.)
 inline void expand_instructions(const int32_t* words, int n, int4* out, bool with_cull) {
     for (int i = 0; i < n; ++i) out[i] = expand_one(words[2 * i], words[2 * i + 1], with_cull);
     out[n] = make_int4(0, 0, 0, 0);
+    if (!with_cull) return;
+    int open_at[MAX_DEPTH + 1], sp = 0;
+    for (int i = 0; i < n; ++i) {
+        const int op = head_op(out[i].x);
+        if (op == OP_OPEN_MIN || op == OP_OPEN_SMOOTH) { if (sp <= MAX_DEPTH) open_at[sp] = i; ++sp; }
+        else if (op == OP_CLOSE_MIN || op == OP_CLOSE_SMOOTH) {
+            --sp;
+            if (sp < 0 || sp > MAX_DEPTH) continue;
+            const int o = open_at[sp];
+            if (op != OP_CLOSE_SMOOTH || !word_cull(out[i].y)) continue;
+            const bool plain_min_child = !(out[i].x & HEAD_ROOT) && head_fold(out[i].x) == FOLD_MIN &&
+                                         head_npost(out[i].x) == 0;
+            out[o].w |= (i & 0xFFFF) | (plain_min_child ? (1 << 16) : 0);
+        }
+    }
 }
 template <int CAP>
 inline void expand_code(const int32_t* words, int n, TapeCode<CAP>& code, bool with_cull = false) {

@@ -55,7 +55,7 @@ MAX_DEPTH = 8           # union nesting depth supported by the interpreter's spi
 MAX_INSTR = 1024        # largest kernel-parameter code block (csrc/rm_tape.h)
 MAX_ORDINAL = 0xFFFF    # children per union
 MAX_PAR_F4 = 0xFFFF     # parameter records addressable by an instruction (float4 units)
-WORD1_CULL = 1 << 31    # leaf: a bounding-sphere record precedes its first record; OPEN/CLOSE: the culled union
+WORD1_CULL = 1 << 31    # leaf: it has an entry with a finite radius in the culled union's sphere table; OPEN/CLOSE: that union
 CULL_MIN_CHILDREN = 8   # smooth unions smaller than this are not worth bounding-sphere tests
 
 _PRIM_OP = {"SDFSphere": OP_SPHERE, "SDFBox": OP_BOX, "SDFPlane": OP_PLANE,
@@ -129,6 +129,7 @@ class Tape:
         big = max(smooth, key=lambda m: len(m.sdfs), default=None)
         self._cull_union = big if big is not None and len(big.sdfs) >= CULL_MIN_CHILDREN else None
         self._cull_leaves: List[dict] = []
+        self._cull_table = 0
         self._in_cull = False
 
         self._ord = [0]                     # next child ordinal of every open union (root: dummy)
@@ -222,6 +223,7 @@ class Tape:
             root = HEAD_ROOT if depth == 0 else 0      # nothing to save / restore around the root union
             culled = node is self._cull_union
             flag = WORD1_CULL if culled else 0
+            open_index = len(self._code)
             if smooth:
                 # (-k, s_min, L_max, log2 n): the last three are 0 unless this is the culled union
                 off4 = self._f4([("neg_theta", self._slot(node.blend_k))] +
@@ -236,6 +238,19 @@ class Tape:
                 self._emit(child, frame, child_fold, [], depth + 1)
             self._in_cull = False
             self._ord.pop()
+            if culled:
+                # Sphere table of the culled union: one float4 (world centre, radius / s_min) per instruction of
+                # its body, in instruction order, contiguous -- lane L of a warp reads entry L of a chunk
+                # (csrc/rm_eval.cuh).  Instructions without a bounding sphere (planes, nested unions and their
+                # leaves) get an infinite radius: never skipped, and they void the whole-union bound.
+                sphere_of = {c["code_index"]: ci for ci, c in enumerate(self._cull_leaves)}
+                self._cull_table = len(self._src) // 4
+                for j in range(open_index + 1, len(self._code)):
+                    ci = sphere_of.get(j)
+                    self._f4([("cull", ci * 4 + i) for i in range(4)] if ci is not None
+                             else [_Src.ZERO, _Src.ZERO, _Src.ZERO, ("big", 0)])
+            if culled:
+                self._code[open_index][2] = self._cull_table     # ordinal field of the OPEN = table offset (float4)
             kinds, entries = self._post_record(posts)
             off4 = self._f4(entries) if kinds else 0
             op = OP_CLOSE_SMOOTH if smooth else OP_CLOSE_MIN
@@ -251,9 +266,9 @@ class Tape:
         self._in_cull = False
         if cull:
             ci = len(self._cull_leaves)
-            self._f4([("cull", ci * 4 + i) for i in range(4)])    # world centre, radius / s_min
             pz = self.n_theta                                      # index of the padding zero
-            info = dict(frame=frame, add=[pz] * 4, box=[pz] * 3, ls=[pz] * 3, le=[pz] * 3)
+            info = dict(frame=frame, add=[pz] * 4, box=[pz] * 3, ls=[pz] * 3, le=[pz] * 3,
+                        code_index=len(self._code))                # the instruction this sphere bounds
             adds = [self._slot(p) for _, p in posts]
             if op in (OP_SPHERE, OP_DISK):
                 adds.append(self._slot(node.radius))
@@ -300,7 +315,8 @@ class Tape:
         base = {"zero": 0, "theta": 1, "neg_theta": 1 + P, "AB": 1 + 2 * P,
                 "ABn": 1 + 2 * P + 3 * nL, "A": 1 + 2 * P + 6 * nL,
                 "b": 1 + 2 * P + 6 * nL + 9 * nA, "cull": 1 + 2 * P + 6 * nL + 12 * nA,
-                "cullu": 1 + 2 * P + 6 * nL + 12 * nA + 4 * nC}
+                "cullu": 1 + 2 * P + 6 * nL + 12 * nA + 4 * nC,
+                "big": 1 + 2 * P + 6 * nL + 12 * nA + 4 * nC + (3 if self._cull_union is not None else 0)}
         i64 = lambda rows: torch.tensor(rows, dtype=torch.int64).reshape(len(rows), -1)
         self._cull_idx = None
         if nC:
@@ -379,6 +395,7 @@ class Tape:
         if self._cull_union is not None:
             pieces += self._cull_pieces(theta, d, A if len(self._affines) else None,
                                         b if len(self._affines) else None)
+            pieces += [theta.new_full((1,), 3.0e38)]          # "big": the radius of an instruction without a sphere
         return torch.cat(pieces)[d["perm"]]
 
     def _cull_pieces(self, theta, d, A, b):

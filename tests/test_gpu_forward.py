@@ -309,6 +309,37 @@ def test_culling_matches_full_evaluation(n_prims):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("W,H,n", [(128, 40, 1), (64, 24, 2), (192, 16, 1)])
+def test_culled_patch_tiles_put_every_pixel_in_place(W, H, n):
+    """The culled kernel walks 16 x 8-pixel warp patches when the width is a multiple of 64 (render_kernel):
+    every pixel is still written, in its own place -- whole frames (a ragged last patch row, two views) and
+    row-interleaved strip shards, against the fully evaluated frame with linear tiles."""
+    from ray_marching_b200 import parallel
+    scene = S.make_synthetic_scene(64, 0, True)
+    loop = _loop(scene, W, H, n=n)
+    q = torch.nn.functional.normalize(torch.tensor([[1.0, 0, 0, 0], [0.9, 0.1, -0.3, 0.05]], device=DEV), dim=-1)[:n]
+    t = torch.tensor([[0.0, 0, -4.0], [0.5, 0.2, -3.5]], device=DEV)[:n]
+    full = loop.render_planes(q, t, gbuffer=True, modes=(0, 3))
+    depth = lambda r: (r.pos - r.origin).norm(dim=-1)
+    loop.cull = True
+    cul = loop.render_planes(q, t, gbuffer=True, modes=(0, 3))
+    assert torch.equal(cul.origin, full.origin) and torch.equal(cul.dirs, full.dirs)      # exact: placement
+    assert torch.equal(cul.images[3], full.images[3])                                   # vignette: ray only
+    assert ((depth(cul) - depth(full)).abs() / depth(full)).max().item() < 1e-5
+    total = n * W * H
+    for G, strip in ((2, 8 * W), (3, 4 * W)):
+        got = torch.full_like(full.pos, float("nan"))
+        for g_ in range(G):
+            sh = parallel.shard_strips(total, g_, G, strip)
+            part = loop.render_planes(q, t, gbuffer=True, modes=(0,), **sh)
+            idx = parallel.strip_ray_index(sh, device=DEV)
+            assert torch.equal(part.origin, full.origin[idx]) and torch.equal(part.dirs, full.dirs[idx])
+            got[idx] = part.pos
+        d = (got - full.origin).norm(dim=-1)
+        assert ((d - depth(full)).abs() / depth(full)).max().item() < 1e-5
+
+
+@pytest.mark.gpu
 def test_inline_rounded_math_is_bit_identical_to_ieee():
     """csrc/rm_math.cuh: the branch-free sqrt / div / reciprocal the IEEE-policy kernels use are the
     in-range instruction sequences of sqrt.rn / div.rn; they must agree bit for bit with the

@@ -102,3 +102,28 @@ def test_fake_kernels_give_the_real_shapes(tape_args):
         fn, fl = torch.ops.rm_b200.normals(fcode, fpar, fp, 5e-2, tape.n_nodes, tape.max_depth)
     for a, b in ((real, fake), (rn, fn), (rl, fl)):
         assert a.shape == b.shape and a.dtype == b.dtype and a.device == b.device
+
+
+def test_opcheck_render_loss(tape_args):
+    """rm_b200::render_loss (the fused loss + backward kernel): schema, fake kernel, autograd registration and
+    AOT dispatch; one block of rays, so the float atomics add in a fixed order."""
+    tape, code, par = tape_args
+    q = torch.nn.functional.normalize(torch.tensor([[0.99, 0.03, -0.08, 0.05]], device=DEV), dim=-1)
+    t = torch.tensor([[0.0, 0.1, -1.5]], device=DEV)
+    poses = ops.pose_records(q, t)
+    W, H, px = 10, 6, 3.45e-6
+    n = W * H
+    gen = torch.Generator().manual_seed(9)
+    lam_t = torch.rand(n, generator=gen).to(DEV)
+    dep_t = (1.0 + 0.2 * torch.rand(n, generator=gen)).to(DEV)
+    common = (1, W, H, px * H, px * W, px * H, 8, 5e-2)
+    tail = (1.0 / n, 1.0 / n, 0, n, tape.n_nodes, tape.max_depth, 1e-7)
+    # no gradient requested: loss only
+    torch.library.opcheck(torch.ops.rm_b200.render_loss.default,
+                          (code, par, poses) + common + (lam_t, dep_t) + tail + (False, 0, 0), test_utils=UTILS[:3])
+    # differentiable inputs, one target missing, an interleaved shard description
+    torch.library.opcheck(torch.ops.rm_b200.render_loss.default,
+                          (code, par.clone().requires_grad_(True), poses.clone().requires_grad_(True)) + common +
+                          (lam_t, None) + tail + (True, 0, 0), test_utils=UTILS)
+    real = torch.ops.rm_b200.render_loss(code, par, poses, *common, lam_t, dep_t, *tail, True, 0, 0)
+    assert real[0].shape == () and real[1].shape == (2,) and real[2].shape == par.shape and real[3].shape == poses.shape
