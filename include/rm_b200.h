@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define RM_B200_ABI_VERSION 6
+#define RM_B200_ABI_VERSION 7
 
 typedef enum RmStatus {
     RM_OK = 0,
@@ -241,7 +241,13 @@ typedef struct RmLossArgs {
     float weight_lambertian;        /* weight of sum_r (lambertian_r - target_r)^2, e.g. 1/n for a mean */
     float weight_depth;             /* weight of sum_r (depth_r - target_r)^2                       */
     float* loss_out;                /* DEVICE [2], overwritten: the two weighted sums over this shard */
+    int64_t scratch_floats;         /* size of the scratch passed to rm_render_loss_bwd, in floats (checked) */
 } RmLossArgs;
+
+/* Floats of scratch rm_render_loss_bwd needs for this tape, ray count and step count: the replayed
+ * trajectory (as rm_bwd_scratch_floats) plus one record per replayed evaluation and union node, which the
+ * reverse pass reads back instead of re-evaluating the scene. */
+int64_t rm_loss_scratch_floats(const RmTape* tape, int64_t n_rays, int32_t steps);
 
 /* Forward AND backward of the inverse-rendering loss of SURVEY.md 8(d) (config 4),
  *     loss = w_l sum_r (clamp(-v.n, 0, 1)_r - lam*_r)^2 + w_d sum_r (|p_S - o|_r - depth*_r)^2,
@@ -252,9 +258,10 @@ typedef struct RmLossArgs {
  * Writes loss->loss_out[2], d loss / d par [tape->n_par] and d loss / d poses [n_views][RM_POSE_STRIDE]
  * (overwritten; gradients of the SUM of both terms with unit upstream).  dpar == dposes == NULL evaluates
  * the loss only.  Uses args->ray_begin, n_rays, steps, normals_eps, bwd_converge_tol (bounces must be 0);
- * a sharded job sums loss_out / dpar / dposes over shards (one all-reduce). */
+ * a sharded job sums loss_out / dpar / dposes over shards (one all-reduce).
+ * `scratch` holds loss->scratch_floats >= rm_loss_scratch_floats(tape, n_rays, steps) floats (else RM_ERR_INVALID). */
 int rm_render_loss_bwd(const RmTape* tape, const RmCamera* cam, const float* poses,
-                       const RmRenderArgs* args, const RmLossArgs* loss, float* traj_scratch,
+                       const RmRenderArgs* args, const RmLossArgs* loss, float* scratch,
                        float* dpar, float* dposes, void* stream);
 
 /* Measurement aid for the FP32 roofline denominator (bench.py): blocks x 256 threads, each issuing

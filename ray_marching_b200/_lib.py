@@ -18,7 +18,7 @@ LIB_PATH = os.environ.get("RM_B200_LIB") or os.path.join(_HERE, "csrc", "librm_b
 POSE_STRIDE = 8
 REDUCE_FLOATS = 8
 MARCH_BWD_STATIC_MAX_FLOATS = 8388608      # include/rm_b200.h: RM_MARCH_BWD_STATIC_MAX_FLOATS
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 
 class RmTape(C.Structure):
@@ -54,7 +54,8 @@ class RmRenderGrads(C.Structure):
 
 class RmLossArgs(C.Structure):
     _fields_ = [("target_lambertian", C.c_void_p), ("target_depth", C.c_void_p),
-                ("weight_lambertian", C.c_float), ("weight_depth", C.c_float), ("loss_out", C.c_void_p)]
+                ("weight_lambertian", C.c_float), ("weight_depth", C.c_float), ("loss_out", C.c_void_p),
+                ("scratch_floats", C.c_int64)]
 
 
 _SIGNATURES = {
@@ -90,6 +91,7 @@ _SIGNATURES = {
     "rm_render_loss_bwd": (C.c_int, [C.POINTER(RmTape), C.POINTER(RmCamera), C.c_void_p,
                                      C.POINTER(RmRenderArgs), C.POINTER(RmLossArgs), C.c_void_p,
                                      C.c_void_p, C.c_void_p, C.c_void_p]),
+    "rm_loss_scratch_floats": (C.c_int64, [C.POINTER(RmTape), C.c_int64, C.c_int32]),
     "rm_probe_ffma": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "rm_probe_issue": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
     "rm_probe_math": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]),

@@ -21,6 +21,7 @@
 #include "../../include/rm_b200.h"
 #include "rm_host.h"
 #include "rm_shade.cuh"
+#include <cstdlib>
 #include "rm_sweep.cuh"
 
 namespace rm {
@@ -42,6 +43,15 @@ namespace rm {
 #endif
 #ifndef RM_LOSS_FAST_REPLAY
 #define RM_LOSS_FAST_REPLAY 1     // rm_render_loss_bwd replays the march with approximate sqrt / exp (see forward_pass)
+#endif
+#ifndef RM_LOSS_PATCHES
+#define RM_LOSS_PATCHES 1   // rm_render_loss_bwd: 8 x 4-pixel warp tiles when the ray range allows (render_bwd_body)
+#endif
+#ifndef RM_LOSS_ONFLY_MIN_INSTR
+#define RM_LOSS_ONFLY_MIN_INSTR 24
+#endif
+#ifndef RM_LOSS_ONFLY
+#define RM_LOSS_ONFLY 1           // rm_render_loss_bwd: node records kept from the replay, leaves re-evaluated by the sweep
 #endif
 constexpr int KB = RM_KB;        // samples per thread in the backward kernels (1, 2 or 4)
 constexpr int BLOCK_B = 128;
@@ -113,6 +123,43 @@ __device__ __forceinline__ void traj_load(float* traj, int s, float (&x)[KB], fl
     }
 }
 
+// Node-record scratch of the fused loss kernel (RM_LOSS_ONFLY), indexed by thread slot like the trajectory:
+// per evaluation of the replay (march steps, then the four offset samples of the stencil) f and, per union
+// node, its raw value and winning child -- NR = 1 + 2 n_nodes floats, each a plane over the slots so that a
+// warp stores / loads 128 contiguous bytes.  The reverse tasks read them back instead of re-evaluating the
+// scene in a recording pass; a smooth union's children are re-evaluated, value-only, by the sweep itself.
+__device__ __forceinline__ size_t nrec_index(int eval, int i, int k, int nr) {
+    const size_t n_slots = (size_t)gridDim.x * BLOCK_B * KB;
+    const size_t slot = ((size_t)blockIdx.x * BLOCK_B + threadIdx.x) * KB + k;
+    return ((size_t)eval * nr + i) * n_slots + slot;
+}
+template <int CAP>
+__device__ __forceinline__ void nrec_store(float* nrec, int n_nodes, int eval, const NodeRecords<KB, CAP>& rec,
+                                           const float (&f)[KB]) {
+    const int nr = 1 + 2 * n_nodes;
+#pragma unroll
+    for (int k = 0; k < KB; ++k) {
+        nrec[nrec_index(eval, 0, k, nr)] = f[k];
+        for (int node = 0; node < n_nodes; ++node) {
+            nrec[nrec_index(eval, 1 + 2 * node, k, nr)] = rec.d[node][k];
+            nrec[nrec_index(eval, 2 + 2 * node, k, nr)] = __int_as_float(rec.win[node][k]);
+        }
+    }
+}
+template <int CAP>
+__device__ __forceinline__ void nrec_load(const float* nrec, int n_nodes, const int (&eval)[KB],
+                                          NodeRecords<KB, CAP>& rec, float (&f)[KB]) {
+    const int nr = 1 + 2 * n_nodes;
+#pragma unroll
+    for (int k = 0; k < KB; ++k) {
+        f[k] = nrec[nrec_index(eval[k], 0, k, nr)];
+        for (int node = 0; node < n_nodes; ++node) {
+            rec.d[node][k] = nrec[nrec_index(eval[k], 1 + 2 * node, k, nr)];
+            rec.win[node][k] = __float_as_int(nrec[nrec_index(eval[k], 2 + 2 * node, k, nr)]);
+        }
+    }
+}
+
 // Shared memory: [tape par (n_par floats) | accumulator columns], see GradAcc (rm_sweep.cuh).
 template <int MODE>
 __device__ __forceinline__ GradAcc<MODE> stage_accumulators(unsigned char* smem, int n_par, int acc_shared) {
@@ -165,13 +212,15 @@ struct StencilAdjoint {          // per-sample inputs of the stencil's reverse t
 // forward of its loss, so there is no separately computed trajectory to reproduce, and a 2^-22 relative
 // change of the evaluation points moves the gradient by ~1e-6 of its size.  rm_render_bwd / rm_march_bwd keep
 // the IEEE replay (it mirrors the IEEE forward kernel that produced the planes).
-template <int CAP, bool FASTM = false>
+template <int CAP, bool FASTM = false, bool ONFLY = false>
 __device__ __forceinline__ void forward_pass(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                              int steps, float tol, const Stencil* st, float* traj,
                                              float (&px)[KB], float (&py)[KB], float (&pz)[KB],
                                              const float (&vx)[KB], const float (&vy)[KB],
                                              const float (&vz)[KB], int (&conv)[KB],
-                                             float (&ux)[KB], float (&uy)[KB], float (&uz)[KB]) {
+                                             float (&ux)[KB], float (&uy)[KB], float (&uz)[KB],
+                                             NodeRecords<KB, CAP>* rec = nullptr, float* nrec = nullptr,
+                                             int n_nodes = 0) {
     float o0[KB], prev[KB];                                    // prev: last step length while settled
 #pragma unroll
     for (int k = 0; k < KB; ++k) { conv[k] = 0; ux[k] = uy[k] = uz[k] = o0[k] = 0.f; prev[k] = -1.f; }
@@ -187,7 +236,13 @@ __device__ __forceinline__ void forward_pass(const TapeCode<CAP>& code, int n_in
         for (int k = 0; k < KB; ++k) { x[k] = px[k] + dx; y[k] = py[k] + dy; z[k] = pz[k] + dz; }
         // ONE call site for steps and samples (a second, correctly rounded one for the samples costs c4b
         // 32.9 -> 35.3 ms in instruction-cache misses and changes no gradient digit: profiles/r02/variants.md)
-        eval_scene<KB, FASTM, CAP>(code, n_instr, spar, x, y, z, d);
+        if constexpr (ONFLY) {
+            // ... recording the union nodes (rec->c, constant per tape, stays in *rec for the reverse pass)
+            eval_scene<KB, FASTM, CAP, 0, 2>(code, n_instr, spar, x, y, z, d, nullptr, nullptr, rec);
+            if (nrec != nullptr) nrec_store<CAP>(nrec, n_nodes, task, *rec, d);
+        } else {
+            eval_scene<KB, FASTM, CAP>(code, n_instr, spar, x, y, z, d);
+        }
         if (marching) {
             bool at_rest = true;
 #pragma unroll
@@ -229,7 +284,10 @@ __device__ __forceinline__ void forward_pass(const TapeCode<CAP>& code, int n_in
 //          with a_0 (S_n - 1), S_n = sum_{j<n} c^j, n = S - conv: the implicit-surface adjoint of the
 //          hit point truncated to the n steps the reference unrolls; O(tol) from the step-by-step sum.
 //   7..    exact steps s = max_warp(conv) - 1 .. 0 of the unrolled graph.
-template <int CAP, int MODE, bool FASTM = false>
+// ONFLY (the fused loss kernel): no recording pass -- the union-node records of every replayed evaluation
+// come back from the scratch (nrec_load) and the sweep evaluates leaf values itself; the centre sample
+// (task 4) is skipped, its adjoint is identically zero for this loss (no f(p), no Laplacian term).
+template <int CAP, int MODE, bool FASTM = false, bool ONFLY = false>
 __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                              int steps, const Stencil* st, const StencilAdjoint* sa,
                                              float* traj, const GradAcc<MODE> sacc, const int (&conv)[KB],
@@ -238,7 +296,9 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
                                              const float (&vx)[KB], const float (&vy)[KB],
                                              const float (&vz)[KB], float (&lx)[KB], float (&ly)[KB],
                                              float (&lz)[KB], float (&dvx)[KB], float (&dvy)[KB],
-                                             float (&dvz)[KB]) {
+                                             float (&dvz)[KB],
+                                             NodeRecords<KB, CAP>* frec = nullptr, const float* nrec = nullptr,
+                                             int n_nodes = 0) {
     bool any_tail = false;
     int first_exact = 0;
 #pragma unroll
@@ -281,12 +341,22 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
             for (int k = 0; k < KB; ++k)
                 a[k] = s < conv[k] ? lx[k] * vx[k] + ly[k] * vy[k] + lz[k] * vz[k] : 0.f;
         }
-        NodeRecords<KB, CAP> rec;
-        eval_record<KB, CAP, FASTM>(code, n_instr, spar, x, y, z, rec, f);
-        sweep_vjp<KB, CAP, MODE>(code, n_instr, spar, x, y, z, a, rec, sacc, gx, gy, gz);
+        if constexpr (ONFLY) {
+            int ev[KB];                                        // which replayed evaluation this task revisits
+#pragma unroll
+            for (int k = 0; k < KB; ++k)
+                ev[k] = task < 5 ? steps + task : (task < 7 ? (conv[k] < steps ? conv[k] : 0) : s);
+            nrec_load<CAP>(nrec, n_nodes, ev, *frec, f);
+            sweep_vjp<KB, CAP, MODE, true, FASTM>(code, n_instr, spar, x, y, z, a, *frec, sacc, gx, gy, gz);
+        } else {
+            NodeRecords<KB, CAP> rec;
+            eval_record<KB, CAP, FASTM>(code, n_instr, spar, x, y, z, rec, f);
+            sweep_vjp<KB, CAP, MODE>(code, n_instr, spar, x, y, z, a, rec, sacc, gx, gy, gz);
+        }
         if (task < 5) {
 #pragma unroll
             for (int k = 0; k < KB; ++k) { lx[k] += gx[k]; ly[k] += gy[k]; lz[k] += gz[k]; }
+            if (ONFLY && task == 3) task = 4;                  // the centre sample carries no adjoint
             if (task == 4 && !tail) task = 6;                  // no lane has a tail: skip tasks 5, 6
         } else if (task == 5) {
 #pragma unroll
@@ -399,6 +469,9 @@ struct RenderBwdParams {
     float w_lam, w_depth;
     float* loss_out;        // [2]: weighted sums of squared residuals (lambertian, depth)
     int want_grad;          // 0: loss only (no reverse pass)
+    float* nrec;            // node-record scratch (RM_LOSS_ONFLY; see nrec_index)
+    int n_nodes;
+    int patch_cols;         // > 0: a warp owns an 8 x 4 pixel patch (patch_cols = width / 8), see render_bwd_body
 };
 
 // Adjoint of w = R(q) b w.r.t. q for an upstream adjoint l of w (R = rotation polynomial):
@@ -445,7 +518,7 @@ __device__ __forceinline__ void flush_pose_grad(float* dposes, int view, const f
 //     d/dn = -g_lam v,  d/dv = -g_lam n,  d/dp_S = g_depth e/|e|,  d/do = -g_depth e/|e|   (e = p_S - o)
 // (clamp passes its gradient on the closed interval, the norm has sub-gradient 0 at 0: torch's
 // conventions).  No G-buffer plane, no gradient plane and no elementwise kernel exists on this route.
-template <int CAP, int MODE, bool LOSS>
+template <int CAP, int MODE, bool LOSS, bool ONFLY = false>
 __device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const float* par, int n_instr, int n_par,
                                                 const float* __restrict__ poses, const RenderBwdParams& P) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -465,7 +538,16 @@ __device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const
     const int iters = P.iters;
     for (int it = 0; it < iters; ++it) {                    // block-uniform trip count (see backward_grid)
         const int64_t g = ((int64_t)it * gridDim.x + blockIdx.x) * BLOCK_B + threadIdx.x;
-        const int64_t first = g * KB;
+        int64_t first = g * KB;
+        if (KB == 1 && P.patch_cols > 0) {
+            // 2-D warp tiles: the 32 rays of a warp are an 8 x 4 pixel patch instead of 32 pixels of one row, so
+            // that what the warp decides together (settled rays, exact steps to reverse, dead children of a
+            // smooth union) is decided for neighbouring rays.  Whole rows, width % 8 == 0, rows % 4 == 0 (host).
+            const unsigned t = (unsigned)(g >> 5), lane = threadIdx.x & 31u;
+            const unsigned ty = t / (unsigned)P.patch_cols, tx = t - ty * (unsigned)P.patch_cols;
+            first = (int64_t)(ty * 4u + (lane >> 3)) * P.cam.width + (tx * 8u + (lane & 7u));
+            if (first >= n) first = n;                      // (grid rounding: past the end, nothing is stored)
+        }
         // ---- rays from the pixel index (PinholeCamera.forward) ----
         float px[KB], py[KB], pz[KB], vx[KB], vy[KB], vz[KB];
         Pose pose;
@@ -480,8 +562,13 @@ __device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const
         // ---- forward pass: replay the march, sample the stencil offsets ----
         int conv[KB];
         float ux[KB], uy[KB], uz[KB];
-        forward_pass<CAP, LOSS && RM_LOSS_FAST_REPLAY>(code, n_instr, spar, P.steps, P.tol, need_stencil ? &P.st : nullptr,
-                                                       P.traj, px, py, pz, vx, vy, vz, conv, ux, uy, uz);
+        NodeRecords<KB, ONFLY ? CAP : 1> frec_store;       // ONFLY: union-node records, shared by replay and sweeps
+        NodeRecords<KB, CAP>* frec = nullptr;
+        if constexpr (ONFLY) frec = &frec_store;
+        forward_pass<CAP, LOSS && RM_LOSS_FAST_REPLAY, ONFLY>(code, n_instr, spar, P.steps, P.tol,
+                                                              need_stencil ? &P.st : nullptr, P.traj, px, py, pz,
+                                                              vx, vy, vz, conv, ux, uy, uz, frec,
+                                                              P.want_grad ? P.nrec : nullptr, P.n_nodes);
 
         // ---- adjoints of the stencil outputs (SDFNormals.forward, ray_marching.py:115-125), of
         //      f(p_S) (control.py:244), of p_S, the direction and the origin ----
@@ -553,9 +640,9 @@ __device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const
         if (LOSS && !P.want_grad) continue;                 // loss evaluation only
 
         // ---- reverse pass: stencil samples, converged tail, exact steps ----
-        reverse_pass<CAP, MODE, LOSS && RM_LOSS_FAST_REPLAY>(code, n_instr, spar, P.steps, &P.st,
+        reverse_pass<CAP, MODE, LOSS && RM_LOSS_FAST_REPLAY, ONFLY>(code, n_instr, spar, P.steps, &P.st,
                           (need_stencil || (!LOSS && P.g.sdf != nullptr)) ? &sa : nullptr, P.traj, sacc, conv,
-                          px, py, pz, vx, vy, vz, lx, ly, lz, dvx, dvy, dvz);
+                          px, py, pz, vx, vy, vz, lx, ly, lz, dvx, dvy, dvz, frec, P.nrec, P.n_nodes);
 
         // ---- camera pose: origin = R(q) o_b + t, dir = R(q) v_b ----
 #pragma unroll
@@ -611,6 +698,26 @@ __global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
 render_loss_bwd_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
                        const float* __restrict__ poses, const __grid_constant__ RenderBwdParams P) {
     render_bwd_body<CAP, MODE, true>(code, par, n_instr, n_par, poses, P);
+}
+// ... with the union-node records kept from the replay and the leaves re-evaluated by the sweep (long tapes)
+template <int CAP, int MODE>
+__global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
+render_loss_onfly_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
+                         const float* __restrict__ poses, const __grid_constant__ RenderBwdParams P) {
+    render_bwd_body<CAP, MODE, true, true>(code, par, n_instr, n_par, poses, P);
+}
+// Which of the two: the records pay for themselves once a recording walk over the tape costs more than their
+// traffic and the slower replay (measured: c4b, 69 instructions, 27.3 -> 23.3 ms; c4, 6 instructions,
+// 0.41 -> 0.52 ms).  A tape-specialised library replays straight-line code and never uses them.
+inline bool loss_onfly(const RmTape* t) {
+#if defined(RM_SPEC_INC) || !RM_LOSS_ONFLY
+    (void)t;
+    return false;
+#else
+    int min_instr = RM_LOSS_ONFLY_MIN_INSTR;
+    if (const char* e = getenv("RM_B200_LOSS_ONFLY_MIN_INSTR")) min_instr = atoi(e);   // tests: force either route
+    return t->n_instr >= min_instr;
+#endif
 }
 
 inline int check_backward_tape(const RmTape* t) {
@@ -695,6 +802,14 @@ extern "C" int64_t rm_bwd_scratch_floats(int64_t n_rays, int32_t steps) {
     return (int64_t)steps * backward_grid(n_rays) * BLOCK_B * KB * 3;
 }
 
+// rm_render_loss_bwd: the trajectory plus (RM_LOSS_ONFLY) the node records of steps + 4 evaluations.
+extern "C" int64_t rm_loss_scratch_floats(const RmTape* tape, int64_t n_rays, int32_t steps) {
+    if (tape == nullptr || n_rays <= 0 || steps < 0) return 0;
+    const int64_t slots = (int64_t)backward_grid(n_rays) * BLOCK_B * KB;
+    const int64_t traj = (int64_t)steps * slots * 3;
+    return loss_onfly(tape) ? traj + (int64_t)(steps + 4) * (1 + 2 * (int64_t)tape->n_nodes) * slots : traj;
+}
+
 extern "C" int rm_sdf_vjp(const RmTape* tape, const float* points, const float* grad_sdf, int64_t n,
                           float* dpoints, float* dpar, void* stream) {
     if (int s = check_backward_tape(tape)) return s;
@@ -760,6 +875,7 @@ static int prepare_render_bwd(const char* who, const RmTape* tape, const RmCamer
     P->traj = traj_scratch; P->dpar = dpar; P->dposes = dposes;
     P->target_lam = P->target_depth = nullptr; P->w_lam = P->w_depth = 0.f; P->loss_out = nullptr;
     P->want_grad = want_grad ? 1 : 0;
+    P->nrec = nullptr; P->n_nodes = tape->n_nodes; P->patch_cols = 0;
     return RM_OK;
 }
 
@@ -793,11 +909,28 @@ extern "C" int rm_render_loss_bwd(const RmTape* tape, const RmCamera* cam, const
         return s;
     RM_CUDA(cudaMemsetAsync(loss->loss_out, 0, 2 * sizeof(float), (cudaStream_t)stream));
     if (a->n_rays == 0) return RM_OK;
+    if (loss->scratch_floats < rm_loss_scratch_floats(tape, a->n_rays, a->steps))
+        return fail(RM_ERR_INVALID, "rm_render_loss_bwd: scratch of %lld floats, rm_loss_scratch_floats asks for %lld",
+                    (long long)loss->scratch_floats, (long long)rm_loss_scratch_floats(tape, a->n_rays, a->steps));
+    P.nrec = traj_scratch + (int64_t)a->steps * backward_grid(a->n_rays) * BLOCK_B * KB * 3;
+#if RM_LOSS_PATCHES
+    {
+        const int64_t Wd = cam->width;
+        if (KB == 1 && Wd % 8 == 0 && a->ray_begin % Wd == 0 && a->n_rays % (4 * Wd) == 0 &&
+            (a->strip_rays == 0 || a->strip_rays % (4 * Wd) == 0) && a->n_rays / 32 <= 0x7fffffff)
+            P.patch_cols = (int)(Wd / 8);
+    }
+#endif
     P.target_lam = loss->target_lambertian; P.target_depth = loss->target_depth;
     P.w_lam = loss->weight_lambertian; P.w_depth = loss->weight_depth; P.loss_out = loss->loss_out;
     const size_t sm = backward_smem(tape);
-    RM_BWD_LAUNCH(tape, render_loss_bwd_kernel, backward_grid(a->n_rays), sm, stream, tape->par, tape->n_instr,
-                  tape->n_par, poses, P);
+    if (loss_onfly(tape)) {
+        RM_BWD_LAUNCH(tape, render_loss_onfly_kernel, backward_grid(a->n_rays), sm, stream, tape->par, tape->n_instr,
+                      tape->n_par, poses, P);
+    } else {
+        RM_BWD_LAUNCH(tape, render_loss_bwd_kernel, backward_grid(a->n_rays), sm, stream, tape->par, tape->n_instr,
+                      tape->n_par, poses, P);
+    }
     RM_CUDA(cudaGetLastError());
     return RM_OK;
 }

@@ -95,6 +95,20 @@ __device__ __forceinline__ float prim_grad(int op, const float4* P, float x, flo
     return x;
 }
 
+// Value only, at the frame-local point: the interpreter's leaf bodies behind one dispatch (the on-the-fly
+// sweep's liveness test; same math policy as the replay that produced the union values it is compared with).
+template <bool FAST>
+__device__ __forceinline__ float prim_value(int op, const float4* P, float x, float y, float z) {
+    switch (op) {
+        case OP_SPHERE: return prim_sphere<FAST>(P[0], x, y, z);
+        case OP_BOX: return prim_box<FAST>(P[0], x, y, z);
+        case OP_TORUS: return prim_torus<FAST>(P[0], x, y, z);
+        case OP_LINE: return prim_line<FAST>(P[0], P[1], P[2], x, y, z);
+        case OP_DISK: return prim_disk<FAST>(P[0], x, y, z);
+        default: return x;                                   // OP_PLANE
+    }
+}
+
 // Sum each of 32 per-lane values across the warp; lane L ends up holding the total of value L.
 __device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
 #pragma unroll

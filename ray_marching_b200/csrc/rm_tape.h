@@ -96,10 +96,10 @@ __host__ __device__ __forceinline__ int4 expand_one(int head, int w1, bool with_
 // plain child of a HARD union (its CLOSE folds with min, no post-op, not the root): then the whole union may be
 // skipped, exactly, whenever a lower bound of its value exceeds the parent's running minimum (rm_eval.cuh).
 // (The ordinal field of that OPEN holds the float4 offset of the union's sphere table: tape.py.)
+// In every launch the z word of that union's CLOSE (no parameter record of its own) holds the pc of its OPEN.
 inline void expand_instructions(const int32_t* words, int n, int4* out, bool with_cull) {
     for (int i = 0; i < n; ++i) out[i] = expand_one(words[2 * i], words[2 * i + 1], with_cull);
     out[n] = make_int4(0, 0, 0, 0);
-    if (!with_cull) return;
     int open_at[MAX_DEPTH + 1], sp = 0;
     for (int i = 0; i < n; ++i) {
         const int op = head_op(out[i].x);
@@ -111,7 +111,8 @@ inline void expand_instructions(const int32_t* words, int n, int4* out, bool wit
             if (op != OP_CLOSE_SMOOTH || !word_cull(out[i].y)) continue;
             const bool plain_min_child = !(out[i].x & HEAD_ROOT) && head_fold(out[i].x) == FOLD_MIN &&
                                          head_npost(out[i].x) == 0;
-            out[o].w |= (i & 0xFFFF) | (plain_min_child ? (1 << 16) : 0);
+            if (with_cull) out[o].w |= (i & 0xFFFF) | (plain_min_child ? (1 << 16) : 0);
+            out[i].z = o;                    // every launch: the CLOSE of the culled union knows its OPEN (reverse sweep)
         }
     }
 }

@@ -480,17 +480,17 @@ def _render_loss(code: Tensor, par: Tensor, poses: Tensor, n_views: int, width: 
         if x is not None and x.numel() != n_rays:
             raise _lib.RmError(f"render_loss: a target plane has {x.numel()} elements for {n_rays} rays")
     spec = _spec.selected_for(code)
-    traj = torch.empty(max(int((spec or lib()).rm_bwd_scratch_floats(n_rays, steps)), 1), device=dev,
-                       dtype=torch.float32)
+    t = _tape_struct(code, par, n_nodes, max_depth)
+    n_scratch = max(int((spec or lib()).rm_loss_scratch_floats(C.byref(t), n_rays, steps)), 1)
+    traj = torch.empty(n_scratch, device=dev, dtype=torch.float32)
     terms = torch.empty(2, device=dev, dtype=torch.float32)
     poses = poses.contiguous()
     dpar = torch.empty_like(par) if want_grad else torch.zeros_like(par)
     dposes = torch.empty_like(poses) if want_grad else torch.zeros_like(poses)
     a = RmRenderArgs(int(ray_begin), int(n_rays), int(steps), 0, float(eps), 0.0, 0.0, 0, -1, 1, 0, 0, 0, float(tol),
                      int(strip_rays), int(strip_stride))
-    la = RmLossArgs(ptr(tl), ptr(td), float(w_lam), float(w_depth), ptr(terms))
+    la = RmLossArgs(ptr(tl), ptr(td), float(w_lam), float(w_depth), ptr(terms), n_scratch)
     cam = camera_struct(n_views, width, height, focal, sensor_w, sensor_h)
-    t = _tape_struct(code, par, n_nodes, max_depth)
     args = (C.byref(t), C.byref(cam), ptr(poses), C.byref(a), C.byref(la), ptr(traj),
             ptr(dpar) if want_grad else None, ptr(dposes) if want_grad else None, stream_ptr(dev))
     if spec is not None:

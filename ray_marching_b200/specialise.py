@@ -232,7 +232,7 @@ def _source_digest(generated: str) -> str:
 _loaded = {}
 # entry points a specialised library exports besides rm_abi_version / rm_last_error
 SPEC_EXPORTS = ("rm_render", "rm_render_bwd", "rm_render_loss_bwd", "rm_march_bwd", "rm_sdf_vjp",
-                "rm_bwd_scratch_floats")
+                "rm_bwd_scratch_floats", "rm_loss_scratch_floats")
 
 # Libraries selected by RenderLoop.specialise(), per TAPE OBJECT: the autograd ops (ops.py:
 # render_gbuffer / render_bwd) receive the tape's host code tensor, not the Tape, so the key is that

@@ -97,6 +97,39 @@ class _Affine:
     level: int             # chain depth (0 for a top-level affine)
 
 
+def _inverse_3x3(A: torch.Tensor) -> torch.Tensor:
+    """Inverse of (n, 3, 3) matrices by the adjugate (rows r0, r1, r2: columns of the inverse are
+    r1 x r2, r2 x r0, r0 x r1 over the determinant); elementwise torch only."""
+    r0, r1, r2 = A[:, 0], A[:, 1], A[:, 2]
+    c0, c1, c2 = torch.linalg.cross(r1, r2), torch.linalg.cross(r2, r0), torch.linalg.cross(r0, r1)
+    det = (r0 * c0).sum(-1)
+    return torch.stack([c0, c1, c2], dim=-1) / det[:, None, None]
+
+
+def _singular_range_3x3(A: torch.Tensor):
+    """(upper bound of the largest, lower bound of the smallest) singular value of (n, 3, 3) matrices:
+    the trigonometric closed form for the eigenvalues of the symmetric A^T A, moved outwards by 1e-3
+    relative -- far more than its float32 error, far less than anything the bounds are used for
+    (culling margins).  Elementwise torch only."""
+    M = A.transpose(-1, -2) @ A
+    m00, m11, m22 = M[:, 0, 0], M[:, 1, 1], M[:, 2, 2]
+    m01, m02, m12 = M[:, 0, 1], M[:, 0, 2], M[:, 1, 2]
+    q = (m00 + m11 + m22) / 3.0
+    p1 = m01 * m01 + m02 * m02 + m12 * m12
+    p2 = (m00 - q) ** 2 + (m11 - q) ** 2 + (m22 - q) ** 2 + 2.0 * p1
+    p = torch.sqrt(p2 / 6.0)
+    ps = torch.where(p > 0, p, torch.ones_like(p))
+    b00, b11, b22 = (m00 - q) / ps, (m11 - q) / ps, (m22 - q) / ps
+    b01, b02, b12 = m01 / ps, m02 / ps, m12 / ps
+    det_b = (b00 * (b11 * b22 - b12 * b12) - b01 * (b01 * b22 - b12 * b02) + b02 * (b01 * b12 - b11 * b02))
+    phi = torch.acos(torch.clamp(det_b / 2.0, -1.0, 1.0)) / 3.0
+    big = q + 2.0 * p * torch.cos(phi)
+    small = q + 2.0 * p * torch.cos(phi + 2.0943951023931953)          # + 2 pi / 3
+    # a scaled rotation (p ~ 0) has a triple eigenvalue q; the margin also covers the cancellation in `small`
+    tol = 1e-3 * big + 1e-6
+    return torch.sqrt(big + tol), torch.sqrt(torch.clamp(small - tol, min=0.0))
+
+
 class Tape:
     """Lowered scene: static code + the recipe that gathers live parameters into ``par``."""
 
@@ -401,14 +434,17 @@ class Tape:
     def _cull_pieces(self, theta, d, A, b):
         """Bounding spheres of the culled union's leaf children (not differentiated): world centre and
         radius / s_min per leaf, and (s_min, L_max, log2 n) for the union record, where every frame
-        satisfies s_min |dx| <= |A dx| <= L_max |dx|.  Left at zero (= culling off) while autograd
-        records: the differentiable forward runs in IEEE mode, which never culls."""
+        satisfies s_min |dx| <= |A dx| <= L_max |dx|.  Plain elementwise torch only (closed-form
+        singular values and inverse of the 3x3 frames): the lowering runs inside captured CUDA graphs
+        (the optimisation step of config 4b), where the LAPACK-backed ``torch.linalg`` calls cannot.
+        The forward culling kernels and the reverse sweep of the fused loss kernel (dead children of
+        the union, csrc/rm_sweep.cuh) read them."""
+        import math
         nC = len(self._cull_leaves)
-        if theta.requires_grad and torch.is_grad_enabled():
-            return [theta.new_zeros(4 * nC), theta.new_zeros(3)]
         with torch.no_grad():
+            theta = theta.detach()
             c = d["cull"]
-            tp = torch.cat([theta.detach(), theta.new_zeros(1)])
+            tp = torch.cat([theta, theta.new_zeros(1)])
             radius = tp[c["add"]].sum(-1) + tp[c["box"]].norm(dim=-1)
             s, e = tp[c["ls"]], tp[c["le"]]
             radius = radius + 0.5 * (e - s).norm(dim=-1)
@@ -416,17 +452,16 @@ class Tape:
             smin = theta.new_ones(nC)
             lmax = theta.new_ones(())
             if A is not None:
-                sv = torch.linalg.svdvals(A.detach().double()).to(theta.dtype)    # (nA, 3) descending
-                lmax = torch.clamp(sv[:, 0].max(), min=1.0)
+                A = A.detach()
+                smax_a, smin_a = _singular_range_3x3(A)
+                lmax = torch.clamp(smax_a.max(), min=1.0)
                 has = c["frame"] >= 0
                 f = c["frame"].clamp(min=0)
-                Ainv = torch.linalg.inv(A.detach().double()).to(theta.dtype)
-                world = (Ainv[f] @ (centre - b.detach()[f])[..., None])[..., 0]
+                world = (_inverse_3x3(A)[f] @ (centre - b.detach()[f])[..., None])[..., 0]
                 centre = torch.where(has[:, None], world, centre)
-                smin = torch.where(has, sv[f, 2], smin)
+                smin = torch.where(has, smin_a[f], smin)
             smin_all = torch.clamp(smin.min(), max=1.0) if nC else theta.new_ones(())
             rec = torch.cat([centre, (radius / smin)[:, None]], dim=-1).reshape(-1)
-            import math
             union = torch.stack([smin_all, lmax, theta.new_tensor(math.log2(max(self._cull_n, 1)))])
             return [rec, union]
 

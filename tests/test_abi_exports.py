@@ -29,7 +29,7 @@ def test_struct_layout_matches_header():
     assert ctypes.sizeof(_lib.RmCamera) == 24
     assert ctypes.sizeof(_lib.RmRenderOut) == 16 * 8
     assert ctypes.sizeof(_lib.RmRenderArgs) == 88
-    assert ctypes.sizeof(_lib.RmLossArgs) == 32
+    assert ctypes.sizeof(_lib.RmLossArgs) == 40
     assert ctypes.sizeof(_lib.RmRenderGrads) == 48
 
 

@@ -334,6 +334,44 @@ def test_loss_fused_kernel_matches_reference_fixture(golden, tag, build, special
     assert rel_err(flat_grads(list(scene.parameters())), g[f"grads/{tag}/dparams_flat"]) < 1e-3
 
 
+@pytest.mark.parametrize("min_instr", ["0", "100000"])
+@pytest.mark.parametrize("w,h", [(16, 16), (24, 10)])
+def test_loss_kernel_routes_agree_with_the_reference(golden, monkeypatch, min_instr, w, h):
+    """The fused loss kernel has two reverse routes (csrc/rm_backward.cu: loss_onfly) -- a recording walk per
+    reverse task, or union-node records kept from the replay with leaf values re-evaluated by the sweep and
+    children that are dead for the whole warp jumped over -- and two ray layouts (8 x 4-pixel warp patches when
+    the range is whole rows with width % 8 == 0 and rows % 4 == 0, else 32 rays of a row).  Every combination
+    against the reference's autograd (fixture, 16 x 16) resp. the composed route (24 x 10: linear tiles)."""
+    monkeypatch.setenv("RM_B200_LOSS_ONFLY_MIN_INSTR", min_instr)
+    g = golden("grads")
+    tag = "syn8"
+    scene = S.make_synthetic_scene(8, 0, True)
+    loop = RenderLoop(scene, normals_eps=5e-2, **cases.config1_camera(w, h)).to(DEV)
+    q = t32(g[f"grads/{tag}/q"]).to(DEV).requires_grad_(True)
+    t = t32(g[f"grads/{tag}/t"]).to(DEV).requires_grad_(True)
+    if (w, h) == (16, 16):
+        lam_t, depth_t = t32(g[f"grads/{tag}/lam_target"]).to(DEV), t32(g[f"grads/{tag}/depth_target"]).to(DEV)
+        loop.inverse_loss(q, t, lam_t, depth_t, marching_steps=32).backward()
+        assert rel_err(q.grad, g[f"grads/{tag}/dq"]) < 1e-3
+        assert rel_err(t.grad, g[f"grads/{tag}/dt"]) < 1e-3
+        assert rel_err(flat_grads(list(scene.parameters())), g[f"grads/{tag}/dparams_flat"]) < 1e-3
+        return
+    gen = torch.Generator().manual_seed(3)
+    lam_t = torch.rand(1, h, w, 1, generator=gen).to(DEV)
+    depth_t = (3.0 + 0.3 * torch.rand(1, h, w, 1, generator=gen)).to(DEV)
+    loop.inverse_loss(q, t, lam_t, depth_t, marching_steps=32).backward()
+    fused = (q.grad.clone(), t.grad.clone(), flat_grads(list(scene.parameters())))
+    scene2 = S.make_synthetic_scene(8, 0, True)
+    loop2 = RenderLoop(scene2, normals_eps=5e-2, **cases.config1_camera(w, h)).to(DEV)
+    q2, t2 = q.detach().clone().requires_grad_(True), t.detach().clone().requires_grad_(True)
+    gb = loop2.gbuffer(q2, t2, 32)
+    loss = ((((-(gb["dirs"] * gb["normals"]).sum(-1, keepdim=True)).clamp(0, 1) - lam_t) ** 2).mean() +
+            (((gb["pos"] - gb["origin"]).norm(dim=-1, keepdim=True) - depth_t) ** 2).mean())
+    loss.backward()
+    assert rel_err(fused[0], q2.grad) < 3e-4 and rel_err(fused[1], t2.grad) < 3e-4
+    assert rel_err(fused[2], flat_grads(list(scene2.parameters()))) < 3e-4
+
+
 def test_loss_fused_kernel_equals_the_composed_route_and_shards_sum():
     """Same loss through (a) gbuffer + torch shader algebra + autograd and (b) the fused kernel: equal to
     float32 rounding.  Ray-range shards of (b) sum to the whole (what a tile-sharded job all-reduces);
