@@ -466,7 +466,7 @@ def run_forward(ctx, wl, steps, warmup, headline):
     # ---- dominant kernel alone (render_kernel) --------------------------------------------------
     res0 = keep[0]
     poses_k = ops.pose_records(q, t)
-    fm = 2 if (loop.fast_math and loop.cull) else int(loop.fast_math)
+    fm = ops.fast_math_level(loop.fast_math, loop.cull)
 
     def launch_render():                               # `reduce` given: no init launch inside the pair
         ops.render(tape, loop.camera.struct(), poses_k, steps=STEPS, normals_eps=EPS, mode_mask=mode_mask,
@@ -481,23 +481,28 @@ def run_forward(ctx, wl, steps, warmup, headline):
     extras = {}
     # the same frame with bounding-sphere culling of smooth-union children
     if tape._cull_union is not None and not loop.cull and (headline or wl["name"] == "c5"):
-        loop.cull = True
-        cbuf = [None]
+        notes = {"culling_exact": "whole job, RenderLoop.cull = 'exact': a smooth union under a hard union is skipped "
+                                  "where its bounding spheres prove, for every ray of the warp, that it loses the "
+                                  "min -- pixels bit-identical to the headline (tests); executed < algorithmic "
+                                  "work, so no roofline fraction is quoted",
+                 "culling": "whole job, RenderLoop.cull = True: additionally smooth-union children whose term is "
+                            "provably < 2^-24 of the largest are skipped (march steps and fast stencil samples); "
+                            "executed < algorithmic work, so no roofline fraction is quoted"}
+        for key, mode in (("culling_exact", "exact"), ("culling", True)):
+            loop.cull = mode
+            cbuf = [None]
 
-        def cstep(i):
-            cbuf[0] = frame(q, t, cbuf[0])
-        for i in range(2):
-            cstep(i)
-        n_c = max(2, min(steps, 5))
-        c_ms, _ = time_total(ctx, n_c, cstep, flush=True)
-        loop.cull = False
-        c_all = ctx.gather(c_ms / n_c)
-        extras["culling"] = {"ms_per_step": max(c_all), "value": total_rays / (max(c_all) * 1e-3) / 1e6,
-                             "unit": "Mrays/s", "per_rank_ms": Ctx.stats(c_all),
-                             "note": "whole job, RenderLoop.cull = True: bounding-sphere culling of smooth-"
-                                     "union children inside march steps; executed < algorithmic work, so no "
-                                     "roofline fraction is quoted"}
-        del cbuf
+            def cstep(i):
+                cbuf[0] = frame(q, t, cbuf[0])
+            for i in range(2):
+                cstep(i)
+            n_c = max(2, min(steps, 5))
+            c_ms, _ = time_total(ctx, n_c, cstep, flush=True)
+            loop.cull = False
+            c_all = ctx.gather(c_ms / n_c)
+            extras[key] = {"ms_per_step": max(c_all), "value": total_rays / (max(c_all) * 1e-3) / 1e6,
+                           "unit": "Mrays/s", "per_rank_ms": Ctx.stats(c_all), "note": notes[key]}
+            del cbuf
     # contiguous vs interleaved sharding of the single image (per-rank kernel time)
     if headline and wl["sharding"] == "strips" and world > 1:
         a, b = parallel.shard_range(W * H, rank, world)
@@ -929,7 +934,7 @@ def compact(rec):
     r = rec["roofline"]
     keep["roofline"] = {k: r[k] for k in ("kernel", "frac", "achieved", "peak", "kernel_ms", "algorithmic_flops_per_ray",
                                           "mufu_frac") if k in r}
-    for k in ("culling", "interpreter", "routes_eager"):
+    for k in ("culling", "culling_exact", "interpreter", "routes_eager"):
         if k in rec:
             keep[k] = rec[k]
     return keep

@@ -105,7 +105,10 @@ typedef struct RmRenderArgs {
     int32_t early_exit;     /* 1: stop marching a ray once p stops changing (bit-identical) */
     int32_t fast_math;      /* 1: approximate sqrt/exp inside march steps (stencil stays IEEE);
                                2: additionally skip smooth-union children whose bounding sphere proves
-                               their softmax term < 2^-24 of the largest one (warp-parallel test)  */
+                               their softmax term < 2^-24 of the largest one (warp-parallel test);
+                               3: like 1, plus only the EXACT skip of 2 -- a whole smooth union under a hard
+                               union is not evaluated where its bounding spheres prove that it loses the
+                               min for every ray of the warp (same pixels as 1, bit for bit)           */
     const float* cmap;      /* [4096][3] cyclic colour LUT for modes 6,7 (may be NULL otherwise) */
     float   bwd_converge_tol; /* rm_render_bwd only: see rm_march_bwd (0 = reverse every step) */
     /* Interleaved shard ("row-interleaved tiles"): with strip_rays > 0 the shard's LOCAL

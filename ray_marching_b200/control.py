@@ -45,7 +45,9 @@ class RenderLoop(nn.Module):
         self.shader = Shader()
         self.early_exit = False          # bit-identical fixed-point exit of the march loop
         self.fast_math = True            # approximate sqrt/exp inside march steps only
-        self.cull = False                # bounding-sphere culling of smooth-union children (march steps)
+        # bounding-sphere culling: False; "exact" = whole smooth unions skipped where they provably lose the
+        # enclosing min (bit-identical pixels); True = additionally children below 2^-24 of the largest term
+        self.cull = False
 
     def specialise(self, enable: bool = True) -> "RenderLoop":
         """Compiles (nvcc, once per scene structure, cached under build/spec/) and selects a render
@@ -77,7 +79,7 @@ class RenderLoop(nn.Module):
                           normals_eps=self.normals.normals_eps, mode_mask=mask, gbuffer=gbuffer,
                           display_mode=display_mode, degree=degree, bounces=bounces,
                           hit_tau=hit_tau, lift_delta=lift_delta, early_exit=self.early_exit,
-                          fast_math=2 if (self.fast_math and self.cull) else int(self.fast_math),
+                          fast_math=ops.fast_math_level(self.fast_math, self.cull),
                           cmap=self.shader.cyclic_cmap,
                           ray_begin=ray_begin, n_rays=n_rays, strip_rays=strip_rays,
                           strip_stride=strip_stride, finalize=finalize, out=out)
@@ -109,7 +111,7 @@ class RenderLoop(nn.Module):
         res = ops.render(tape_of(self.scene), cam, poses, steps=marching_steps,
                          normals_eps=self.normals.normals_eps, mode_mask=1 << m, degree=degree,
                          early_exit=self.early_exit,
-                         fast_math=2 if (self.fast_math and self.cull) else int(self.fast_math),
+                         fast_math=ops.fast_math_level(self.fast_math, self.cull),
                          cmap=self.shader.cyclic_cmap)
         fine = res.images[m].reshape(N, H, factor, W, factor, -1)
         return fine.mean(dim=(2, 4)).expand(-1, H, W, 3)

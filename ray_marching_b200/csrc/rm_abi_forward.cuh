@@ -235,7 +235,7 @@ extern "C" int rm_render(const RmTape* tape, const RmCamera* cam, const float* p
         }
     }
 #else
-    RM_WITH_CODE_EX(tape, a->fast_math >= 2, {
+    RM_WITH_CODE_EX(tape, (a->fast_math >= 3 ? 2 : (a->fast_math >= 2 ? 1 : 0)), {
         if (sfast && a->fast_math >= 2) {
             if (int s = prepare_smem(render_kernel<true, CAP, true, true>, sm)) return s;
             render_kernel<true, CAP, true, true><<<grid, threads, sm, (cudaStream_t)stream>>>(

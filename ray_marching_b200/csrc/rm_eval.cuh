@@ -341,7 +341,8 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
                                 continue;
                             }
                         }
-                        cull_on = __reduce_and_sync(0xffffffffu, (sm > -CUDART_INF_F && rw < CUDART_INF_F) ? 1u : 0u) != 0u;
+                        const bool exact_only = (ins.w & (1 << 17)) != 0;       // rm_tape.h: no child may be masked
+                        cull_on = !exact_only && __reduce_and_sync(0xffffffffu, (sm > -CUDART_INF_F && rw < CUDART_INF_F) ? 1u : 0u) != 0u;
                         mask_base = -0x40000000;                               // first child: compute a mask
                         if (cull_on) RM_STAT(1, 1);
                     }

@@ -94,10 +94,12 @@ __host__ __device__ __forceinline__ int4 expand_one(int head, int w1, bool with_
 // Culling launches: the OPEN of the culled smooth union additionally carries, in the (otherwise unused)
 // post-op offset field of its w word, the pc of its CLOSE [0:16] and a flag [16] saying that the union is a
 // plain child of a HARD union (its CLOSE folds with min, no post-op, not the root): then the whole union may be
-// skipped, exactly, whenever a lower bound of its value exceeds the parent's running minimum (rm_eval.cuh).
+// skipped, exactly, whenever a lower bound of its value exceeds the parent's running minimum (rm_eval.cuh);
+// flag [17] (cull_mode 2) says that this exact skip is ALL the launch may do: no child is masked.
 // (The ordinal field of that OPEN holds the float4 offset of the union's sphere table: tape.py.)
 // In every launch the z word of that union's CLOSE (no parameter record of its own) holds the pc of its OPEN.
-inline void expand_instructions(const int32_t* words, int n, int4* out, bool with_cull) {
+inline void expand_instructions(const int32_t* words, int n, int4* out, int cull_mode) {
+    const bool with_cull = cull_mode != 0;
     for (int i = 0; i < n; ++i) out[i] = expand_one(words[2 * i], words[2 * i + 1], with_cull);
     out[n] = make_int4(0, 0, 0, 0);
     int open_at[MAX_DEPTH + 1], sp = 0;
@@ -111,14 +113,15 @@ inline void expand_instructions(const int32_t* words, int n, int4* out, bool wit
             if (op != OP_CLOSE_SMOOTH || !word_cull(out[i].y)) continue;
             const bool plain_min_child = !(out[i].x & HEAD_ROOT) && head_fold(out[i].x) == FOLD_MIN &&
                                          head_npost(out[i].x) == 0;
-            if (with_cull) out[o].w |= (i & 0xFFFF) | (plain_min_child ? (1 << 16) : 0);
+            if (with_cull) out[o].w |= (i & 0xFFFF) | (plain_min_child ? (1 << 16) : 0) | (cull_mode == 2 ? (1 << 17) : 0);
             out[i].z = o;                    // every launch: the CLOSE of the culled union knows its OPEN (reverse sweep)
         }
     }
 }
 template <int CAP>
-inline void expand_code(const int32_t* words, int n, TapeCode<CAP>& code, bool with_cull = false) {
-    expand_instructions(words, n, code.ins, with_cull);
+inline void expand_code(const int32_t* words, int n, TapeCode<CAP>& code, int cull_mode = 0) {
+    const bool with_cull = cull_mode != 0;
+    expand_instructions(words, n, code.ins, cull_mode);
     code.hdr = make_int4(0, n, 0, 0);
     if (n >= 2) {
         const int open = words[0], close = words[2 * (n - 1)];

@@ -127,7 +127,7 @@ class FrameLoop:
         ops.render(tape_of(loop.scene), loop.camera.struct(), self.path.poses, steps=self.marching_steps,
                    normals_eps=loop.normals.normals_eps, display_mode=self.mode, degree=self.degree,
                    early_exit=loop.early_exit,
-                   fast_math=2 if (loop.fast_math and loop.cull) else int(loop.fast_math),
+                   fast_math=ops.fast_math_level(loop.fast_math, loop.cull),
                    cmap=loop.shader.cyclic_cmap, out=self._res)
 
     def frame(self, translation_input=None, orientation_input=None) -> Tensor:
@@ -147,7 +147,7 @@ class FrameLoop:
             # everything _launch bakes into the captured kernel arguments
             loop, cam = self.loop, self.loop.camera
             key = (par.data_ptr(), par._version, scripted, self.mode, self.degree, self.marching_steps,
-                   bool(loop.early_exit), bool(loop.fast_math), bool(loop.cull),
+                   bool(loop.early_exit), bool(loop.fast_math), str(loop.cull),
                    id(getattr(tape_of(loop.scene), "spec_lib", None)), float(loop.normals.normals_eps),
                    cam.num_cameras, cam.px_width, cam.px_height, float(cam.focal_length),
                    float(cam.sensor_width), float(cam.sensor_height))

@@ -37,6 +37,18 @@ MODE_CHANNELS = [1, 1, 1, 1, 3, 1, 3, 3]
 NORMALISED_MODES = (1 << 1) | (1 << 2) | (1 << 5)
 
 
+def fast_math_level(fast_math, cull) -> int:
+    """``RenderLoop.fast_math`` / ``.cull`` -> ``RmRenderArgs.fast_math`` (include/rm_b200.h): culling needs
+    the approximate-math kernels; ``cull="exact"`` selects the skips that leave every pixel bit-identical."""
+    if not fast_math:
+        return 0
+    if isinstance(cull, str):
+        if cull != "exact":
+            raise ValueError(f"cull must be False, True or 'exact', not {cull!r}")
+        return 3
+    return 2 if cull else 1
+
+
 def _tape_struct(code: Tensor, par: Tensor, n_nodes: int, max_depth: int) -> RmTape:
     if code.is_cuda or code.dtype != torch.int32 or not code.is_contiguous():
         raise _lib.RmError("tape code must be a contiguous int32 HOST tensor (tape.code_tensor())")
@@ -169,7 +181,7 @@ def render(tape, cam: RmCamera, poses: Tensor, *, steps: int = 32, normals_eps: 
     """One launch of the fused camera->march->stencil->shade kernel (no autograd).
 
     ``fast_math``: 0 IEEE everywhere, 1 approximate sqrt/exp inside march steps, 2 additionally
-    bounding-sphere culling of smooth-union children inside march steps.
+    bounding-sphere culling of smooth-union children, 3 = 1 + only the exact whole-union skips of 2.
     ``strip_rays`` / ``strip_stride``: interleaved shard (``parallel.shard_strips``; ``n_rays`` is then
     required): local ray l = global ray ``ray_begin + (l // strip_rays) * strip_stride + l % strip_rays``.
     ``finalize=False`` leaves modes 1/2/5 un-normalised (so a sharded job can all-reduce

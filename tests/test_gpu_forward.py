@@ -309,6 +309,33 @@ def test_culling_matches_full_evaluation(n_prims):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("n_prims,W,H,bounces", [(64, 128, 72, 2), (64, 96, 54, 2), (512, 64, 36, 0), (8, 64, 32, 1)])
+def test_exact_culling_is_bit_identical(n_prims, W, H, bounces):
+    """RenderLoop.cull = "exact" (fast_math = 3): the only thing skipped is a whole smooth union under a hard
+    union where its bounding spheres prove, for every ray of the warp, that it loses the min -- min(parent, f_U)
+    = parent -- so every plane equals the fully evaluated frame BIT FOR BIT (march positions, stencil, shaders,
+    reflected segments; patch tiles and linear tiles)."""
+    scene = S.make_synthetic_scene(n_prims, 0, True)
+    loop = _loop(scene, W, H)
+    q = torch.nn.functional.normalize(torch.tensor([[0.98, 0.05, -0.15, 0.02]], device=DEV), dim=-1)
+    t = torch.tensor([[0.2, -0.1, -4.0]], device=DEV)
+    kw = dict(marching_steps=32, bounces=bounces, hit_tau=1e-3, lift_delta=0.1)
+    full = loop.render_planes(q, t, modes=(0, 3, 4), **kw)
+    full_g = loop.render_planes(q, t, gbuffer=True, modes=(0,), **kw)
+    loop.cull = "exact"
+    ex = loop.render_planes(q, t, modes=(0, 3, 4), **kw)
+    ex_g = loop.render_planes(q, t, gbuffer=True, modes=(0,), **kw)
+    same = lambda a, b: torch.equal(a, b) or torch.equal(torch.nan_to_num(a, nan=-7.0), torch.nan_to_num(b, nan=-7.0))
+    for m in (0, 3, 4):
+        assert same(ex.images[m], full.images[m]), m
+    for name in ("pos", "sdf", "normals", "laplacian", "dirs", "origin"):
+        assert same(getattr(ex_g, name), getattr(full_g, name)), name
+    with pytest.raises(ValueError):
+        loop.cull = "roughly"
+        loop.render_planes(q, t, modes=(0,))
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("W,H,n", [(128, 40, 1), (64, 24, 2), (192, 16, 1)])
 def test_culled_patch_tiles_put_every_pixel_in_place(W, H, n):
     """The culled kernel walks 16 x 8-pixel warp patches when the width is a multiple of 64 (render_kernel):

@@ -18,6 +18,8 @@ loop = RenderLoop(wl["scene"](), num_cameras=1, px_width=W, px_height=H, focal_l
                   sensor_width=bench.PX * W, sensor_height=bench.PX * H, normals_eps=bench.EPS).to(dev)
 if os.environ.get("RM_CULL") == "1":
     loop.cull = True
+if os.environ.get("RM_CULL") == "exact":
+    loop.cull = "exact"
 if os.environ.get("RM_SPEC") == "1":
     loop.specialise(True)
 q, t = bench.ring_pose(0, 1, wl["cam_t"], dev)
