@@ -158,3 +158,15 @@ def test_quaternion_edge_cases():
     tt = 2 * torch.linalg.cross(u, vv)
     (vv + w * tt + torch.linalg.cross(u, tt)).sum().backward()
     np.testing.assert_allclose(qq.grad.numpy(), q2.grad.numpy(), rtol=1e-5, atol=1e-6)
+
+
+def test_fast_math_levels():
+    """RenderLoop.fast_math / .cull -> RmRenderArgs.fast_math (include/rm_b200.h): culling only exists on the
+    approximate-math kernels; "exact" is the bit-identical subset."""
+    from ray_marching_b200 import ops
+    assert ops.fast_math_level(False, False) == 0 and ops.fast_math_level(False, True) == 0
+    assert ops.fast_math_level(False, "exact") == 0
+    assert ops.fast_math_level(True, False) == 1 and ops.fast_math_level(True, True) == 2
+    assert ops.fast_math_level(True, "exact") == 3
+    with pytest.raises(ValueError):
+        ops.fast_math_level(True, "fuzzy")

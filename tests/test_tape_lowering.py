@@ -120,3 +120,51 @@ def test_lowered_params_cache_sees_parameter_writes():
         tape.invalidate()
         d = tape.lowered_params()
         assert d is not c and float(-d[tape._perm.tolist().index(1 + tape.n_theta + tape._slot(k))]) == 7.0
+
+
+def test_sphere_table_bounds_hold_and_need_no_lapack():
+    """tape.py: the culled union's sphere table comes from closed-form 3x3 singular values / inverses (plain
+    elementwise torch: the lowering runs inside captured CUDA graphs).  The bounds must bracket LAPACK's values,
+    tightly for the near-isometric frames scenes use; every child's surface must lie inside its sphere; and the
+    table must be there while autograd records (the loss kernel's reverse sweep reads it)."""
+    g = torch.Generator().manual_seed(0)
+    A = torch.randn(500, 3, 3, generator=g)
+    A[:200] = torch.linalg.qr(torch.randn(200, 3, 3, generator=g))[0] * (0.5 + torch.rand(200, 1, 1, generator=g))
+    hi, lo = T._singular_range_3x3(A)
+    sv = torch.linalg.svdvals(A.double()).float()
+    assert (hi >= sv[:, 0]).all() and (lo <= sv[:, 2]).all()
+    assert (hi[:200] / sv[:200, 0]).max() < 1.002 and (lo[:200] / sv[:200, 2]).min() > 0.998
+    assert ((T._inverse_3x3(A[:200]) @ A[:200] - torch.eye(3)).abs().max() < 1e-4)
+
+    scene = S.make_synthetic_scene(16, 0, True)
+    tape = T.tape_of(scene)
+    assert tape._cull_union is not None
+    par_grad = tape.lowered_params("cpu")                      # autograd recording: table present
+    with torch.no_grad():
+        par = tape.lowered_params("cpu")
+    assert par_grad.requires_grad and torch.equal(par_grad.detach(), par)
+    code = tape.code
+    opens = [i for i, (w0, w1) in enumerate(code.tolist()) if T.decode(w0, w1)[0] == T.OP_OPEN_SMOOTH and T.decode(w0, w1)[8]]
+    assert len(opens) == 1
+    o = opens[0]
+    table_f4 = T.decode(*code[o].tolist())[5]                  # ordinal field of the OPEN = table offset (float4)
+    union_rec = par[T.decode(*code[o].tolist())[6] * 4: T.decode(*code[o].tolist())[6] * 4 + 4]
+    assert union_rec[0] < 0 and 0 < union_rec[1] <= 1.0 and union_rec[2] >= 1.0 and union_rec[3] == 4.0   # -k, s_min, L_max, log2 16
+    # every leaf child: sample its zero set through the oracle-free route -- points at which the child's own
+    # value is ~0 must lie inside its sphere.  Use the children's evaluation on random points near the sphere.
+    children = list(scene.sdfs[1].sdfs) if hasattr(scene.sdfs[1], "sdfs") else []
+    assert len(children) == 16
+    pts = (torch.rand(20000, 3, generator=g) - 0.5) * 8.0
+    for j, child in enumerate(children):
+        cx, cy, cz, r = par[(table_f4 + j) * 4: (table_f4 + j) * 4 + 4].tolist()
+        with torch.no_grad():
+            f = _cpu_value(child, pts)
+        inside = f <= 0
+        if inside.any():
+            d = (pts[inside] - torch.tensor([cx, cy, cz])).norm(dim=-1)
+            assert d.max().item() <= r * 1.0001, (j, d.max().item(), r)
+
+
+def _cpu_value(node, pts):
+    """Value of one scene node at CPU points through the oracle's restatement of the reference classes."""
+    return O.sdf(node, pts).reshape(-1)
