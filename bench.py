@@ -203,7 +203,7 @@ def ncu_traffic(kernel: str, workload: str):
     import glob
     import re
     tag = {"render_kernel": "render", "render_bwd_kernel": "render_bwd",
-           "render_loss_bwd_kernel": "render_loss_bwd"}[kernel]
+           "render_loss_bwd_kernel": "render_loss_bwd", "render_loss_onfly_kernel": "render_loss_onfly", "render_loss_onfly4_kernel": "render_loss_onfly4"}[kernel]
     files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*", f"*_{tag}_{workload}_summary.txt")))
     if not files:
         return None, None
@@ -773,7 +773,9 @@ def run_backward(ctx, wl, steps, warmup, headline):
         kmax = max(kern_all)
         alg = (fwd_flops + bwd_flops) * rays          # the kernel does the forward AND the backward
         ach = alg / (kmax * 1e-3) / 1e12
-        traffic, traffic_src = ncu_traffic("render_loss_bwd_kernel", wl["name"])
+        # which loss kernel runs (csrc/rm_backward.cu: loss_route): node records on long tapes
+        kname = "render_loss_onfly_kernel" if (not spec_on and tape.n_instr >= 24) else "render_loss_bwd_kernel"
+        traffic, traffic_src = ncu_traffic(kname, wl["name"])
         rec = {
             "metric": "Mrays/s fwd+bwd", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": steps,
             "warmup": max(warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -788,7 +790,7 @@ def run_backward(ctx, wl, steps, warmup, headline):
                        "per_rank_ms_per_step": Ctx.stats(rank_ms), "wall_ms_per_step": Ctx.stats(rank_wall),
                        "final_loss": float(state["loss"].detach())},
             "gpu_launches": 1 * steps,
-            "roofline": {"bound": "fp32", "kernel": "render_loss_bwd_kernel", "achieved": ach,
+            "roofline": {"bound": "fp32", "kernel": kname, "achieved": ach,
                          "peak": ctx.peak["tflops"], "unit": "TFLOP/s", "frac": ach / ctx.peak["tflops"],
                          "traffic": traffic, "traffic_from": traffic_src, "traffic_unit": "bytes of DRAM per launch",
                          "kernel_ms": kmax, "algorithmic_flops_per_ray": fwd_flops + bwd_flops,

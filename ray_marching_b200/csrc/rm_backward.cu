@@ -47,6 +47,9 @@ namespace rm {
 #ifndef RM_LOSS_PATCHES
 #define RM_LOSS_PATCHES 1   // rm_render_loss_bwd: 8 x 4-pixel warp tiles when the ray range allows (render_bwd_body)
 #endif
+#ifndef RM_LOSS_TWO_PHASE
+#define RM_LOSS_TWO_PHASE 0   // 1: long tapes take the four-ray replay (render_loss_onfly4_kernel); measured slower, see below
+#endif
 #ifndef RM_LOSS_ONFLY_MIN_INSTR
 #define RM_LOSS_ONFLY_MIN_INSTR 24
 #endif
@@ -133,8 +136,8 @@ __device__ __forceinline__ size_t nrec_index(int eval, int i, int k, int nr) {
     const size_t slot = ((size_t)blockIdx.x * BLOCK_B + threadIdx.x) * KB + k;
     return ((size_t)eval * nr + i) * n_slots + slot;
 }
-template <int CAP>
-__device__ __forceinline__ void nrec_store(float* nrec, int n_nodes, int eval, const NodeRecords<KB, CAP>& rec,
+template <class REC>
+__device__ __forceinline__ void nrec_store(float* nrec, int n_nodes, int eval, const REC& rec,
                                            const float (&f)[KB]) {
     const int nr = 1 + 2 * n_nodes;
 #pragma unroll
@@ -146,16 +149,46 @@ __device__ __forceinline__ void nrec_store(float* nrec, int n_nodes, int eval, c
         }
     }
 }
-template <int CAP>
+// (kf, ksel): the two-phase kernel (render_loss_onfly4_kernel) keeps kf rays per thread slot; field i of ray
+// ksel is plane (i * kf + ksel) of a record of nr * kf planes.
+template <class REC>
 __device__ __forceinline__ void nrec_load(const float* nrec, int n_nodes, const int (&eval)[KB],
-                                          NodeRecords<KB, CAP>& rec, float (&f)[KB]) {
-    const int nr = 1 + 2 * n_nodes;
+                                          REC& rec, float (&f)[KB], int kf = 1, int ksel = 0) {
+    const int nr = (1 + 2 * n_nodes) * kf;
 #pragma unroll
     for (int k = 0; k < KB; ++k) {
-        f[k] = nrec[nrec_index(eval[k], 0, k, nr)];
+        f[k] = nrec[nrec_index(eval[k], ksel, k, nr)];
         for (int node = 0; node < n_nodes; ++node) {
-            rec.d[node][k] = nrec[nrec_index(eval[k], 1 + 2 * node, k, nr)];
-            rec.win[node][k] = __float_as_int(nrec[nrec_index(eval[k], 2 + 2 * node, k, nr)]);
+            rec.d[node][k] = nrec[nrec_index(eval[k], (1 + 2 * node) * kf + ksel, k, nr)];
+            rec.win[node][k] = __float_as_int(nrec[nrec_index(eval[k], (2 + 2 * node) * kf + ksel, k, nr)]);
+        }
+    }
+}
+// K-generic stores of the two-phase kernel's replay (KB == 1 slots): trajectory [(s * KF + k)][slot][3],
+// records [eval][field * KF + k][slot] -- what traj_slot / nrec_load address with (kf, ksel).
+template <int KF>
+__device__ __forceinline__ void traj_store_k(float* traj, int s, const float (&x)[KF], const float (&y)[KF],
+                                             const float (&z)[KF]) {
+    const size_t n_slots = (size_t)gridDim.x * BLOCK_B;
+    const size_t slot = (size_t)blockIdx.x * BLOCK_B + threadIdx.x;
+#pragma unroll
+    for (int k = 0; k < KF; ++k) {
+        float* p = traj + ((size_t)(s * KF + k) * n_slots + slot) * 3;
+        p[0] = x[k]; p[1] = y[k]; p[2] = z[k];
+    }
+}
+template <int KF, class REC>
+__device__ __forceinline__ void nrec_store_k(float* nrec, int n_nodes, int eval, const REC& rec,
+                                             const float (&f)[KF]) {
+    const size_t n_slots = (size_t)gridDim.x * BLOCK_B;
+    const size_t slot = (size_t)blockIdx.x * BLOCK_B + threadIdx.x;
+    const size_t base = (size_t)eval * (1 + 2 * n_nodes) * KF;
+#pragma unroll
+    for (int k = 0; k < KF; ++k) {
+        nrec[(base + k) * n_slots + slot] = f[k];
+        for (int node = 0; node < n_nodes; ++node) {
+            nrec[(base + (size_t)(1 + 2 * node) * KF + k) * n_slots + slot] = rec.d[node][k];
+            nrec[(base + (size_t)(2 + 2 * node) * KF + k) * n_slots + slot] = __int_as_float(rec.win[node][k]);
         }
     }
 }
@@ -212,14 +245,14 @@ struct StencilAdjoint {          // per-sample inputs of the stencil's reverse t
 // forward of its loss, so there is no separately computed trajectory to reproduce, and a 2^-22 relative
 // change of the evaluation points moves the gradient by ~1e-6 of its size.  rm_render_bwd / rm_march_bwd keep
 // the IEEE replay (it mirrors the IEEE forward kernel that produced the planes).
-template <int CAP, bool FASTM = false, bool ONFLY = false>
+template <int CAP, bool FASTM = false, bool ONFLY = false, class REC = NodeRecords<KB, CAP>>
 __device__ __forceinline__ void forward_pass(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                              int steps, float tol, const Stencil* st, float* traj,
                                              float (&px)[KB], float (&py)[KB], float (&pz)[KB],
                                              const float (&vx)[KB], const float (&vy)[KB],
                                              const float (&vz)[KB], int (&conv)[KB],
                                              float (&ux)[KB], float (&uy)[KB], float (&uz)[KB],
-                                             NodeRecords<KB, CAP>* rec = nullptr, float* nrec = nullptr,
+                                             REC* rec = nullptr, float* nrec = nullptr,
                                              int n_nodes = 0) {
     float o0[KB], prev[KB];                                    // prev: last step length while settled
 #pragma unroll
@@ -238,8 +271,8 @@ __device__ __forceinline__ void forward_pass(const TapeCode<CAP>& code, int n_in
         // 32.9 -> 35.3 ms in instruction-cache misses and changes no gradient digit: profiles/r02/variants.md)
         if constexpr (ONFLY) {
             // ... recording the union nodes (rec->c, constant per tape, stays in *rec for the reverse pass)
-            eval_scene<KB, FASTM, CAP, 0, 2>(code, n_instr, spar, x, y, z, d, nullptr, nullptr, rec);
-            if (nrec != nullptr) nrec_store<CAP>(nrec, n_nodes, task, *rec, d);
+            eval_scene<KB, FASTM, CAP, 0, 2, REC>(code, n_instr, spar, x, y, z, d, nullptr, nullptr, rec);
+            if (nrec != nullptr) nrec_store(nrec, n_nodes, task, *rec, d);
         } else {
             eval_scene<KB, FASTM, CAP>(code, n_instr, spar, x, y, z, d);
         }
@@ -287,7 +320,7 @@ __device__ __forceinline__ void forward_pass(const TapeCode<CAP>& code, int n_in
 // ONFLY (the fused loss kernel): no recording pass -- the union-node records of every replayed evaluation
 // come back from the scratch (nrec_load) and the sweep evaluates leaf values itself; the centre sample
 // (task 4) is skipped, its adjoint is identically zero for this loss (no f(p), no Laplacian term).
-template <int CAP, int MODE, bool FASTM = false, bool ONFLY = false>
+template <int CAP, int MODE, bool FASTM = false, bool ONFLY = false, class REC = NodeRecords<KB, CAP>>
 __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_instr, const float4* spar,
                                              int steps, const Stencil* st, const StencilAdjoint* sa,
                                              float* traj, const GradAcc<MODE> sacc, const int (&conv)[KB],
@@ -297,8 +330,8 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
                                              const float (&vz)[KB], float (&lx)[KB], float (&ly)[KB],
                                              float (&lz)[KB], float (&dvx)[KB], float (&dvy)[KB],
                                              float (&dvz)[KB],
-                                             NodeRecords<KB, CAP>* frec = nullptr, const float* nrec = nullptr,
-                                             int n_nodes = 0) {
+                                             REC* frec = nullptr, const float* nrec = nullptr,
+                                             int n_nodes = 0, int kf = 1, int ksel = 0) {
     bool any_tail = false;
     int first_exact = 0;
 #pragma unroll
@@ -330,13 +363,13 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
 #pragma unroll
             for (int k = 0; k < KB; ++k) {
                 // stationary point q = p_conv, read from this lane's own slot (unused when conv == steps)
-                const float* slot = traj_slot(traj, conv[k] < steps ? conv[k] : 0) + 3 * k;
+                const float* slot = traj_slot(traj, (conv[k] < steps ? conv[k] : 0) * kf + ksel) + 3 * k;
                 x[k] = slot[0]; y[k] = slot[1]; z[k] = slot[2];
                 if (task == 5) a0[k] = conv[k] < steps ? lx[k] * vx[k] + ly[k] * vy[k] + lz[k] * vz[k] : 0.f;
                 a[k] = task == 5 ? a0[k] : rest[k];
             }
         } else {
-            traj_load(traj, s, x, y, z);
+            traj_load(traj, s * kf + ksel, x, y, z);
 #pragma unroll
             for (int k = 0; k < KB; ++k)
                 a[k] = s < conv[k] ? lx[k] * vx[k] + ly[k] * vy[k] + lz[k] * vz[k] : 0.f;
@@ -346,8 +379,8 @@ __device__ __forceinline__ void reverse_pass(const TapeCode<CAP>& code, int n_in
 #pragma unroll
             for (int k = 0; k < KB; ++k)
                 ev[k] = task < 5 ? steps + task : (task < 7 ? (conv[k] < steps ? conv[k] : 0) : s);
-            nrec_load<CAP>(nrec, n_nodes, ev, *frec, f);
-            sweep_vjp<KB, CAP, MODE, true, FASTM>(code, n_instr, spar, x, y, z, a, *frec, sacc, gx, gy, gz);
+            nrec_load(nrec, n_nodes, ev, *frec, f, kf, ksel);
+            sweep_vjp<KB, CAP, MODE, true, FASTM, REC>(code, n_instr, spar, x, y, z, a, *frec, sacc, gx, gy, gz);
         } else {
             NodeRecords<KB, CAP> rec;
             eval_record<KB, CAP, FASTM>(code, n_instr, spar, x, y, z, rec, f);
@@ -562,10 +595,11 @@ __device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const
         // ---- forward pass: replay the march, sample the stencil offsets ----
         int conv[KB];
         float ux[KB], uy[KB], uz[KB];
-        NodeRecords<KB, ONFLY ? CAP : 1> frec_store;       // ONFLY: union-node records, shared by replay and sweeps
-        NodeRecords<KB, CAP>* frec = nullptr;
+        using NodeRec = NodeRecords<KB, ONFLY ? 1 : CAP>;  // ONFLY: union nodes only (no per-instruction values)
+        NodeRec frec_store;                                // ... shared by the replay and the sweeps
+        NodeRec* frec = nullptr;
         if constexpr (ONFLY) frec = &frec_store;
-        forward_pass<CAP, LOSS && RM_LOSS_FAST_REPLAY, ONFLY>(code, n_instr, spar, P.steps, P.tol,
+        forward_pass<CAP, LOSS && RM_LOSS_FAST_REPLAY, ONFLY, NodeRec>(code, n_instr, spar, P.steps, P.tol,
                                                               need_stencil ? &P.st : nullptr, P.traj, px, py, pz,
                                                               vx, vy, vz, conv, ux, uy, uz, frec,
                                                               P.want_grad ? P.nrec : nullptr, P.n_nodes);
@@ -640,7 +674,7 @@ __device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const
         if (LOSS && !P.want_grad) continue;                 // loss evaluation only
 
         // ---- reverse pass: stencil samples, converged tail, exact steps ----
-        reverse_pass<CAP, MODE, LOSS && RM_LOSS_FAST_REPLAY, ONFLY>(code, n_instr, spar, P.steps, &P.st,
+        reverse_pass<CAP, MODE, LOSS && RM_LOSS_FAST_REPLAY, ONFLY, NodeRec>(code, n_instr, spar, P.steps, &P.st,
                           (need_stencil || (!LOSS && P.g.sdf != nullptr)) ? &sa : nullptr, P.traj, sacc, conv,
                           px, py, pz, vx, vy, vz, lx, ly, lz, dvx, dvy, dvz, frec, P.nrec, P.n_nodes);
 
@@ -706,18 +740,240 @@ render_loss_onfly_kernel(const __grid_constant__ TapeCode<CAP> code, const float
                          const float* __restrict__ poses, const __grid_constant__ RenderBwdParams P) {
     render_bwd_body<CAP, MODE, true, true>(code, par, n_instr, n_par, poses, P);
 }
+// ---- two-phase loss kernel for long tapes (render_loss_onfly4_kernel) ---------------------------------
+// One ray per thread leaves the replay's interpreter decode unamortised (~100 warp instructions per tape
+// instruction against ~35 at four rays per thread).  Here a thread REPLAYS four rays at once (phase 1:
+// replay_record, node records and trajectory to the slot scratch, planes [.][k][slot]) and then REVERSES them
+// one after the other (phase 2: the one-ray reverse_pass with (kf, ksel) addressing).  The four rays of a
+// thread are the same lane position of four different warp tiles -- tiles t0 + 4 k + warp -- so that in phase
+// 2, pass k, the 32 lanes of a warp hold one whole tile (an 8 x 4 pixel patch, or 32 rays of a row): what the
+// warp decides together is still decided for neighbouring rays, and every scratch element is read by the
+// thread that wrote it (no block barrier between the phases).
+// Measured (c4b, 1024^2): 23.6 ms against 21.4 ms for the one-ray route -- the replay executes a third of the
+// instructions, but 512 rays per block iteration quantise 2048 iterations onto 592 block slots (1.73 waves,
+// 13 % idle) and the four-ray recording interpreter spills inside the 128-register kernel.  Kept as an opt-in
+// route (RM_B200_LOSS_ROUTE=onfly4, -DRM_LOSS_TWO_PHASE=1) with the same tests; a per-warp tile queue would
+// remove the quantisation.
+constexpr int KF = 4;
+
+template <int CAP>
+__device__ __forceinline__ void replay_record(const TapeCode<CAP>& code, int n_instr, const float4* spar,
+                                              int steps, float tol, const Stencil* st, float* traj,
+                                              float (&px)[KF], float (&py)[KF], float (&pz)[KF],
+                                              const float (&vx)[KF], const float (&vy)[KF],
+                                              const float (&vz)[KF], int (&conv)[KF],
+                                              float (&ux)[KF], float (&uy)[KF], float (&uz)[KF],
+                                              NodeRecords<KF, 1>& rec, float* nrec, int n_nodes) {
+    float o0[KF], prev[KF];
+#pragma unroll
+    for (int k = 0; k < KF; ++k) { conv[k] = 0; ux[k] = uy[k] = uz[k] = o0[k] = 0.f; prev[k] = -1.f; }
+    const int n_tasks = steps + (st != nullptr ? 4 : 0);
+    for (int task = 0; task < n_tasks; ++task) {               // forward_pass, four rays wide
+        const bool marching = task < steps;
+        const int j = marching ? 4 : task - steps;
+        float x[KF], y[KF], z[KF], d[KF];
+        float dx = 0.f, dy = 0.f, dz = 0.f;
+        if (!marching) { dx = st->off[j][0]; dy = st->off[j][1]; dz = st->off[j][2]; }
+        else if (nrec != nullptr) traj_store_k<KF>(traj, task, px, py, pz);
+#pragma unroll
+        for (int k = 0; k < KF; ++k) { x[k] = px[k] + dx; y[k] = py[k] + dy; z[k] = pz[k] + dz; }
+        eval_scene<KF, true, CAP, 0, 2, NodeRecords<KF, 1>>(code, n_instr, spar, x, y, z, d, nullptr, nullptr, &rec);
+        if (nrec != nullptr) nrec_store_k<KF>(nrec, n_nodes, task, rec, d);
+        if (marching) {
+            bool at_rest = true;
+#pragma unroll
+            for (int k = 0; k < KF; ++k) {
+                const float scale = 1.f + fmaxf(fabsf(px[k]), fmaxf(fabsf(py[k]), fabsf(pz[k])));
+                const float ad = fabsf(d[k]);
+                const bool within = ad <= tol * scale;                       // false for NaN
+                if (!within) conv[k] = task + 1;
+                at_rest = at_rest && within && prev[k] >= ad;
+                prev[k] = within ? ad : -1.f;
+                px[k] = fmaf(d[k], vx[k], px[k]); py[k] = fmaf(d[k], vy[k], py[k]); pz[k] = fmaf(d[k], vz[k], pz[k]);
+            }
+#if RM_BWD_EARLY_BREAK
+            if (__all_sync(0xffffffffu, at_rest)) task = steps - 1;
+#endif
+        } else {
+            const float wx = st->w[j][0], wy = st->w[j][1], wz = st->w[j][2], first = st->first[j];
+#pragma unroll
+            for (int k = 0; k < KF; ++k) {
+                o0[k] = first != 0.f ? d[k] : o0[k];
+                const float dj = d[k] - o0[k];
+                ux[k] = fmaf(wx, dj, ux[k]); uy[k] = fmaf(wy, dj, uy[k]); uz[k] = fmaf(wz, dj, uz[k]);
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ float pick(const float (&a)[KF], int j) {      // a[j] without a local-memory array
+    return j == 0 ? a[0] : (j == 1 ? a[1] : (j == 2 ? a[2] : a[3]));
+}
+
+template <int CAP, int MODE>
+__global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
+render_loss_onfly4_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
+                          const float* __restrict__ poses, const __grid_constant__ RenderBwdParams P) {
+    static_assert(KB == 1, "the two-phase loss kernel reverses one ray per thread");
+    extern __shared__ __align__(16) unsigned char smem[];
+    const GradAcc<MODE> sacc = stage_accumulators<MODE>(smem, n_par, P.acc_shared);
+    const float4* spar = stage_params(par, n_par, smem);
+    const int64_t n = P.n_rays;
+    const bool need_stencil = P.target_lam != nullptr;
+    const int64_t per_view = (int64_t)P.cam.width * P.cam.height;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    float cam_acc[7];
+#pragma unroll
+    for (int i = 0; i < 7; ++i) cam_acc[i] = 0.f;
+    int acc_view = -1;
+    float loss_l = 0.f, loss_d = 0.f;
+
+    for (int it = 0; it < P.iters; ++it) {                     // block-uniform trip count
+        // ---- the thread's four rays: lane `lane` of tiles t0 + 4 k + warp ----
+        const int64_t t0 = ((int64_t)it * gridDim.x + blockIdx.x) * (KF * (BLOCK_B / 32));
+        int64_t first[KF];
+        float px[KF], py[KF], pz[KF], vx[KF], vy[KF], vz[KF];
+        Pose pose;
+        int cur_view = -1;
+#pragma unroll
+        for (int k = 0; k < KF; ++k) {
+            const int64_t t = t0 + k * (BLOCK_B / 32) + warp;
+            int64_t f = t * 32 + lane;
+            if (P.patch_cols > 0) {
+                const unsigned ty = (unsigned)t / (unsigned)P.patch_cols, tx = (unsigned)t - ty * (unsigned)P.patch_cols;
+                f = (int64_t)(ty * 4u + ((unsigned)lane >> 3)) * P.cam.width + (tx * 8u + ((unsigned)lane & 7u));
+            }
+            first[k] = f < n ? f : n;                          // past the end: marched (clamped duplicate), never used
+            float ob[3], vb[3], ow[3], vw[3];
+            world_ray(P.cam, poses, shard_ray(P.ray_begin, P.strip_rays, P.strip_stride, first[k]), pose, cur_view, ob, vb, ow, vw);
+            px[k] = ow[0]; py[k] = ow[1]; pz[k] = ow[2];
+            vx[k] = vw[0]; vy[k] = vw[1]; vz[k] = vw[2];
+        }
+        // ---- phase 1: replay four rays, records to the scratch ----
+        int conv[KF];
+        float ux[KF], uy[KF], uz[KF];
+        NodeRecords<KF, 1> rec4;
+        replay_record<CAP>(code, n_instr, spar, P.steps, P.tol, need_stencil ? &P.st : nullptr, P.traj,
+                           px, py, pz, vx, vy, vz, conv, ux, uy, uz, rec4, P.want_grad ? P.nrec : nullptr, P.n_nodes);
+        NodeRecords<1, 1> rec1;                                // c (constant per tape) for the sweeps
+        for (int node = 0; node < P.n_nodes; ++node) rec1.c[node] = rec4.c[node];
+
+        // ---- phase 2: loss, seeds and reverse pass, one ray at a time ----
+#pragma unroll 1
+        for (int j = 0; j < KF; ++j) {
+            const int64_t fj = j == 0 ? first[0] : (j == 1 ? first[1] : (j == 2 ? first[2] : first[3]));
+            const bool valid = fj < n;
+            const int64_t r = shard_ray(P.ray_begin, P.strip_rays, P.strip_stride, fj);
+            const float psx[1] = {pick(px, j)}, psy[1] = {pick(py, j)}, psz[1] = {pick(pz, j)};
+            const float v1x[1] = {pick(vx, j)}, v1y[1] = {pick(vy, j)}, v1z[1] = {pick(vz, j)};
+            const float u0 = pick(ux, j), u1 = pick(uy, j), u2 = pick(uz, j);
+            const int conv1[1] = {j == 0 ? conv[0] : (j == 1 ? conv[1] : (j == 2 ? conv[2] : conv[3]))};
+            float ob[3], vb[3], ow[3], vw[3];
+            world_ray(P.cam, poses, r, pose, cur_view, ob, vb, ow, vw);          // origin, regenerated
+            // residuals and adjoint seeds (the LOSS branch of render_bwd_body)
+            const bool has_n = P.target_lam != nullptr;
+            const float len = sqrt_rn_inline(u0 * u0 + u1 * u1 + u2 * u2);
+            const float il = has_n ? div_rn_inline(1.f, len) : 0.f;
+            const float nx = u0 * il, ny = u1 * il, nz = u2 * il;
+            float g_lam = 0.f, g_dep = 0.f;
+            if (has_n && valid) {
+                const float nv = -(v1x[0] * nx + v1y[0] * ny + v1z[0] * nz);
+                const float res = clamp_nan(nv, 0.f, 1.f) - __ldg(P.target_lam + fj);
+                loss_l = fmaf(res, res, loss_l);
+                g_lam = (!(nv < 0.f) && !(nv > 1.f)) ? 2.f * P.w_lam * res : 0.f;
+            }
+            const float ex = psx[0] - ow[0], ey = psy[0] - ow[1], ez = psz[0] - ow[2];
+            float hx = 0.f, hy = 0.f, hz = 0.f;
+            if (P.target_depth != nullptr && valid) {
+                const float depth = sqrt_rn_inline(ex * ex + ey * ey + ez * ez);
+                const float res = depth - __ldg(P.target_depth + fj);
+                loss_d = fmaf(res, res, loss_d);
+                g_dep = 2.f * P.w_depth * res;
+                const float id = rcp_or_zero(depth);
+                hx = g_dep * ex * id; hy = g_dep * ey * id; hz = g_dep * ez * id;
+            }
+            if (!P.want_grad) continue;                        // loss evaluation only
+            float lx[1] = {hx}, ly[1] = {hy}, lz[1] = {hz};
+            const float gox = -hx, goy = -hy, goz = -hz;
+            float dvx[1] = {-g_lam * nx}, dvy[1] = {-g_lam * ny}, dvz[1] = {-g_lam * nz};
+            StencilAdjoint sa;
+            {
+                const float gnx = -g_lam * v1x[0], gny = -g_lam * v1y[0], gnz = -g_lam * v1z[0];
+                const float gn = gnx * nx + gny * ny + gnz * nz;
+                sa.gux[0] = has_n ? (gnx - gn * nx) * il : 0.f;
+                sa.guy[0] = has_n ? (gny - gn * ny) * il : 0.f;
+                sa.guz[0] = has_n ? (gnz - gn * nz) * il : 0.f;
+                sa.gm[0] = 0.f; sa.gs[0] = 0.f;
+            }
+            reverse_pass<CAP, MODE, true, true, NodeRecords<1, 1>>(code, n_instr, spar, P.steps, &P.st, need_stencil ? &sa : nullptr,
+                                                P.traj, sacc, conv1, psx, psy, psz, v1x, v1y, v1z, lx, ly, lz,
+                                                dvx, dvy, dvz, &rec1, P.nrec, P.n_nodes, KF, j);
+            // camera pose: origin = R(q) o_b + t, dir = R(q) v_b
+            const int view = valid ? (int)(r / per_view) : acc_view;
+            if (view != acc_view) {
+                if (acc_view >= 0) {
+#pragma unroll
+                    for (int i = 0; i < 7; ++i)
+                        if (cam_acc[i] != 0.f) atomicAdd(P.dposes + (size_t)acc_view * POSE_STRIDE + i, cam_acc[i]);
+                }
+#pragma unroll
+                for (int i = 0; i < 7; ++i) cam_acc[i] = 0.f;
+                acc_view = view;
+            }
+            if (valid) {
+                const float lo[3] = {lx[0] + gox, ly[0] + goy, lz[0] + goz};
+                const float lv[3] = {dvx[0], dvy[0], dvz[0]};
+                float dq[4] = {0.f, 0.f, 0.f, 0.f};
+                rotation_vjp(pose.q, ob, lo, dq);
+                rotation_vjp(pose.q, vb, lv, dq);
+                cam_acc[0] += dq[0]; cam_acc[1] += dq[1]; cam_acc[2] += dq[2]; cam_acc[3] += dq[3];
+                cam_acc[4] += lo[0]; cam_acc[5] += lo[1]; cam_acc[6] += lo[2];
+            }
+        }
+    }
+    const float sl = warp_sum(loss_l) * P.w_lam, sd = warp_sum(loss_d) * P.w_depth;
+    if ((threadIdx.x & 31) == 0) {
+        if (P.target_lam != nullptr) atomicAdd(P.loss_out + 0, sl);
+        if (P.target_depth != nullptr) atomicAdd(P.loss_out + 1, sd);
+    }
+    if (!P.want_grad) return;
+    flush_pose_grad(P.dposes, acc_view, cam_acc);
+    flush_accumulators(sacc, P.dpar, n_par);
+}
 // Which of the two: the records pay for themselves once a recording walk over the tape costs more than their
 // traffic and the slower replay (measured: c4b, 69 instructions, 27.3 -> 23.3 ms; c4, 6 instructions,
 // 0.41 -> 0.52 ms).  A tape-specialised library replays straight-line code and never uses them.
-inline bool loss_onfly(const RmTape* t) {
+// Route of rm_render_loss_bwd: 0 = recording walk per reverse task (render_loss_bwd_kernel), 1 = node records,
+// one ray per thread throughout (render_loss_onfly_kernel), 2 = node records with the four-ray replay
+// (render_loss_onfly4_kernel).  RM_B200_LOSS_ROUTE = record | onfly | onfly4 forces one (tests).
+inline int loss_route(const RmTape* t) {
 #if defined(RM_SPEC_INC) || !RM_LOSS_ONFLY
     (void)t;
-    return false;
+    return 0;
 #else
-    int min_instr = RM_LOSS_ONFLY_MIN_INSTR;
-    if (const char* e = getenv("RM_B200_LOSS_ONFLY_MIN_INSTR")) min_instr = atoi(e);   // tests: force either route
-    return t->n_instr >= min_instr;
+    if (const char* e = getenv("RM_B200_LOSS_ROUTE")) {
+        if (e[0] == 'r') return 0;
+        if (e[0] == 'o') return (e[1] == 'n' && e[2] == 'f' && e[3] == 'l' && e[4] == 'y' && e[5] == '4') ? 2 : 1;
+    }
+    return t->n_instr >= RM_LOSS_ONFLY_MIN_INSTR ? (RM_LOSS_TWO_PHASE ? 2 : 1) : 0;
 #endif
+}
+// Launch geometry and scratch of a route: blocks, block-uniform iterations, floats of trajectory and records.
+struct LossLaunch { int route; unsigned grid; int iters; int64_t traj_floats, nrec_floats; };
+inline LossLaunch loss_launch(const RmTape* t, int64_t n_rays, int steps) {
+    LossLaunch L;
+    L.route = loss_route(t);
+    const int kf = L.route == 2 ? KF : KB;
+    const int64_t want = (n_rays + (int64_t)BLOCK_B * kf - 1) / ((int64_t)BLOCK_B * kf);
+    const int64_t cap = 148 * 8;
+    L.iters = (int)((want + cap - 1) / cap > 0 ? (want + cap - 1) / cap : 1);
+    const int64_t blocks = (want + L.iters - 1) / L.iters;
+    L.grid = (unsigned)(blocks > 0 ? blocks : 1);
+    const int64_t slots = (int64_t)L.grid * BLOCK_B;
+    L.traj_floats = (int64_t)steps * kf * slots * 3;
+    L.nrec_floats = L.route == 0 ? 0 : (int64_t)(steps + 4) * (1 + 2 * (int64_t)t->n_nodes) * kf * slots;
+    return L;
 }
 
 inline int check_backward_tape(const RmTape* t) {
@@ -805,9 +1061,8 @@ extern "C" int64_t rm_bwd_scratch_floats(int64_t n_rays, int32_t steps) {
 // rm_render_loss_bwd: the trajectory plus (RM_LOSS_ONFLY) the node records of steps + 4 evaluations.
 extern "C" int64_t rm_loss_scratch_floats(const RmTape* tape, int64_t n_rays, int32_t steps) {
     if (tape == nullptr || n_rays <= 0 || steps < 0) return 0;
-    const int64_t slots = (int64_t)backward_grid(n_rays) * BLOCK_B * KB;
-    const int64_t traj = (int64_t)steps * slots * 3;
-    return loss_onfly(tape) ? traj + (int64_t)(steps + 4) * (1 + 2 * (int64_t)tape->n_nodes) * slots : traj;
+    const LossLaunch L = loss_launch(tape, n_rays, steps);
+    return L.traj_floats + L.nrec_floats;
 }
 
 extern "C" int rm_sdf_vjp(const RmTape* tape, const float* points, const float* grad_sdf, int64_t n,
@@ -909,10 +1164,12 @@ extern "C" int rm_render_loss_bwd(const RmTape* tape, const RmCamera* cam, const
         return s;
     RM_CUDA(cudaMemsetAsync(loss->loss_out, 0, 2 * sizeof(float), (cudaStream_t)stream));
     if (a->n_rays == 0) return RM_OK;
-    if (loss->scratch_floats < rm_loss_scratch_floats(tape, a->n_rays, a->steps))
+    const LossLaunch L = loss_launch(tape, a->n_rays, a->steps);
+    if (loss->scratch_floats < L.traj_floats + L.nrec_floats)
         return fail(RM_ERR_INVALID, "rm_render_loss_bwd: scratch of %lld floats, rm_loss_scratch_floats asks for %lld",
-                    (long long)loss->scratch_floats, (long long)rm_loss_scratch_floats(tape, a->n_rays, a->steps));
-    P.nrec = traj_scratch + (int64_t)a->steps * backward_grid(a->n_rays) * BLOCK_B * KB * 3;
+                    (long long)loss->scratch_floats, (long long)(L.traj_floats + L.nrec_floats));
+    P.nrec = traj_scratch + L.traj_floats;
+    P.iters = L.iters;
 #if RM_LOSS_PATCHES
     {
         const int64_t Wd = cam->width;
@@ -924,12 +1181,12 @@ extern "C" int rm_render_loss_bwd(const RmTape* tape, const RmCamera* cam, const
     P.target_lam = loss->target_lambertian; P.target_depth = loss->target_depth;
     P.w_lam = loss->weight_lambertian; P.w_depth = loss->weight_depth; P.loss_out = loss->loss_out;
     const size_t sm = backward_smem(tape);
-    if (loss_onfly(tape)) {
-        RM_BWD_LAUNCH(tape, render_loss_onfly_kernel, backward_grid(a->n_rays), sm, stream, tape->par, tape->n_instr,
-                      tape->n_par, poses, P);
+    if (L.route == 2) {
+        RM_BWD_LAUNCH(tape, render_loss_onfly4_kernel, L.grid, sm, stream, tape->par, tape->n_instr, tape->n_par, poses, P);
+    } else if (L.route == 1) {
+        RM_BWD_LAUNCH(tape, render_loss_onfly_kernel, L.grid, sm, stream, tape->par, tape->n_instr, tape->n_par, poses, P);
     } else {
-        RM_BWD_LAUNCH(tape, render_loss_bwd_kernel, backward_grid(a->n_rays), sm, stream, tape->par, tape->n_instr,
-                      tape->n_par, poses, P);
+        RM_BWD_LAUNCH(tape, render_loss_bwd_kernel, L.grid, sm, stream, tape->par, tape->n_instr, tape->n_par, poses, P);
     }
     RM_CUDA(cudaGetLastError());
     return RM_OK;

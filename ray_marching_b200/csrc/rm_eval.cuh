@@ -99,7 +99,8 @@ __device__ __forceinline__ int4 tape_ins(const TapeCode<CAP>& C, int pc) { retur
 // CULLMODE: 0 = the code carries no culling flags; 1 = flags present (a culling launch) but this
 // instance evaluates every child (IEEE stencil samples); 2 = cull.
 // RECORD: 0 = value only; 1 = fill the node records and every smooth-union child's value (pass 1 of the
-// scene VJP); 2 = node records only (the replay of the fused loss kernel, whose sweep re-evaluates leaves).
+// scene VJP); 2 = node records only (the replay of the fused loss kernel, whose sweep re-evaluates leaves):
+// REC may then be NodeRecords<K, 1> -- the per-instruction array y is never touched.
 //
 // Culling (one smooth union per tape, tape.py: the largest one).  A child whose term 2^(c f_i) is below
 // 2^CULL_LOG2 of the union's largest term cannot change a float32 logsumexp by more than 2^CULL_LOG2 relative,
@@ -117,13 +118,13 @@ __device__ __forceinline__ int4 tape_ins(const TapeCode<CAP>& C, int pc) { retur
 //     exactly (min(parent, f_U) = parent).
 // render_kernel gives a culling warp a 16 x 8 pixel patch instead of 128 pixels of one row: r_w is what
 // decides how many children survive.
-template <int K, bool FAST, int CAP, int CULLMODE = 0, int RECORD = 0>
+template <int K, bool FAST, int CAP, int CULLMODE = 0, int RECORD = 0, class REC = NodeRecords<K, CAP>>
 __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_instr,
                                            const float4* __restrict__ spar, const float (&px)[K],
                                            const float (&py)[K], const float (&pz)[K],
                                            float (&out)[K], float* hint = nullptr,
                                            const float* move = nullptr,
-                                           NodeRecords<K, CAP>* rec = nullptr) {
+                                           REC* rec = nullptr) {
 #ifdef RM_SPEC_INC
     if constexpr (!RECORD && CULLMODE != 2) {
         eval_spec<K, FAST>(spar, px, py, pz, out);
@@ -410,7 +411,7 @@ __device__ __forceinline__ void eval_scene(const TapeCode<CAP>& C, const int n_i
         if (tail & (FOLD_SMOOTH * 4)) {
 #pragma unroll
             for (int k = 0; k < K; ++k) {
-                if (RECORD == 1) rec->y[pc][k] = d[k];
+                if constexpr (RECORD == 1) rec->y[pc][k] = d[k];
                 const float x = c * d[k];
                 const float e = M::exp(-fabsf(x - a0[k]));
                 a1[k] = (x > a0[k]) ? fmaf(a1[k], e, 1.f) : a1[k] + e;

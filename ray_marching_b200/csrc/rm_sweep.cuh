@@ -181,11 +181,11 @@ __device__ RM_LIVE_INLINE bool smooth_leaf_live(const float4* __restrict__ spar,
 // ONFLY: the records hold the union nodes only (d, win, c); a smooth-union child's value is evaluated here,
 // value-only (FASTM = the math policy of the evaluation that produced the node records), for the liveness test
 // -- one walk over the tape per reverse task instead of a recording walk plus this one.
-template <int K, int CAP, int MODE, bool ONFLY = false, bool FASTM = false>
+template <int K, int CAP, int MODE, bool ONFLY = false, bool FASTM = false, class REC = NodeRecords<K, CAP>>
 __device__ __forceinline__ void sweep_vjp(const TapeCode<CAP>& C, const int n_instr,
                                           const float4* __restrict__ spar, const float (&px)[K],
                                           const float (&py)[K], const float (&pz)[K],
-                                          const float (&abar)[K], const NodeRecords<K, CAP>& rec,
+                                          const float (&abar)[K], const REC& rec,
                                           const GradAcc<MODE> acc, float (&gx)[K], float (&gy)[K],
                                           float (&gz)[K]) {
     OpenNode<K> cur;

@@ -334,15 +334,16 @@ def test_loss_fused_kernel_matches_reference_fixture(golden, tag, build, special
     assert rel_err(flat_grads(list(scene.parameters())), g[f"grads/{tag}/dparams_flat"]) < 1e-3
 
 
-@pytest.mark.parametrize("min_instr", ["0", "100000"])
+@pytest.mark.parametrize("route", ["record", "onfly", "onfly4"])
 @pytest.mark.parametrize("w,h", [(16, 16), (24, 10)])
-def test_loss_kernel_routes_agree_with_the_reference(golden, monkeypatch, min_instr, w, h):
-    """The fused loss kernel has two reverse routes (csrc/rm_backward.cu: loss_onfly) -- a recording walk per
-    reverse task, or union-node records kept from the replay with leaf values re-evaluated by the sweep and
-    children that are dead for the whole warp jumped over -- and two ray layouts (8 x 4-pixel warp patches when
+def test_loss_kernel_routes_agree_with_the_reference(golden, monkeypatch, route, w, h):
+    """The fused loss kernel has three routes (csrc/rm_backward.cu: loss_route) -- a recording walk per reverse
+    task; union-node records kept from the replay, leaf values re-evaluated by the sweep and children that are
+    dead for the whole warp jumped over; the same with a four-ray replay feeding one-ray reverse passes -- and
+    two ray layouts (8 x 4-pixel warp patches when
     the range is whole rows with width % 8 == 0 and rows % 4 == 0, else 32 rays of a row).  Every combination
     against the reference's autograd (fixture, 16 x 16) resp. the composed route (24 x 10: linear tiles)."""
-    monkeypatch.setenv("RM_B200_LOSS_ONFLY_MIN_INSTR", min_instr)
+    monkeypatch.setenv("RM_B200_LOSS_ROUTE", route)
     g = golden("grads")
     tag = "syn8"
     scene = S.make_synthetic_scene(8, 0, True)
