@@ -304,3 +304,33 @@ def test_config4b_gradients_match_reference_fixture(golden, route):
         print(f"c4b {route} {k}: vs reference float32 {e32:.2e}, vs float64 {e64:.2e}; reference float32 vs float64 {noise:.2e}")
         assert noise < 1e-3, "the fixture's own float32 gradient is unusable"
         assert e64 < 1e-3 + noise and e32 < 1e-3 + 2 * noise, (k, e32, e64, noise)
+
+
+def test_config4b_loss_routes_agree_over_several_block_iterations(monkeypatch):
+    """c4b's scene at 512 x 512 -- 262 144 rays, more than one grid-stride iteration of the loss kernels, so the
+    slot-indexed trajectory / node-record scratch is reused -- through the three routes of rm_render_loss_bwd
+    (recording walk; node records; node records with the four-ray replay): loss equal to 1e-6, every gradient
+    to 3e-4 of its size (the routes differ only in the order of float32 sums and, for the liveness test, in
+    the math policy of a value that decides about weights below 1e-9)."""
+    scene = S.make_synthetic_scene(64, 0, True)
+    loop = _loop(scene, 512, 512)
+    q0 = torch.nn.functional.normalize(torch.tensor([[0.98, 0.05, -0.15, 0.02]], device=DEV), dim=-1)
+    t0 = torch.tensor([[0.2, -0.1, -4.0]], device=DEV)
+    gen = torch.Generator().manual_seed(11)
+    lam_t = torch.rand(1, 512, 512, 1, generator=gen).to(DEV)
+    depth_t = (3.0 + 0.5 * torch.rand(1, 512, 512, 1, generator=gen)).to(DEV)
+    out = {}
+    for route in ("record", "onfly", "onfly4"):
+        monkeypatch.setenv("RM_B200_LOSS_ROUTE", route)
+        for p in scene.parameters():
+            p.grad = None
+        q, t = q0.clone().requires_grad_(True), t0.clone().requires_grad_(True)
+        loss = loop.inverse_loss(q, t, lam_t, depth_t, marching_steps=32)
+        loss.backward()
+        flat = torch.cat([(p.grad if p.grad is not None else torch.zeros_like(p)).reshape(-1) for p in scene.parameters()])
+        out[route] = (loss.item(), q.grad.clone(), t.grad.clone(), flat.clone())
+    rel = lambda a, b: ((a - b).abs().max() / (b.abs().max() + 1e-30)).item()
+    for route in ("onfly", "onfly4"):
+        assert abs(out[route][0] - out["record"][0]) < 1e-6 * max(1.0, abs(out["record"][0])), route
+        for i in (1, 2, 3):
+            assert rel(out[route][i], out["record"][i]) < 3e-4, (route, i, rel(out[route][i], out["record"][i]))
