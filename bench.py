@@ -203,7 +203,8 @@ def ncu_traffic(kernel: str, workload: str):
     import glob
     import re
     tag = {"render_kernel": "render", "render_bwd_kernel": "render_bwd",
-           "render_loss_bwd_kernel": "render_loss_bwd", "render_loss_onfly_kernel": "render_loss_onfly", "render_loss_onfly4_kernel": "render_loss_onfly4"}[kernel]
+           "render_loss_bwd_kernel": "render_loss_bwd", "render_loss_onfly_kernel": "render_loss_onfly", "render_loss_onfly4_kernel": "render_loss_onfly4",
+           "loss_replay_kernel + render_loss_reverse_kernel": "render_loss_reverse"}[kernel]
     files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*", f"*_{tag}_{workload}_summary.txt")))
     if not files:
         return None, None
@@ -620,7 +621,8 @@ def measure_e2e(ctx, frame, wl, q, t, my_rays, steps):
 def run_backward(ctx, wl, steps, warmup, headline):
     """c4 / c4b: one Adam step of inverse rendering per step -- the fused loss kernel (camera, march
     replay, stencil, lambertian + raw depth, MSE residuals against a target rendered from perturbed
-    parameters, reverse march, camera-pose contraction: ONE launch, RenderLoop.inverse_loss), the
+    parameters, reverse march, camera-pose contraction: ONE launch -- two for long tapes, whose replay is a
+    kernel of its own -- RenderLoop.inverse_loss), the
     autograd scatter of d loss / d par to the nn.Parameters, the NCCL SUM all-reduce of the flat
     gradient (one view per rank), Adam -- captured as one CUDA graph."""
     from ray_marching_b200 import RenderLoop, ops, parallel
@@ -746,7 +748,7 @@ def run_backward(ctx, wl, steps, warmup, headline):
         n_x = max(3, min(steps, 10))
         extras["routes_eager"] = {"composed_ms_per_step": c_ms / n_x, "fused_ms_per_step": f_ms / n_x,
                                   "note": "eager launches, same optimiser: G-buffer planes + torch loss algebra + "
-                                          "rm_render_bwd (round 1) vs RenderLoop.inverse_loss (one kernel)"}
+                                          "rm_render_bwd (round 1) vs RenderLoop.inverse_loss (one ABI call)"}
 
     def e2e_loop():
         host = torch.empty(1).pin_memory()
@@ -773,8 +775,9 @@ def run_backward(ctx, wl, steps, warmup, headline):
         kmax = max(kern_all)
         alg = (fwd_flops + bwd_flops) * rays          # the kernel does the forward AND the backward
         ach = alg / (kmax * 1e-3) / 1e12
-        # which loss kernel runs (csrc/rm_backward.cu: loss_route): node records on long tapes
-        kname = "render_loss_onfly_kernel" if (not spec_on and tape.n_instr >= 24) else "render_loss_bwd_kernel"
+        # which loss kernels run (csrc/rm_backward.cu: loss_route): long tapes replay in a kernel of their own
+        split = not spec_on and tape.n_instr >= 24
+        kname = "loss_replay_kernel + render_loss_reverse_kernel" if split else "render_loss_bwd_kernel"
         traffic, traffic_src = ncu_traffic(kname, wl["name"])
         rec = {
             "metric": "Mrays/s fwd+bwd", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": steps,
@@ -789,7 +792,7 @@ def run_backward(ctx, wl, steps, warmup, headline):
                        "kernels": spec_note, "adam": adam_note, "n_parameters": sum(p.numel() for p in params) + 7,
                        "per_rank_ms_per_step": Ctx.stats(rank_ms), "wall_ms_per_step": Ctx.stats(rank_wall),
                        "final_loss": float(state["loss"].detach())},
-            "gpu_launches": 1 * steps,
+            "gpu_launches": (2 if split else 1) * steps,
             "roofline": {"bound": "fp32", "kernel": kname, "achieved": ach,
                          "peak": ctx.peak["tflops"], "unit": "TFLOP/s", "frac": ach / ctx.peak["tflops"],
                          "traffic": traffic, "traffic_from": traffic_src, "traffic_unit": "bytes of DRAM per launch",

@@ -47,6 +47,9 @@ namespace rm {
 #ifndef RM_LOSS_PATCHES
 #define RM_LOSS_PATCHES 1   // rm_render_loss_bwd: 8 x 4-pixel warp tiles when the ray range allows (render_bwd_body)
 #endif
+#ifndef RM_LOSS_SPLIT
+#define RM_LOSS_SPLIT 1       // long tapes: replay in a kernel of its own (loss_replay_kernel), reverse in another
+#endif
 #ifndef RM_LOSS_TWO_PHASE
 #define RM_LOSS_TWO_PHASE 0   // 1: long tapes take the four-ray replay (render_loss_onfly4_kernel); measured slower, see below
 #endif
@@ -505,6 +508,8 @@ struct RenderBwdParams {
     float* nrec;            // node-record scratch (RM_LOSS_ONFLY; see nrec_index)
     int n_nodes;
     int patch_cols;         // > 0: a warp owns an 8 x 4 pixel patch (patch_cols = width / 8), see render_bwd_body
+    float* aux;             // split route: per-ray planes (conv, u[3], p_S[3]) + c per node, see loss_replay_kernel
+    int rev_grid;           // split route: blocks of the reverse kernel (the replay kernel addresses ITS slots)
 };
 
 // Adjoint of w = R(q) b w.r.t. q for an upstream adjoint l of w (R = rotation polynomial):
@@ -551,7 +556,7 @@ __device__ __forceinline__ void flush_pose_grad(float* dposes, int view, const f
 //     d/dn = -g_lam v,  d/dv = -g_lam n,  d/dp_S = g_depth e/|e|,  d/do = -g_depth e/|e|   (e = p_S - o)
 // (clamp passes its gradient on the closed interval, the norm has sub-gradient 0 at 0: torch's
 // conventions).  No G-buffer plane, no gradient plane and no elementwise kernel exists on this route.
-template <int CAP, int MODE, bool LOSS, bool ONFLY = false>
+template <int CAP, int MODE, bool LOSS, bool ONFLY = false, bool SPLIT = false>
 __device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const float* par, int n_instr, int n_par,
                                                 const float* __restrict__ poses, const RenderBwdParams& P) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -599,10 +604,25 @@ __device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const
         NodeRec frec_store;                                // ... shared by the replay and the sweeps
         NodeRec* frec = nullptr;
         if constexpr (ONFLY) frec = &frec_store;
-        forward_pass<CAP, LOSS && RM_LOSS_FAST_REPLAY, ONFLY, NodeRec>(code, n_instr, spar, P.steps, P.tol,
-                                                              need_stencil ? &P.st : nullptr, P.traj, px, py, pz,
-                                                              vx, vy, vz, conv, ux, uy, uz, frec,
-                                                              P.want_grad ? P.nrec : nullptr, P.n_nodes);
+        if constexpr (SPLIT) {
+            // the replay ran in loss_replay_kernel: p_S, u, conv of this thread's ray and c per node come back
+            // from its planes; column = (iteration, slot), as reverse_pass addresses it with (kf, ksel) = (iters, it)
+            const size_t n_slots = (size_t)gridDim.x * BLOCK_B, ncols = n_slots * (size_t)P.iters;
+            const size_t col = (size_t)it * n_slots + (size_t)blockIdx.x * BLOCK_B + threadIdx.x;
+            static_assert(!SPLIT || KB == 1, "the split route reverses one ray per thread");
+            const bool mine = first < n;                     // threads past the end own no column: inert values
+            conv[0] = mine ? __float_as_int(P.aux[0 * ncols + col]) : 0;
+            ux[0] = mine ? P.aux[1 * ncols + col] : 0.f; uy[0] = mine ? P.aux[2 * ncols + col] : 0.f;
+            uz[0] = mine ? P.aux[3 * ncols + col] : 1.f;
+            px[0] = mine ? P.aux[4 * ncols + col] : 0.f; py[0] = mine ? P.aux[5 * ncols + col] : 0.f;
+            pz[0] = mine ? P.aux[6 * ncols + col] : 0.f;
+            for (int node = 0; node < P.n_nodes; ++node) frec->c[node] = P.aux[7 * ncols + node];
+        } else {
+            forward_pass<CAP, LOSS && RM_LOSS_FAST_REPLAY, ONFLY, NodeRec>(code, n_instr, spar, P.steps, P.tol,
+                                                                  need_stencil ? &P.st : nullptr, P.traj, px, py, pz,
+                                                                  vx, vy, vz, conv, ux, uy, uz, frec,
+                                                                  P.want_grad ? P.nrec : nullptr, P.n_nodes);
+        }
 
         // ---- adjoints of the stencil outputs (SDFNormals.forward, ray_marching.py:115-125), of
         //      f(p_S) (control.py:244), of p_S, the direction and the origin ----
@@ -676,7 +696,8 @@ __device__ __forceinline__ void render_bwd_body(const TapeCode<CAP>& code, const
         // ---- reverse pass: stencil samples, converged tail, exact steps ----
         reverse_pass<CAP, MODE, LOSS && RM_LOSS_FAST_REPLAY, ONFLY, NodeRec>(code, n_instr, spar, P.steps, &P.st,
                           (need_stencil || (!LOSS && P.g.sdf != nullptr)) ? &sa : nullptr, P.traj, sacc, conv,
-                          px, py, pz, vx, vy, vz, lx, ly, lz, dvx, dvy, dvz, frec, P.nrec, P.n_nodes);
+                          px, py, pz, vx, vy, vz, lx, ly, lz, dvx, dvy, dvz, frec, P.nrec, P.n_nodes,
+                          SPLIT ? P.iters : 1, SPLIT ? it : 0);
 
         // ---- camera pose: origin = R(q) o_b + t, dir = R(q) v_b ----
 #pragma unroll
@@ -944,9 +965,132 @@ render_loss_onfly4_kernel(const __grid_constant__ TapeCode<CAP> code, const floa
 // Which of the two: the records pay for themselves once a recording walk over the tape costs more than their
 // traffic and the slower replay (measured: c4b, 69 instructions, 27.3 -> 23.3 ms; c4, 6 instructions,
 // 0.41 -> 0.52 ms).  A tape-specialised library replays straight-line code and never uses them.
+// ---- split route for long tapes: loss_replay_kernel + render_loss_reverse_kernel ------------------------
+// Inside the 128-register loss kernel (16 warps per SM) the replay runs far below what the forward kernel
+// reaches on the same interpreter.  Here it is a kernel of its own, shaped like render_kernel -- four rays per
+// thread, 256 threads, 64 registers, 32 warps per SM -- that writes every ray's trajectory, node records and
+// (conv, u, p_S) to per-ray planes; the reverse kernel is the one-ray body of the node-record route without its
+// replay.  The planes are addressed the way the REVERSE kernel numbers its threads: column = (iteration,
+// slot), so reverse_pass finds them with (kf, ksel) = (iterations, iteration) and nothing else changes.
+__device__ __forceinline__ size_t reverse_column(const RenderBwdParams& P, int64_t f) {
+    // global thread index g of the reverse kernel that owns local ray f (the inverse of its ray mapping)
+    int64_t g = f;
+    if (P.patch_cols > 0) {
+        const unsigned row = (unsigned)(f / P.cam.width), colp = (unsigned)(f - (int64_t)row * P.cam.width);
+        const unsigned t = (row >> 2) * (unsigned)P.patch_cols + (colp >> 3);
+        g = (int64_t)t * 32 + ((row & 3u) << 3) + (colp & 7u);
+    }
+    return (size_t)g;          // = iteration * n_slots + slot, because slot = g mod n_slots and iteration = g / n_slots
+}
+
+constexpr int BLOCK_A = 256;      // replay kernel: the forward kernel's launch shape (256 threads x 4 rays, 64 registers)
+template <int CAP>
+__global__ void __launch_bounds__(BLOCK_A, 4)
+loss_replay_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
+                   const float* __restrict__ poses, const __grid_constant__ RenderBwdParams P) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const float4* spar = stage_params(par, n_par, smem);
+    const int64_t n = P.n_rays;
+    const size_t ncols = (size_t)P.rev_grid * BLOCK_B * (size_t)P.iters;
+    const int nr = 1 + 2 * P.n_nodes;
+    const int64_t first = ((int64_t)blockIdx.x * BLOCK_A + threadIdx.x) * KF;
+    // no early return: the replay votes with full-warp masks; rays past the end are clamped duplicates, not stored
+    float px[KF], py[KF], pz[KF], vx[KF], vy[KF], vz[KF];
+    size_t col[KF];
+    bool valid[KF];
+    Pose pose;
+    int cur_view = -1;
+#pragma unroll
+    for (int k = 0; k < KF; ++k) {
+        valid[k] = first + k < n;
+        col[k] = reverse_column(P, valid[k] ? first + k : 0);
+        float ob[3], vb[3], ow[3], vw[3];
+        world_ray(P.cam, poses, shard_ray(P.ray_begin, P.strip_rays, P.strip_stride, valid[k] ? first + k : n - 1), pose, cur_view, ob, vb, ow, vw);
+        px[k] = ow[0]; py[k] = ow[1]; pz[k] = ow[2];
+        vx[k] = vw[0]; vy[k] = vw[1]; vz[k] = vw[2];
+    }
+    const Stencil* st = P.target_lam != nullptr ? &P.st : nullptr;
+    int conv[KF];
+    float ux[KF], uy[KF], uz[KF], o0[KF], prev[KF];
+#pragma unroll
+    for (int k = 0; k < KF; ++k) { conv[k] = 0; ux[k] = uy[k] = uz[k] = o0[k] = 0.f; prev[k] = -1.f; }
+    NodeRecords<KF, 1> rec;
+    const int n_tasks = P.steps + (st != nullptr ? 4 : 0);
+    for (int task = 0; task < n_tasks; ++task) {               // forward_pass, four rays wide, per-ray planes
+        const bool marching = task < P.steps;
+        const int j = marching ? 4 : task - P.steps;
+        float x[KF], y[KF], z[KF], d[KF];
+        float dx = 0.f, dy = 0.f, dz = 0.f;
+        if (!marching) { dx = st->off[j][0]; dy = st->off[j][1]; dz = st->off[j][2]; }
+        else {
+#pragma unroll
+            for (int k = 0; k < KF; ++k)
+                if (valid[k]) {
+                    float* p = P.traj + ((size_t)task * ncols + col[k]) * 3;
+                    p[0] = px[k]; p[1] = py[k]; p[2] = pz[k];
+                }
+        }
+#pragma unroll
+        for (int k = 0; k < KF; ++k) { x[k] = px[k] + dx; y[k] = py[k] + dy; z[k] = pz[k] + dz; }
+        eval_scene<KF, true, CAP, 0, 2, NodeRecords<KF, 1>>(code, n_instr, spar, x, y, z, d, nullptr, nullptr, &rec);
+#pragma unroll
+        for (int k = 0; k < KF; ++k)
+            if (valid[k]) {
+                float* q = P.nrec + (size_t)task * nr * ncols + col[k];
+                q[0] = d[k];
+                for (int node = 0; node < P.n_nodes; ++node) {
+                    q[(size_t)(1 + 2 * node) * ncols] = rec.d[node][k];
+                    q[(size_t)(2 + 2 * node) * ncols] = __int_as_float(rec.win[node][k]);
+                }
+            }
+        if (marching) {
+            bool at_rest = true;
+#pragma unroll
+            for (int k = 0; k < KF; ++k) {
+                const float scale = 1.f + fmaxf(fabsf(px[k]), fmaxf(fabsf(py[k]), fabsf(pz[k])));
+                const float ad = fabsf(d[k]);
+                const bool within = ad <= P.tol * scale;                     // false for NaN
+                if (!within) conv[k] = task + 1;
+                at_rest = at_rest && within && prev[k] >= ad;
+                prev[k] = within ? ad : -1.f;
+                px[k] = fmaf(d[k], vx[k], px[k]); py[k] = fmaf(d[k], vy[k], py[k]); pz[k] = fmaf(d[k], vz[k], pz[k]);
+            }
+#if RM_BWD_EARLY_BREAK
+            if (__all_sync(0xffffffffu, at_rest)) task = P.steps - 1;
+#endif
+        } else {
+            const float wx = st->w[j][0], wy = st->w[j][1], wz = st->w[j][2], firstw = st->first[j];
+#pragma unroll
+            for (int k = 0; k < KF; ++k) {
+                o0[k] = firstw != 0.f ? d[k] : o0[k];
+                const float dj = d[k] - o0[k];
+                ux[k] = fmaf(wx, dj, ux[k]); uy[k] = fmaf(wy, dj, uy[k]); uz[k] = fmaf(wz, dj, uz[k]);
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < KF; ++k)
+        if (valid[k]) {
+            float* a = P.aux + col[k];
+            a[0] = __int_as_float(conv[k]);
+            a[1 * ncols] = ux[k]; a[2 * ncols] = uy[k]; a[3 * ncols] = uz[k];
+            a[4 * ncols] = px[k]; a[5 * ncols] = py[k]; a[6 * ncols] = pz[k];
+        }
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+        for (int node = 0; node < P.n_nodes; ++node) P.aux[7 * ncols + node] = rec.c[node];
+}
+
+template <int CAP, int MODE>
+__global__ void __launch_bounds__(BLOCK_B, RM_MINB_BWD)
+render_loss_reverse_kernel(const __grid_constant__ TapeCode<CAP> code, const float* par, int n_instr, int n_par,
+                           const float* __restrict__ poses, const __grid_constant__ RenderBwdParams P) {
+    render_bwd_body<CAP, MODE, true, true, true>(code, par, n_instr, n_par, poses, P);
+}
+
 // Route of rm_render_loss_bwd: 0 = recording walk per reverse task (render_loss_bwd_kernel), 1 = node records,
 // one ray per thread throughout (render_loss_onfly_kernel), 2 = node records with the four-ray replay
-// (render_loss_onfly4_kernel).  RM_B200_LOSS_ROUTE = record | onfly | onfly4 forces one (tests).
+// (render_loss_onfly4_kernel), 3 = node records written by a replay kernel of its own (loss_replay_kernel +
+// render_loss_reverse_kernel).  RM_B200_LOSS_ROUTE = record | onfly | onfly4 | split forces one (tests).
 inline int loss_route(const RmTape* t) {
 #if defined(RM_SPEC_INC) || !RM_LOSS_ONFLY
     (void)t;
@@ -954,16 +1098,19 @@ inline int loss_route(const RmTape* t) {
 #else
     if (const char* e = getenv("RM_B200_LOSS_ROUTE")) {
         if (e[0] == 'r') return 0;
+        if (e[0] == 's') return 3;
         if (e[0] == 'o') return (e[1] == 'n' && e[2] == 'f' && e[3] == 'l' && e[4] == 'y' && e[5] == '4') ? 2 : 1;
     }
-    return t->n_instr >= RM_LOSS_ONFLY_MIN_INSTR ? (RM_LOSS_TWO_PHASE ? 2 : 1) : 0;
+    return t->n_instr >= RM_LOSS_ONFLY_MIN_INSTR ? (RM_LOSS_SPLIT ? 3 : (RM_LOSS_TWO_PHASE ? 2 : 1)) : 0;
 #endif
 }
 // Launch geometry and scratch of a route: blocks, block-uniform iterations, floats of trajectory and records.
-struct LossLaunch { int route; unsigned grid; int iters; int64_t traj_floats, nrec_floats; };
-inline LossLaunch loss_launch(const RmTape* t, int64_t n_rays, int steps) {
+struct LossLaunch { int route; unsigned grid; int iters; int64_t traj_floats, nrec_floats, aux_floats; };
+inline LossLaunch loss_launch(const RmTape* t, int64_t n_rays, int steps, bool want_grad = true) {
     LossLaunch L;
     L.route = loss_route(t);
+    if (L.route == 3 && !want_grad) L.route = 1;          // loss only: one kernel, nothing to hand over
+    L.aux_floats = 0;
     const int kf = L.route == 2 ? KF : KB;
     const int64_t want = (n_rays + (int64_t)BLOCK_B * kf - 1) / ((int64_t)BLOCK_B * kf);
     const int64_t cap = 148 * 8;
@@ -973,6 +1120,18 @@ inline LossLaunch loss_launch(const RmTape* t, int64_t n_rays, int steps) {
     const int64_t slots = (int64_t)L.grid * BLOCK_B;
     L.traj_floats = (int64_t)steps * kf * slots * 3;
     L.nrec_floats = L.route == 0 ? 0 : (int64_t)(steps + 4) * (1 + 2 * (int64_t)t->n_nodes) * kf * slots;
+    if (L.route == 3) {                                    // per-ray planes: a column per (iteration, slot)
+        const int64_t ncols = slots * L.iters;
+        L.traj_floats = (int64_t)steps * ncols * 3;
+        L.nrec_floats = (int64_t)(steps + 4) * (1 + 2 * (int64_t)t->n_nodes) * ncols;
+        L.aux_floats = 7 * ncols + MAX_NODES;
+        if (L.traj_floats + L.nrec_floats + L.aux_floats > (int64_t)1 << 31) {   // > 8 GB of planes: one-kernel route
+            L.route = 1;
+            L.aux_floats = 0;
+            L.traj_floats = (int64_t)steps * kf * slots * 3;
+            L.nrec_floats = (int64_t)(steps + 4) * (1 + 2 * (int64_t)t->n_nodes) * kf * slots;
+        }
+    }
     return L;
 }
 
@@ -1062,7 +1221,7 @@ extern "C" int64_t rm_bwd_scratch_floats(int64_t n_rays, int32_t steps) {
 extern "C" int64_t rm_loss_scratch_floats(const RmTape* tape, int64_t n_rays, int32_t steps) {
     if (tape == nullptr || n_rays <= 0 || steps < 0) return 0;
     const LossLaunch L = loss_launch(tape, n_rays, steps);
-    return L.traj_floats + L.nrec_floats;
+    return L.traj_floats + L.nrec_floats + L.aux_floats;
 }
 
 extern "C" int rm_sdf_vjp(const RmTape* tape, const float* points, const float* grad_sdf, int64_t n,
@@ -1130,7 +1289,7 @@ static int prepare_render_bwd(const char* who, const RmTape* tape, const RmCamer
     P->traj = traj_scratch; P->dpar = dpar; P->dposes = dposes;
     P->target_lam = P->target_depth = nullptr; P->w_lam = P->w_depth = 0.f; P->loss_out = nullptr;
     P->want_grad = want_grad ? 1 : 0;
-    P->nrec = nullptr; P->n_nodes = tape->n_nodes; P->patch_cols = 0;
+    P->nrec = nullptr; P->n_nodes = tape->n_nodes; P->patch_cols = 0; P->aux = nullptr; P->rev_grid = 0;
     return RM_OK;
 }
 
@@ -1164,12 +1323,14 @@ extern "C" int rm_render_loss_bwd(const RmTape* tape, const RmCamera* cam, const
         return s;
     RM_CUDA(cudaMemsetAsync(loss->loss_out, 0, 2 * sizeof(float), (cudaStream_t)stream));
     if (a->n_rays == 0) return RM_OK;
-    const LossLaunch L = loss_launch(tape, a->n_rays, a->steps);
-    if (loss->scratch_floats < L.traj_floats + L.nrec_floats)
+    const LossLaunch L = loss_launch(tape, a->n_rays, a->steps, want_grad);
+    if (loss->scratch_floats < L.traj_floats + L.nrec_floats + L.aux_floats)
         return fail(RM_ERR_INVALID, "rm_render_loss_bwd: scratch of %lld floats, rm_loss_scratch_floats asks for %lld",
-                    (long long)loss->scratch_floats, (long long)(L.traj_floats + L.nrec_floats));
+                    (long long)loss->scratch_floats, (long long)(L.traj_floats + L.nrec_floats + L.aux_floats));
     P.nrec = traj_scratch + L.traj_floats;
+    P.aux = P.nrec + L.nrec_floats;
     P.iters = L.iters;
+    P.rev_grid = (int)L.grid;
 #if RM_LOSS_PATCHES
     {
         const int64_t Wd = cam->width;
@@ -1181,7 +1342,18 @@ extern "C" int rm_render_loss_bwd(const RmTape* tape, const RmCamera* cam, const
     P.target_lam = loss->target_lambertian; P.target_depth = loss->target_depth;
     P.w_lam = loss->weight_lambertian; P.w_depth = loss->weight_depth; P.loss_out = loss->loss_out;
     const size_t sm = backward_smem(tape);
-    if (L.route == 2) {
+    if (L.route == 3) {
+        // replay: four rays per thread, the forward kernel's launch shape; then the reverse kernel
+        const size_t sm_a = tape_smem_bytes(tape);
+        const unsigned grid_a = (unsigned)((a->n_rays + (int64_t)BLOCK_A * KF - 1) / ((int64_t)BLOCK_A * KF));
+        RM_WITH_CODE(tape, {
+            if (int s_ = prepare_smem(loss_replay_kernel<CAP>, sm_a)) return s_;
+            loss_replay_kernel<CAP><<<grid_a, BLOCK_A, sm_a, (cudaStream_t)stream>>>(code, tape->par, tape->n_instr,
+                                                                                   tape->n_par, poses, P);
+        });
+        RM_CUDA(cudaGetLastError());
+        RM_BWD_LAUNCH(tape, render_loss_reverse_kernel, L.grid, sm, stream, tape->par, tape->n_instr, tape->n_par, poses, P);
+    } else if (L.route == 2) {
         RM_BWD_LAUNCH(tape, render_loss_onfly4_kernel, L.grid, sm, stream, tape->par, tape->n_instr, tape->n_par, poses, P);
     } else if (L.route == 1) {
         RM_BWD_LAUNCH(tape, render_loss_onfly_kernel, L.grid, sm, stream, tape->par, tape->n_instr, tape->n_par, poses, P);

@@ -334,7 +334,7 @@ def test_loss_fused_kernel_matches_reference_fixture(golden, tag, build, special
     assert rel_err(flat_grads(list(scene.parameters())), g[f"grads/{tag}/dparams_flat"]) < 1e-3
 
 
-@pytest.mark.parametrize("route", ["record", "onfly", "onfly4"])
+@pytest.mark.parametrize("route", ["record", "onfly", "onfly4", "split"])
 @pytest.mark.parametrize("w,h", [(16, 16), (24, 10)])
 def test_loss_kernel_routes_agree_with_the_reference(golden, monkeypatch, route, w, h):
     """The fused loss kernel has three routes (csrc/rm_backward.cu: loss_route) -- a recording walk per reverse
