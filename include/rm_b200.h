@@ -256,7 +256,8 @@ int64_t rm_loss_scratch_floats(const RmTape* tape, int64_t n_rays, int32_t steps
  *     loss = w_l sum_r (clamp(-v.n, 0, 1)_r - lam*_r)^2 + w_d sum_r (|p_S - o|_r - depth*_r)^2,
  * over the pipeline of RenderLoop.forward (control.py:239-245) + LambertianShader (shader.py:16-20), in
  * ONE kernel: rays from the pixel index, march replay, stencil, shading, residuals and adjoint seeds in
- * registers, reverse march, camera-pose contraction.  What torch.autograd does through the reference's
+ * registers, reverse march, camera-pose contraction (tapes of >= 24 instructions: two kernels -- the replay at
+ * four rays per thread writes per-ray planes into `scratch`, the reverse kernel reads them).  What torch.autograd does through the reference's
  * unrolled graph plus its loss algebra; no G-buffer or gradient plane touches memory.
  * Writes loss->loss_out[2], d loss / d par [tape->n_par] and d loss / d poses [n_views][RM_POSE_STRIDE]
  * (overwritten; gradients of the SUM of both terms with unit upstream).  dpar == dposes == NULL evaluates
