@@ -75,3 +75,43 @@ def test_cpu_tensors_are_rejected_loudly():
     from ray_marching_b200 import scene as S
     with pytest.raises(_lib.RmError):
         S.SDFSphere(0.5)(torch.zeros(4, 3))
+
+
+def test_loss_scratch_size_follows_the_route(monkeypatch):
+    """rm_loss_scratch_floats (host arithmetic only): short tapes take the recording route (trajectory, slot
+    indexed); long tapes the split route (per-ray planes of trajectory, node records and (conv, u, p_S));
+    ranges whose planes would exceed 8 GB fall back to the slot-indexed node-record route; the test override
+    RM_B200_LOSS_ROUTE moves the size with the route."""
+    handle = _lib.lib()
+    steps, block = 32, 128
+    size = lambda tape, n: int(handle.rm_loss_scratch_floats(ctypes.byref(tape), n, steps))
+
+    def geometry(n, rays_per_block):
+        want = -(-n // rays_per_block)
+        iters = max(1, -(-want // (148 * 8)))
+        return -(-want // iters), iters                       # blocks, block-uniform iterations
+
+    short = _lib.RmTape(0, 0, 6, 24, 1, 1)                    # scene2-like: 6 instructions
+    long_ = _lib.RmTape(0, 0, 69, 1420, 2, 2)                 # c4b-like: 69 instructions, 2 union nodes
+    monkeypatch.delenv("RM_B200_LOSS_ROUTE", raising=False)
+    n = 1 << 20
+    grid, iters = geometry(n, block)
+    slots = grid * block
+    assert size(short, n) == steps * slots * 3
+    ncols = slots * iters
+    nr = 1 + 2 * 2
+    assert size(long_, n) == steps * ncols * 3 + (steps + 4) * nr * ncols + 7 * ncols + 16
+    assert ncols >= n
+    # 2^26 rays: the planes would take ~19 G floats -> the slot-indexed route (independent of the ray count)
+    big = 1 << 26
+    gridb, _ = geometry(big, block)
+    assert size(long_, big) == steps * gridb * block * 3 + (steps + 4) * nr * gridb * block
+    assert size(long_, big) < 1 << 31
+    for route, expect in (("record", steps * slots * 3),
+                          ("onfly", steps * slots * 3 + (steps + 4) * nr * slots)):
+        monkeypatch.setenv("RM_B200_LOSS_ROUTE", route)
+        assert size(long_, n) == expect, route
+    monkeypatch.setenv("RM_B200_LOSS_ROUTE", "onfly4")
+    g4, _ = geometry(n, block * 4)
+    assert size(long_, n) == steps * 4 * g4 * block * 3 + (steps + 4) * nr * 4 * g4 * block
+    assert size(long_, 0) == 0 and size(long_, -5) == 0
